@@ -1,0 +1,290 @@
+#!/usr/bin/env python
+"""bench.py -- MTL samples/s on synthetic DAS patches (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--batch B] [--precision bf16|fp32]
+
+Workload (config.workload): BASELINE.json configs[1] -- MTL (model A) inference, batch 4096 synthetic
+patches per GPU, eval-mode BatchNorm, log-probs for both tasks.  A "step" is one forward pass of the hot
+path over the batch.  `value` is timed with inputs resident in HBM (410 MB > L2, so no L2 flush is
+needed between iterations); `e2e` goes through the C-ABI host entry point (pinned host buffers, H2D
+of the patches and D2H of the log-probs inside the timed region).  N > 1: every rank runs its own batch
+(window/batch sharding, no data-path collective) -> weak scaling; time = max over ranks (device events).
+
+`--impl reference` times the reference's CPU path (the oracle port: the same torch-CPU ATen ops the
+reference's nn.Module executes; the reference is pure Python so there is nothing to compile into
+oracle/_ref) on the host cores, on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "mtl-das.pytorch_b200")
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+METRIC = "MTL samples/sec (inference; train fwd+bwd) on synthetic DAS patches"
+UNIT = "samples/s"
+PATCH_BYTES = 100 * 250 * 4
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=4096, help="patches per GPU per step")
+    ap.add_argument("--micro-batch", type=int, default=int(os.environ.get("MTLDAS_MICRO_BATCH", "256")))
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--cpu-sample", type=int, default=256, help="patches per CPU-baseline step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port on the host cores
+# ------------------------------------------------------------------------------------------------
+def cpu_samples_per_s(sample, steps, warmup):
+    import torch
+    from oracle import mtl_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = O.synth_state_dict("MTL", seed=0)
+    x, _, _ = O.synth_patches(sample, seed=1234)
+    with torch.no_grad():
+        for _ in range(warmup):
+            O.forward(sd, x, "MTL", training=False)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            O.forward(sd, x, "MTL", training=False)
+        dt = time.perf_counter() - t0
+    return sample * steps / dt, dt / steps * 1e3, cores
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    val, ms, cores = cpu_samples_per_s(args.cpu_sample, args.steps, args.warmup)
+    sample = f"{args.cpu_sample} patches/step x {args.steps} steps, eval forward, torch CPU fp32, {cores} threads"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "MTL (model A) inference, synthetic DAS patches [1,100,250] (bounded CPU sample)",
+                   "batch_per_step": args.cpu_sample},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for t, line in self.rows:
+            f = [s.strip() for s in line.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                mhz, mx = float(f[1]), float(f[2])
+            except ValueError:
+                continue
+            if t0 - 0.05 <= t <= t1 + 0.05:
+                sm.append(mhz)
+                for nme, v in zip(names, f[4:8]):
+                    if v == "Active":
+                        reasons.add(nme)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# algorithmic bytes of the conv kernel launches (each reference conv reads its input once
+# and writes its output once, bf16 storage, weights ignored)
+# ------------------------------------------------------------------------------------------------
+def conv_algorithmic_elems_per_sample(desc):
+    layers = {L["conv"]: L for L in desc["layers"]}
+    per_op = []
+    for op in desc["program"]:
+        if op["op"] != "conv":
+            per_op.append(0)
+            continue
+        e = 0
+        for g in op["groups"]:
+            for s in g["segs"]:
+                L = layers[s["layer"]]
+                ho, wo = op["H"], op["W"]
+                hi, wi = (ho, wo) if L["stride"] == 1 else {17: (33, 83), 9: (17, 42), 5: (9, 21)}[ho]
+                e += L["cin"] * hi * wi + L["cout"] * ho * wo
+        per_op.append(e)
+    return per_op
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from oracle import mtl_oracle as O          # synthetic weights / patches generator (and CPU baseline leg)
+    from mtldas_b200 import EvalPlan
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    B = args.batch
+    plan = EvalPlan("MTL", args.micro_batch, args.precision, dev)
+    sd = O.synth_state_dict("MTL", seed=0)
+    plan.pack({k: v.to(dev) for k, v in sd.items()})
+    # synthetic patches: 64 distinct oracle patches tiled to the batch (+ per-rank roll so ranks differ)
+    base, _, _ = O.synth_patches(64, seed=1234 + rank)
+    x_host = base.repeat((B + 63) // 64, 1, 1, 1)[:B].contiguous().pin_memory()
+    x = x_host.to(dev)
+    outs_host = [torch.empty((B, c), dtype=torch.float32).pin_memory() for c in plan.classes]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing -------------------------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        plan.forward(x)
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    t_wall0 = time.perf_counter()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        outs = plan.forward(x)
+    e1.record()
+    barrier()
+    t_wall1 = time.perf_counter()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    launches = plan.last_launch_count * args.steps
+    clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
+
+    # ---- end to end through the host entry point ----------------------------------------------------
+    for _ in range(2):
+        plan.forward_host(x_host, outs_host)
+    barrier()
+    e2e_steps = max(3, min(args.steps, 10))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        plan.forward_host(x_host, outs_host)
+    barrier()
+    e2e_s = torch.tensor([time.perf_counter() - t0], device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_val = world * B * e2e_steps / float(e2e_s.item())
+
+    # ---- live per-kernel durations for the roofline (CUDA events around every launch) --------------
+    roof = None
+    if rank == 0:
+        desc = plan.describe()
+        per_op_ms = plan.profile(x)
+        elems = conv_algorithmic_elems_per_sample(desc)
+        conv_ms = sum(m for m, op in zip(per_op_ms, desc["program"]) if op["op"] == "conv")
+        conv_bytes = sum(elems) * B * (2 if args.precision == "bf16" else 4)
+        passes = (B + args.micro_batch - 1) // args.micro_batch
+        n_conv = sum(1 for op in desc["program"] if op["op"] == "conv") * passes
+        peak = 6650.0
+        peak_src = "fallback"
+        try:
+            peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+            peak_src = "measured"
+        except Exception:
+            pass
+        ach = conv_bytes / (conv_ms * 1e-3) / 1e9
+        roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                "kernel": "conv_umma_kernel" if args.precision == "bf16" else "conv_fp32_kernel",
+                "launches_per_step": n_conv, "avg_launch_ms": conv_ms / n_conv,
+                "algorithmic_bytes_per_step": conv_bytes, "peak_source": peak_src,
+                "share_of_step": conv_ms / sum(per_op_ms),
+                "per_op_ms": {(op.get("name") or op["op"]) + f"#{i}": round(m, 4)
+                              for i, (m, op) in enumerate(zip(per_op_ms, desc["program"]))}}
+
+    if rank == 0:
+        value = world * B * args.steps / (ms_total * 1e-3)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
+            "config": {"workload": "MTL (model A) inference, eval-mode BN, batch %d synthetic DAS patches [1,100,250] "
+                                   "per GPU (BASELINE.json configs[1])" % B,
+                       "batch_per_gpu": B, "micro_batch": args.micro_batch, "precision": args.precision,
+                       "l2": "inputs (%.0f MB/step) larger than L2; no flush" % (B * PATCH_BYTES / 1e6),
+                       "parallelism": "batch-sharded x%d, no collective" % world},
+            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": B * PATCH_BYTES,
+                    "d2h_bytes_per_step": B * sum(plan.classes) * 4},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": roof,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            steps = 16
+            val, cms, cores = cpu_samples_per_s(args.cpu_sample, steps, 2)
+            line["cpu_baseline"] = {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
+                                    "sample": f"{args.cpu_sample} patches/step x {steps} steps, eval forward, "
+                                              f"torch CPU fp32 oracle port, {cores} threads"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.gpus > 1 and "RANK" not in os.environ:
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.abspath(__file__)] + sys.argv[1:]
+        sys.exit(subprocess.call(cmd))
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,133 @@
+/*
+ * mtldas.h -- C ABI of libmtldas_b200.so: the B200 (sm_100a) implementation of the
+ * MTL-DAS hot path (forward / backward of the two-level multi-task CNN).
+ *
+ * The reference (sunmin123456/MTL-DAS.PyTorch) has no FFI of its own: its "plugin
+ * boundary" is the Python nn.Module protocol used by utils.py.  Every entry point below
+ * therefore cites the reference *Python* interface it serves; the ctypes binding that a
+ * maintainer adds on the reference side is shown in INTEGRATION.md and implemented in
+ * mtl-das.pytorch_b200/mtldas_b200/_lib.py.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; all `dev` pointers are device pointers owned by the
+ *     caller, all `host` pointers are host pointers owned by the caller;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*) unless the
+ *     name ends in `_host` (those synchronise the stream before returning);
+ *   - return value 0 = OK, negative = error; text via mtldas_last_error() (thread local);
+ *   - the library keeps no pointer beyond the call except the workspace bound to a plan;
+ *   - current-device semantics: the caller makes the plan's device current;
+ *   - there is NO CPU fallback anywhere: without a B200 the compute calls fail.
+ */
+#ifndef MTLDAS_H_
+#define MTLDAS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define MTLDAS_API __attribute__((visibility("default")))
+#else
+#define MTLDAS_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MTLDAS_OK 0
+#define MTLDAS_ERR_ARG -1
+#define MTLDAS_ERR_CUDA -2
+#define MTLDAS_ERR_STATE -3
+#define MTLDAS_ERR_UNSUPPORTED -4
+
+/* model kinds: utils.py:85-96 (`--model MTL | single_distance | single_event`) */
+#define MTLDAS_MODEL_MTL 0             /* model/modelA_MTL.py:53  MTL_Net()                        */
+#define MTLDAS_MODEL_SINGLE_DISTANCE 1 /* model/modelB_singleTask.py:53 Single_Task_Net('distance') */
+#define MTLDAS_MODEL_SINGLE_EVENT 2    /* model/modelB_singleTask.py:53 Single_Task_Net('event')    */
+
+/* arithmetic of the convolutions (BASELINE.json north_star: "FP32 path" / "BF16 tensor-core path") */
+#define MTLDAS_PREC_BF16 0 /* tcgen05 (UMMA) bf16 x bf16 -> fp32 TMEM accumulators, bf16 activations in HBM */
+#define MTLDAS_PREC_FP32 1 /* CUDA-core FFMA, fp32 activations in HBM                                       */
+
+/* epilogues of the single-conv entry point */
+#define MTLDAS_EPI_NONE 0        /* y = conv + bias                                   */
+#define MTLDAS_EPI_RELU 1        /* relu(y)                 modelA_MTL.py:16,47,102   */
+#define MTLDAS_EPI_ADD_RELU 2    /* relu(y + aux)           modelA_MTL.py:29-30       */
+#define MTLDAS_EPI_SIGMOID_MUL 3 /* sigmoid(y) * aux        modelA_MTL.py:50,144      */
+
+typedef struct mtldas_plan mtldas_plan; /* opaque; not thread safe; distinct plans may run concurrently */
+
+/* library identity / error text ------------------------------------------------------------ */
+MTLDAS_API const char* mtldas_version(void);
+MTLDAS_API const char* mtldas_last_error(void);
+/* 1 if the current device is compute capability 10.x, 0 otherwise (no device: 0). */
+MTLDAS_API int mtldas_device_ok(void);
+
+/* plan life cycle ---------------------------------------------------------------------------
+ * Replaces: constructing the module and moving it to the GPU
+ *   utils.py:85-96 (model = MTL_Net() / Single_Task_Net(task=...)), utils.py:124-125 (model.cuda()).
+ * `micro_batch` is the number of patches processed per pass over the layer program (the
+ * workspace is sized for it; any batch size is accepted by forward and is cut into passes). */
+MTLDAS_API mtldas_plan* mtldas_plan_create(int model_kind, int micro_batch, int precision);
+MTLDAS_API void mtldas_plan_destroy(mtldas_plan* plan);
+/* number of state_dict entries the plan expects (268 for MTL, 194 for single task: SURVEY.md App. C) */
+MTLDAS_API int mtldas_plan_num_state_entries(const mtldas_plan* plan);
+/* key of entry i in state_dict order, e.g. "att_mask_generato2.0.0.weight" (modelA_MTL.py:93, typo kept) */
+MTLDAS_API const char* mtldas_plan_state_key(const mtldas_plan* plan, int i);
+MTLDAS_API size_t mtldas_plan_workspace_bytes(const mtldas_plan* plan);
+/* Bind caller-owned device scratch (>= workspace_bytes, 256-byte aligned).  Zero-fills it once
+ * (the zero padding of every activation tensor lives there) on `stream`. */
+MTLDAS_API int mtldas_plan_bind_workspace(mtldas_plan* plan, void* dev_workspace, size_t bytes, void* stream);
+/* JSON description of tensors / ops / weight packing, for tests and debugging. Returns needed size. */
+MTLDAS_API size_t mtldas_plan_describe(const mtldas_plan* plan, char* buf, size_t cap);
+
+/* weights ------------------------------------------------------------------------------------
+ * Replaces: model.load_state_dict(sd, strict=True) + model.eval()  (utils.py:122-123,249-250).
+ * `dev_state[i]` is the device pointer of state_dict entry i (fp32 tensors, int64 counters) in the
+ * reference's state_dict order.  Folds eval-mode BatchNorm (running statistics, eps 1e-5) into the
+ * packed convolution weights. Must be called again whenever the parameters change. */
+MTLDAS_API int mtldas_plan_pack_eval(mtldas_plan* plan, const void* const* dev_state, int n_entries, void* stream);
+
+/* forward ------------------------------------------------------------------------------------
+ * Replaces: out1, out2 = model(x) in eval mode  (utils.py:272; modelA_MTL.py:127-174,
+ * modelB_singleTask.py:130-178).  dev_x: fp32 [n,1,100,250] contiguous.
+ * MTL: dev_out0 = log-probs distance [n,16], dev_out1 = log-probs event [n,2].
+ * single task: dev_out0 = [n,16] or [n,2]; dev_out1 ignored (may be NULL). */
+MTLDAS_API int mtldas_plan_forward_eval(mtldas_plan* plan, const float* dev_x, int n, float* dev_out0, float* dev_out1,
+                             void* stream);
+/* Same through HOST buffers (pinned or pageable): H2D of x, forward, D2H of the log-probs, then a
+ * stream synchronise.  Replaces the `valX.cuda()` + `model(valX)` + `.cpu()` sequence of
+ * utils.py:264-277.  Uses staging space inside the bound workspace; allocates nothing. */
+MTLDAS_API int mtldas_plan_forward_eval_host(mtldas_plan* plan, const float* host_x, int n, float* host_out0,
+                                  float* host_out1, void* stream);
+/* Instrumented forward for bench.py: same work as forward_eval with a CUDA-event pair around every launch;
+ * host_ms_per_op[i] receives the device time of program op i (order of describe()'s "program") summed over
+ * the micro-batch passes. Synchronises the stream. No reference counterpart (measurement only). */
+MTLDAS_API int mtldas_plan_profile_eval(mtldas_plan* plan, const float* dev_x, int n, float* dev_out0, float* dev_out1,
+                                        void* stream, float* host_ms_per_op, int cap);
+/* number of kernels the last forward launched (for bench.py's gpu_launches) */
+MTLDAS_API int mtldas_plan_last_launch_count(const mtldas_plan* plan);
+/* Debug/test: copy an internal activation tensor of the LAST micro-batch pass out as fp32 NCHW
+ * [nb, C, H, W] (C,H,W as listed by describe). */
+MTLDAS_API int mtldas_plan_read_tensor(mtldas_plan* plan, const char* name, int nb, float* dev_out_nchw, void* stream);
+
+/* single fused convolution (unit-parity entry point) -----------------------------------------
+ * Replaces one nn.Conv2d (+ folded eval BatchNorm) + activation of the reference, e.g.
+ * modelA_MTL.py:13-18 (ResBlock.left), :23 (shortcut), :45-50 (att_generator), :37 (conv3x3).
+ * x: fp32 NCHW [n, cin, h, w]; x2 (optional, may be NULL): second source concatenated after x along
+ * channels [n, cin2, h, w] (torch.cat, modelA_MTL.py:149); weight fp32 [cout, cin+cin2, k, k];
+ * bias fp32 [cout] or NULL; aux fp32 NCHW [n, cout, ho, wo] for ADD_RELU / SIGMOID_MUL;
+ * out fp32 NCHW [n, cout, ho, wo].  ksize in {1,3}, stride in {1,2}, padding = ksize/2 for 3, 0 for 1.
+ * Allocates temporaries with cudaMalloc (test entry point, not for the hot loop). Synchronous. */
+MTLDAS_API int mtldas_conv2d_nchw(const float* dev_x, const float* dev_x2, const float* dev_weight, const float* dev_bias,
+                       const float* dev_aux, float* dev_out, int n, int cin, int cin2, int h, int w, int cout,
+                       int ksize, int stride, int epilogue, int precision, int aux_phase_split);
+
+/* tcgen05 descriptor self-test: runs one 128xNx16 UMMA on known operands under the descriptor
+ * conventions the library uses and returns the max abs error (or <0 on error). */
+MTLDAS_API float mtldas_umma_selftest(int n_cols, int row_shift, int swap_lbo_sbo);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MTLDAS_H_ */

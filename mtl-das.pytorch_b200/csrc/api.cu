@@ -1,0 +1,178 @@
+// extern "C" surface of libmtldas_b200.so (see include/mtldas.h).
+#include <cstdlib>
+#include <cstring>
+
+#include "../../include/mtldas.h"
+#include "kernels.h"
+#include "plan.h"
+
+using namespace mtldas;
+
+struct mtldas_plan {
+  Plan* p;
+};
+
+extern "C" {
+
+const char* mtldas_version(void) { return "mtldas-b200 0.1 (sm_100a)"; }
+const char* mtldas_last_error(void) { return last_error_text(); }
+
+int mtldas_device_ok(void) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return prop.major == 10 ? 1 : 0;
+}
+
+mtldas_plan* mtldas_plan_create(int model_kind, int micro_batch, int precision) {
+  if (model_kind < 0 || model_kind > 2 || micro_batch < 1 || micro_batch > 1024 || precision < 0 || precision > 1) {
+    set_error("plan_create: bad arguments (kind %d, micro_batch %d, precision %d)", model_kind, micro_batch,
+              precision);
+    return nullptr;
+  }
+  mtldas_plan* h = new mtldas_plan();
+  h->p = build_plan(model_kind, micro_batch, precision);
+  const char* sw = getenv("MTLDAS_UMMA_SWAP_DESC");
+  h->p->swap_desc = (sw && sw[0] == '1') ? 1 : 0;
+  return h;
+}
+void mtldas_plan_destroy(mtldas_plan* plan) {
+  if (!plan) return;
+  delete plan->p;
+  delete plan;
+}
+int mtldas_plan_num_state_entries(const mtldas_plan* plan) { return plan ? (int)plan->p->state_keys.size() : -1; }
+const char* mtldas_plan_state_key(const mtldas_plan* plan, int i) {
+  if (!plan || i < 0 || i >= (int)plan->p->state_keys.size()) return nullptr;
+  return plan->p->state_keys[i].c_str();
+}
+size_t mtldas_plan_workspace_bytes(const mtldas_plan* plan) { return plan ? plan->p->ws_bytes : 0; }
+
+int mtldas_plan_bind_workspace(mtldas_plan* plan, void* dev_workspace, size_t bytes, void* stream) {
+  if (!plan || !dev_workspace || bytes < plan->p->ws_bytes || ((uintptr_t)dev_workspace & 255)) {
+    set_error("bind_workspace: need %zu bytes, 256-byte aligned", plan ? plan->p->ws_bytes : (size_t)0);
+    return MTLDAS_ERR_ARG;
+  }
+  cudaError_t e = cudaMemsetAsync(dev_workspace, 0, plan->p->ws_bytes, (cudaStream_t)stream);
+  if (e != cudaSuccess) {
+    set_error("bind_workspace: %s", cudaGetErrorString(e));
+    return MTLDAS_ERR_CUDA;
+  }
+  plan->p->ws = (char*)dev_workspace;
+  plan->p->packed = false;
+  return 0;
+}
+
+size_t mtldas_plan_describe(const mtldas_plan* plan, char* buf, size_t cap) {
+  if (!plan) return 0;
+  std::string s = plan->p->describe();
+  if (buf && cap) {
+    size_t n = s.size() < cap - 1 ? s.size() : cap - 1;
+    memcpy(buf, s.data(), n);
+    buf[n] = 0;
+  }
+  return s.size() + 1;
+}
+
+int mtldas_plan_pack_eval(mtldas_plan* plan, const void* const* dev_state, int n_entries, void* stream) {
+  if (!plan || !dev_state || n_entries != (int)plan->p->state_keys.size()) {
+    set_error("pack_eval: expected %d state entries", plan ? (int)plan->p->state_keys.size() : -1);
+    return MTLDAS_ERR_ARG;
+  }
+  for (int i = 0; i < n_entries; ++i)
+    if (!dev_state[i]) {
+      set_error("pack_eval: state entry %d (%s) is NULL", i, plan->p->state_keys[i].c_str());
+      return MTLDAS_ERR_ARG;
+    }
+  return plan_pack_eval(*plan->p, dev_state, (cudaStream_t)stream);
+}
+
+int mtldas_plan_forward_eval(mtldas_plan* plan, const float* dev_x, int n, float* dev_out0, float* dev_out1,
+                             void* stream) {
+  if (!plan || !dev_x || !dev_out0 || n < 0) {
+    set_error("forward_eval: bad arguments");
+    return MTLDAS_ERR_ARG;
+  }
+  if (n == 0) return 0;
+  return plan_forward_eval(*plan->p, dev_x, n, dev_out0, dev_out1, (cudaStream_t)stream);
+}
+
+int mtldas_plan_forward_eval_host(mtldas_plan* plan, const float* host_x, int n, float* host_out0, float* host_out1,
+                                  void* stream) {
+  if (!plan || !host_x || !host_out0 || n < 0) {
+    set_error("forward_eval_host: bad arguments");
+    return MTLDAS_ERR_ARG;
+  }
+  Plan& p = *plan->p;
+  if (!p.ws || !p.packed) {
+    set_error("forward_eval_host: bind a workspace and pack weights first");
+    return MTLDAS_ERR_STATE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const int c0 = p.heads[0].classes, c1 = p.heads.size() > 1 ? p.heads[1].classes : 0;
+  float* xs = reinterpret_cast<float*>(p.ws + p.x_stage_off);
+  float* o0 = reinterpret_cast<float*>(p.ws + p.out_stage_off);
+  float* o1 = o0 + (size_t)p.mb * 16;
+  int launches = 0;
+  for (int s = 0; s < n; s += p.mb) {
+    const int nb = n - s < p.mb ? n - s : p.mb;
+    cudaError_t e = cudaMemcpyAsync(xs, host_x + (size_t)s * kPatchH * kPatchW, (size_t)nb * kPatchH * kPatchW * 4,
+                                    cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) {
+      int rc = plan_forward_eval(p, xs, nb, o0, c1 ? o1 : nullptr, st);
+      if (rc) return rc;
+      launches += p.last_launches;
+      e = cudaMemcpyAsync(host_out0 + (size_t)s * c0, o0, (size_t)nb * c0 * 4, cudaMemcpyDeviceToHost, st);
+    }
+    if (e == cudaSuccess && c1 && host_out1)
+      e = cudaMemcpyAsync(host_out1 + (size_t)s * c1, o1, (size_t)nb * c1 * 4, cudaMemcpyDeviceToHost, st);
+    if (e != cudaSuccess) {
+      set_error("forward_eval_host: %s", cudaGetErrorString(e));
+      return MTLDAS_ERR_CUDA;
+    }
+  }
+  p.last_launches = launches;
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) {
+    set_error("forward_eval_host: %s", cudaGetErrorString(e));
+    return MTLDAS_ERR_CUDA;
+  }
+  return 0;
+}
+
+int mtldas_plan_profile_eval(mtldas_plan* plan, const float* dev_x, int n, float* dev_out0, float* dev_out1,
+                             void* stream, float* host_ms_per_op, int cap) {
+  if (!plan || !dev_x || !dev_out0 || !host_ms_per_op || n < 1) {
+    set_error("profile_eval: bad arguments");
+    return MTLDAS_ERR_ARG;
+  }
+  return plan_profile_eval(*plan->p, dev_x, n, dev_out0, dev_out1, (cudaStream_t)stream, host_ms_per_op, cap);
+}
+
+int mtldas_plan_last_launch_count(const mtldas_plan* plan) { return plan ? plan->p->last_launches : -1; }
+
+int mtldas_plan_read_tensor(mtldas_plan* plan, const char* name, int nb, float* dev_out_nchw, void* stream) {
+  if (!plan || !name || !dev_out_nchw) return MTLDAS_ERR_ARG;
+  return plan_read_tensor(*plan->p, name, nb, dev_out_nchw, (cudaStream_t)stream);
+}
+
+int mtldas_conv2d_nchw(const float* dev_x, const float* dev_x2, const float* dev_weight, const float* dev_bias,
+                       const float* dev_aux, float* dev_out, int n, int cin, int cin2, int h, int w, int cout,
+                       int ksize, int stride, int epilogue, int precision, int aux_phase_split) {
+  const char* sw = getenv("MTLDAS_UMMA_SWAP_DESC");
+  return single_conv(dev_x, dev_x2, dev_weight, dev_bias, dev_aux, dev_out, n, cin, cin2, h, w, cout, ksize, stride,
+                     epilogue, precision, aux_phase_split, (sw && sw[0] == '1') ? 1 : 0);
+}
+
+float mtldas_umma_selftest(int n_cols, int row_shift, int swap_lbo_sbo) {
+  return umma_selftest(n_cols, row_shift, swap_lbo_sbo);
+}
+
+}  // extern "C"

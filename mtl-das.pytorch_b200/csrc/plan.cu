@@ -1,0 +1,730 @@
+// Builds the layer program of MTL_Net (modelA_MTL.py:59-174) / Single_Task_Net
+// (modelB_singleTask.py:58-178) over the P8 layouts and runs it.
+#include "plan.h"
+
+#include <algorithm>
+#include <climits>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <sstream>
+
+#include "kernels.h"
+
+namespace mtldas {
+
+static thread_local char g_err[512] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+const char* last_error_text() { return g_err; }
+
+static inline long long round_up(long long v, long long a) { return (v + a - 1) / a * a; }
+
+// ---------------------------------------------------------------------------------------------
+// layer table in state_dict registration order (modelA_MTL.py:73-113)
+// ---------------------------------------------------------------------------------------------
+static void add_layer(Plan& p, const std::string& conv, const std::string& bn, int cin, int cout, int k, int s,
+                      int pad, bool bias) {
+  LayerSpec L;
+  L.conv = conv, L.bn = bn, L.cin = cin, L.cout = cout, L.ksize = k, L.stride = s, L.pad = pad, L.bias = bias;
+  auto push = [&](const std::string& key) {
+    p.state_keys.push_back(key);
+    return (int)p.state_keys.size() - 1;
+  };
+  L.i_w = push(conv + ".weight");
+  L.i_b = bias ? push(conv + ".bias") : -1;
+  L.i_gamma = push(bn + ".weight");
+  L.i_beta = push(bn + ".bias");
+  L.i_rm = push(bn + ".running_mean");
+  L.i_rv = push(bn + ".running_var");
+  L.i_nbt = push(bn + ".num_batches_tracked");
+  p.layers.push_back(L);
+}
+
+static int layer_index(const Plan& p, const std::string& conv) {
+  for (size_t i = 0; i < p.layers.size(); ++i)
+    if (p.layers[i].conv == conv) return (int)i;
+  return -1;
+}
+
+static const int kResCfg[8][3] = {{16, 16, 1}, {16, 16, 1}, {16, 32, 2}, {32, 32, 1},
+                                  {32, 64, 2}, {64, 64, 1}, {64, 128, 2}, {128, 128, 1}};
+static const char* kAttNames[4] = {"att_mask_generator1", "att_mask_generato2", "att_mask_generator3",
+                                   "att_mask_generator4"};  // typo is part of the contract (modelA_MTL.py:93)
+static const int kAttCfg[4][3] = {{16, 8, 16}, {64, 16, 32}, {128, 32, 64}, {256, 64, 128}};
+static const int kOutCfg[3][2] = {{16, 32}, {32, 64}, {64, 128}};
+
+static void build_layers(Plan& p) {
+  add_layer(p, "conv1.0", "conv1.1", 1, 16, 7, 3, 2, false);
+  for (int i = 0; i < 8; ++i) {
+    std::string rb = "resblock" + std::to_string(i + 1);
+    int ci = kResCfg[i][0], co = kResCfg[i][1], s = kResCfg[i][2];
+    add_layer(p, rb + ".left.0", rb + ".left.1", ci, co, 3, s, 1, false);
+    add_layer(p, rb + ".left.3", rb + ".left.4", co, co, 3, 1, 1, false);
+    if (s != 1 || ci != co) add_layer(p, rb + ".shortcut.0", rb + ".shortcut.1", ci, co, 1, s, 0, false);
+  }
+  for (int l = 0; l < 4; ++l)
+    for (int t = 0; t < p.ntasks; ++t) {
+      std::string a = std::string(kAttNames[l]) + "." + std::to_string(t);
+      add_layer(p, a + ".0", a + ".1", kAttCfg[l][0], kAttCfg[l][1], 1, 1, 0, true);
+      add_layer(p, a + ".3", a + ".4", kAttCfg[l][1], kAttCfg[l][2], 3, 1, 1, true);
+    }
+  for (int l = 0; l < 3; ++l)
+    for (int t = 0; t < p.ntasks; ++t) {
+      std::string o = "output_layer" + std::to_string(l + 1) + "." + std::to_string(t);
+      add_layer(p, o + ".0", o + ".1", kOutCfg[l][0], kOutCfg[l][1], 3, 1, 1, false);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// tensors
+// ---------------------------------------------------------------------------------------------
+static int add_tensor(Plan& p, const std::string& name, int C, int H, int W, int layout) {
+  TensorInfo t;
+  t.name = name, t.C = C, t.H = H, t.W = W, t.layout = layout;
+  t.Hs = layout == LAY_P8 ? H : (H + 1) / 2;
+  t.Ws = layout == LAY_P8 ? W : (W + 1) / 2;
+  t.Wp = t.Ws + 1;
+  t.Pimg = (t.Hs + 1) * t.Wp;
+  t.g_lo = (int)round_up(t.Wp + 1, 8);
+  t.plane = round_up((long long)t.g_lo + (long long)p.mb * t.Pimg + kMaxTile + t.Wp + 1, 8);
+  t.nchunks = C / 8;
+  t.nphase = layout == LAY_P8 ? 1 : 4;
+  t.bytes = (size_t)t.nphase * t.nchunks * t.plane * p.gran;
+  t.offset = 0;
+  p.tensors.push_back(t);
+  return (int)p.tensors.size() - 1;
+}
+
+int Plan::find_tensor(const std::string& n) const {
+  for (size_t i = 0; i < tensors.size(); ++i)
+    if (tensors[i].name == n) return (int)i;
+  return -1;
+}
+
+ActView Plan::view(int tensor, int chunk0) const {
+  const TensorInfo& t = tensors[tensor];
+  ActView v;
+  v.base = ws + t.offset + (size_t)chunk0 * t.plane * gran;
+  v.plane = t.plane;
+  v.phase_stride = t.layout == LAY_P8 ? 0 : (long long)t.nchunks * t.plane;
+  v.g_lo = t.g_lo;
+  v.layout = t.layout;
+  v.Wp2 = t.Wp;
+  v.Pimg2 = t.Pimg;
+  return v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// conv op construction
+// ---------------------------------------------------------------------------------------------
+void choose_tiling(ConvOpHost& op) {
+  op.tap_bytes = op.nchunks * 8 * op.Cout * 2;
+  const int total_w = op.ntaps * op.tap_bytes;
+  int MT = 4;
+  size_t slab = 0;
+  for (;; MT >>= 1) {
+    int SP = MT * kTileM + op.halo_lo + op.halo_hi;
+    slab = (size_t)op.nsrc * op.nchunks * SP * 16;
+    if (MT == 1) break;
+    if (MT * op.Cout <= 256 && slab <= 80 * 1024) break;
+  }
+  op.MT = MT;
+  if (slab + total_w <= 96 * 1024) {
+    op.tps = op.ntaps;
+    op.NS = 1;
+  } else {
+    op.tps = 1;
+    long long room = 110 * 1024 - (long long)slab;
+    int ns = (int)(room / op.tap_bytes);
+    if (ns < 3) ns = (int)((220 * 1024 - (long long)slab) / op.tap_bytes);
+    op.NS = std::max(1, std::min(std::min(ns, op.ntaps), kMaxRing));
+  }
+  op.nstages = (op.ntaps + op.tps - 1) / op.tps;
+  int cols = 32;
+  while (cols < MT * op.Cout) cols <<= 1;
+  op.tmem_cols = cols;
+}
+
+namespace {
+struct Builder {
+  Plan& p;
+  explicit Builder(Plan& pl) : p(pl) {}
+
+  ConvOpHost base(const std::string& name, int H, int W, int Cout, int nchunks, int epi, int ngroups) {
+    ConvOpHost op{};
+    op.name = name, op.H = H, op.W = W, op.Cout = Cout, op.nchunks = nchunks, op.epi = epi, op.ngroups = ngroups;
+    for (auto& g : op.g) {
+      g.aux_tensor = -1, g.aux_chunk0 = 0, g.aux_nchunks = Cout / 8;
+      g.out_tensor = -1, g.out_chunk0 = 0;
+      for (auto& s : g.src) s = SrcRef{-1, 0, -1};
+    }
+    return op;
+  }
+  // 3x3 stride 1 pad 1 over one P8 source
+  void taps_3x3_s1(ConvOpHost& op) {
+    int Wp = op.W + 1;
+    op.nsrc = 1, op.ntaps = 9;
+    for (int r = 0; r < 3; ++r)
+      for (int s = 0; s < 3; ++s) op.tap[r * 3 + s] = ConvTapDev{0, (r - 1) * Wp + (s - 1)};
+    op.halo_lo = Wp + 1, op.halo_hi = Wp + 1;
+  }
+  // 3x3 stride 2 pad 1 over the four phase planes of a P8S2 source: input row 2i-1+r
+  //   r=0 -> odd rows, index i-1 ; r=1 -> even rows, index i ; r=2 -> odd rows, index i
+  void taps_3x3_s2(ConvOpHost& op) {
+    int Wp = op.W + 1;
+    op.nsrc = 4, op.ntaps = 9;
+    for (int r = 0; r < 3; ++r)
+      for (int s = 0; s < 3; ++s) {
+        int ph = (r == 1) ? 0 : 1, pw = (s == 1) ? 0 : 1;
+        int dh = (r == 0) ? -1 : 0, dw = (s == 0) ? -1 : 0;
+        op.tap[r * 3 + s] = ConvTapDev{ph * 2 + pw, dh * Wp + dw};
+      }
+    op.halo_lo = Wp + 1, op.halo_hi = 0;
+  }
+  void taps_1x1(ConvOpHost& op, int nsrc) {
+    op.nsrc = nsrc, op.ntaps = nsrc;
+    for (int s = 0; s < nsrc; ++s) op.tap[s] = ConvTapDev{s, 0};
+    op.halo_lo = op.halo_hi = 0;
+  }
+  void finish(ConvOpHost& op) {
+    choose_tiling(op);
+    p.convs.push_back(op);
+    p.program.push_back(Op{1, (int)p.convs.size() - 1});
+  }
+  PackSegHost seg(const std::string& conv, int split = INT_MAX, int k_off = 0, int cout_off = 0) {
+    int li = layer_index(p, conv);
+    return PackSegHost{li, split, k_off, cout_off};
+  }
+};
+}  // namespace
+
+Plan* build_plan(int kind, int mb, int precision) {
+  Plan* pp = new Plan();
+  Plan& p = *pp;
+  p.kind = kind, p.mb = mb, p.precision = precision;
+  p.ntasks = kind == 0 ? 2 : 1;
+  p.gran = precision == 0 ? 16 : 32;
+  build_layers(p);
+  Builder b(p);
+  const int T = p.ntasks;
+  const int H[4] = {33, 17, 9, 5}, W[4] = {83, 42, 21, 11}, C[4] = {16, 32, 64, 128};
+
+  // ---- shared trunk ---------------------------------------------------------------------------
+  p.stem_layer = 0;
+  int stem = add_tensor(p, "stem", 16, H[0], W[0], LAY_P8);
+  p.stem_out = stem;
+  p.program.push_back(Op{0, 0});
+  int sb[8];
+  int prev = stem;
+  for (int i = 0; i < 8; ++i) {
+    const int st = i / 2;  // stage of the block output
+    const std::string rb = "resblock" + std::to_string(i + 1);
+    const bool down = kResCfg[i][2] == 2;
+    const bool next_down = (i + 1 < 8) && kResCfg[i + 1][2] == 2;  // output feeds stride-2 convs -> phase split
+    int mid = add_tensor(p, rb + ".mid", C[st], H[st], W[st], LAY_P8);
+    int sc = -1;
+    {
+      ConvOpHost op = b.base(rb + ".left.0", H[st], W[st], C[st], p.tensors[prev].nchunks, EPI_RELU, 1);
+      if (down) {
+        b.taps_3x3_s2(op);
+        for (int ph = 0; ph < 4; ++ph) op.g[0].src[ph] = SrcRef{prev, 0, ph};
+      } else {
+        b.taps_3x3_s1(op);
+        op.g[0].src[0] = SrcRef{prev, 0, -1};
+      }
+      op.g[0].out_tensor = mid;
+      op.g[0].segs.push_back(b.seg(rb + ".left.0"));
+      b.finish(op);
+    }
+    if (down) {
+      sc = add_tensor(p, rb + ".sc", C[st], H[st], W[st], LAY_P8);
+      ConvOpHost op = b.base(rb + ".shortcut.0", H[st], W[st], C[st], p.tensors[prev].nchunks, EPI_NONE, 1);
+      b.taps_1x1(op, 1);
+      op.g[0].src[0] = SrcRef{prev, 0, 0};  // 1x1 stride 2 reads x[2i,2j] = the (even,even) phase plane
+      op.g[0].out_tensor = sc;
+      op.g[0].segs.push_back(b.seg(rb + ".shortcut.0"));
+      b.finish(op);
+    }
+    sb[i] = add_tensor(p, "sb" + std::to_string(i), C[st], H[st], W[st], next_down ? LAY_P8S2 : LAY_P8);
+    {
+      ConvOpHost op = b.base(rb + ".left.3", H[st], W[st], C[st], C[st] / 8, EPI_ADD_RELU, 1);
+      b.taps_3x3_s1(op);
+      op.g[0].src[0] = SrcRef{mid, 0, -1};
+      op.g[0].out_tensor = sb[i];
+      op.g[0].aux_tensor = down ? sc : prev;
+      op.g[0].segs.push_back(b.seg(rb + ".left.3"));
+      b.finish(op);
+    }
+    prev = sb[i];
+  }
+
+  // ---- task-specific sub-networks (modelA_MTL.py:142-163) --------------------------------------
+  int a_prev = -1;  // pooled task feature of the previous level, channels = C[l] * T (task t at chunk C[l]/8*t)
+  for (int l = 0; l < 4; ++l) {
+    const std::string an = kAttNames[l];
+    const int cm = kAttCfg[l][1], co = kAttCfg[l][2];
+    const int cm_p = std::max(cm, 16);  // level 1 has 8 mid channels per task: padded / merged to 16
+    int tmid, amask;
+    if (l == 0) {
+      // both tasks read the same sb0: one 1x1 conv with the tasks' filters stacked along Cout (8+8),
+      // then one 3x3 conv with block-diagonal weights producing [mask_0 | mask_1].
+      tmid = add_tensor(p, "att1.mid", 16, H[0], W[0], LAY_P8);
+      amask = add_tensor(p, "a1", co * T, H[0], W[0], LAY_P8);
+      ConvOpHost op = b.base(an + ".0", H[0], W[0], 16, 2, EPI_RELU, 1);
+      b.taps_1x1(op, 1);
+      op.g[0].src[0] = SrcRef{sb[0], 0, -1};
+      op.g[0].out_tensor = tmid;
+      for (int t = 0; t < T; ++t) op.g[0].segs.push_back(b.seg(an + "." + std::to_string(t) + ".0", INT_MAX, 0, 8 * t));
+      b.finish(op);
+      ConvOpHost op2 = b.base(an + ".3", H[0], W[0], co * T, 2, EPI_SIGMOID_MUL, 1);
+      b.taps_3x3_s1(op2);
+      op2.g[0].src[0] = SrcRef{tmid, 0, -1};
+      op2.g[0].out_tensor = amask;
+      op2.g[0].aux_tensor = sb[1];
+      op2.g[0].aux_nchunks = co / 8;  // both tasks multiply the same 16-channel sb1
+      for (int t = 0; t < T; ++t)
+        op2.g[0].segs.push_back(b.seg(an + "." + std::to_string(t) + ".3", INT_MAX, 8 * t, co * t));
+      b.finish(op2);
+    } else {
+      tmid = add_tensor(p, "att" + std::to_string(l + 1) + ".mid", cm_p * T, H[l], W[l], LAY_P8);
+      amask = add_tensor(p, "a" + std::to_string(l + 1), co * T, H[l], W[l], LAY_P8);
+      ConvOpHost op = b.base(an + ".0", H[l], W[l], cm_p, C[l] / 8, EPI_RELU, T);
+      b.taps_1x1(op, 2);  // torch.cat((shared, task), dim=1): shared channels first
+      for (int t = 0; t < T; ++t) {
+        op.g[t].src[0] = SrcRef{sb[2 * l], 0, -1};
+        op.g[t].src[1] = SrcRef{a_prev, (C[l] / 8) * t, -1};
+        op.g[t].out_tensor = tmid, op.g[t].out_chunk0 = (cm_p / 8) * t;
+        op.g[t].segs.push_back(b.seg(an + "." + std::to_string(t) + ".0", C[l], 0, 0));
+      }
+      b.finish(op);
+      ConvOpHost op2 = b.base(an + ".3", H[l], W[l], co, cm_p / 8, EPI_SIGMOID_MUL, T);
+      b.taps_3x3_s1(op2);
+      for (int t = 0; t < T; ++t) {
+        op2.g[t].src[0] = SrcRef{tmid, (cm_p / 8) * t, -1};
+        op2.g[t].out_tensor = amask, op2.g[t].out_chunk0 = (co / 8) * t;
+        op2.g[t].aux_tensor = sb[2 * l + 1];
+        op2.g[t].segs.push_back(b.seg(an + "." + std::to_string(t) + ".3"));
+      }
+      b.finish(op2);
+    }
+    if (l == 3) {
+      for (int t = 0; t < T; ++t) {
+        int classes = (p.kind == 2 || (p.kind == 0 && t == 1)) ? 2 : 16;
+        p.heads.push_back(HeadOpHost{amask, (co / 8) * t, classes, t});
+        p.program.push_back(Op{3, (int)p.heads.size() - 1});
+      }
+      break;
+    }
+    // output layer l+1 and down-sampling
+    const int oc = kOutCfg[l][1];
+    int o = add_tensor(p, "o" + std::to_string(l + 1), oc * T, H[l], W[l], LAY_P8);
+    int pooled = add_tensor(p, "p" + std::to_string(l + 1), oc * T, H[l + 1], W[l + 1], LAY_P8);
+    ConvOpHost op3 = b.base("output_layer" + std::to_string(l + 1), H[l], W[l], oc, co / 8, EPI_RELU, T);
+    b.taps_3x3_s1(op3);
+    for (int t = 0; t < T; ++t) {
+      op3.g[t].src[0] = SrcRef{amask, (co / 8) * t, -1};
+      op3.g[t].out_tensor = o, op3.g[t].out_chunk0 = (oc / 8) * t;
+      op3.g[t].segs.push_back(b.seg("output_layer" + std::to_string(l + 1) + "." + std::to_string(t) + ".0"));
+    }
+    b.finish(op3);
+    p.pools.push_back(PoolOpHost{"pool" + std::to_string(l + 1), o, pooled});
+    p.program.push_back(Op{2, (int)p.pools.size() - 1});
+    a_prev = pooled;
+  }
+
+  // ---- workspace map ---------------------------------------------------------------------------
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    size_t o = off;
+    off = (size_t)round_up((long long)(off + bytes), 256);
+    return o;
+  };
+  for (auto& t : p.tensors) t.offset = take(t.bytes);
+  for (auto& c : p.convs)
+    for (int gi = 0; gi < c.ngroups; ++gi) {
+      size_t wbytes = (size_t)c.ntaps * c.nchunks * 8 * c.Cout * (precision == 0 ? 2 : 4);
+      c.g[gi].w_off = take(wbytes);
+      c.g[gi].bias_off = take((size_t)c.Cout * 4);
+    }
+  p.stem_w_off = take(49 * 16 * 4);
+  p.stem_b_off = take(16 * 4);
+  p.x_stage_off = take((size_t)mb * kPatchH * kPatchW * 4);
+  p.out_stage_off = take((size_t)mb * 18 * 4);
+  p.ws_bytes = off;
+  return pp;
+}
+
+// ---------------------------------------------------------------------------------------------
+// device parameter blocks
+// ---------------------------------------------------------------------------------------------
+ConvParams Plan::conv_params(const ConvOpHost& op, int nb) const {
+  ConvParams q{};
+  q.H = op.H, q.W = op.W, q.Wp = op.W + 1, q.Pimg = (op.H + 1) * (op.W + 1);
+  q.body = (long long)nb * q.Pimg;
+  q.Cout = op.Cout, q.nchunks = op.nchunks, q.nsrc = op.nsrc, q.ntaps = op.ntaps;
+  q.halo_lo = op.halo_lo, q.halo_hi = op.halo_hi;
+  q.MT = op.MT, q.SP = op.MT * kTileM + op.halo_lo + op.halo_hi;
+  q.tps = op.tps, q.NS = op.NS, q.nstages = op.nstages, q.tap_bytes = op.tap_bytes, q.tmem_cols = op.tmem_cols;
+  q.epi = op.epi, q.swap_desc = swap_desc, q.ngroups = op.ngroups;
+  for (int t = 0; t < op.ntaps; ++t) q.tap[t] = op.tap[t];
+  for (int gi = 0; gi < op.ngroups; ++gi) {
+    const ConvGroupHost& g = op.g[gi];
+    ConvGroupDev& d = q.g[gi];
+    for (int s = 0; s < op.nsrc; ++s) {
+      const TensorInfo& t = tensors[g.src[s].tensor];
+      long long pos = (long long)g.src[s].chunk0 * t.plane + t.g_lo;
+      if (g.src[s].phase >= 0) pos += (long long)g.src[s].phase * t.nchunks * t.plane;
+      d.src[s].base = ws + t.offset + (size_t)pos * gran;
+      d.src[s].plane_bytes = t.plane * gran;
+    }
+    d.w = ws + g.w_off;
+    d.bias = reinterpret_cast<const float*>(ws + g.bias_off);
+    d.out = view(g.out_tensor, g.out_chunk0);
+    if (g.aux_tensor >= 0) d.aux = view(g.aux_tensor, g.aux_chunk0);
+    d.aux_nchunks = g.aux_nchunks;
+  }
+  return q;
+}
+
+// ---------------------------------------------------------------------------------------------
+// weight packing (eval)
+// ---------------------------------------------------------------------------------------------
+#define CK(call)                                                                      \
+  do {                                                                                \
+    cudaError_t e_ = (call);                                                          \
+    if (e_ != cudaSuccess) {                                                          \
+      set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+      return -2;                                                                      \
+    }                                                                                 \
+  } while (0)
+
+static PackSeg make_seg(const Plan& p, const PackSegHost& h, const void* const* state) {
+  const LayerSpec& L = p.layers[h.layer];
+  PackSeg s{};
+  s.w = (const float*)state[L.i_w];
+  s.conv_bias = L.i_b >= 0 ? (const float*)state[L.i_b] : nullptr;
+  s.gamma = (const float*)state[L.i_gamma];
+  s.beta = (const float*)state[L.i_beta];
+  s.rmean = (const float*)state[L.i_rm];
+  s.rvar = (const float*)state[L.i_rv];
+  s.cout = L.cout, s.cin = L.cin, s.ksize = L.ksize;
+  s.split = h.split, s.k_off = h.k_off, s.cout_off = h.cout_off;
+  return s;
+}
+
+int plan_pack_eval(Plan& p, const void* const* state, cudaStream_t stream) {
+  if (!p.ws) {
+    set_error("pack_eval: no workspace bound");
+    return -3;
+  }
+  for (auto& c : p.convs)
+    for (int gi = 0; gi < c.ngroups; ++gi) {
+      size_t wbytes = (size_t)c.ntaps * c.nchunks * 8 * c.Cout * (p.precision == 0 ? 2 : 4);
+      CK(cudaMemsetAsync(p.ws + c.g[gi].w_off, 0, wbytes, stream));
+      CK(cudaMemsetAsync(p.ws + c.g[gi].bias_off, 0, (size_t)c.Cout * 4, stream));
+      for (auto& sh : c.g[gi].segs) {
+        PackParams q{};
+        q.seg = make_seg(p, sh, state);
+        q.dst = p.ws + c.g[gi].w_off;
+        q.bias_dst = reinterpret_cast<float*>(p.ws + c.g[gi].bias_off);
+        q.Cout_p = c.Cout, q.K_tap = c.nchunks * 8;
+        q.fp32 = p.precision == 0 ? 0 : 1;
+        q.fold = 1, q.eps = 1e-5f;
+        CK(launch_pack(q, stream));
+      }
+    }
+  {
+    PackParams q{};
+    q.seg = make_seg(p, PackSegHost{p.stem_layer, INT_MAX, 0, 0}, state);
+    q.dst = p.ws + p.stem_w_off;
+    q.bias_dst = reinterpret_cast<float*>(p.ws + p.stem_b_off);
+    q.Cout_p = 16, q.K_tap = 1, q.fp32 = 1, q.fold = 1, q.eps = 1e-5f;
+    CK(launch_pack(q, stream));
+  }
+  p.packed = true;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// forward (eval)
+// ---------------------------------------------------------------------------------------------
+static int run_pass(Plan& p, const float* x, int nb, float* out0, float* out1, cudaStream_t stream,
+                    std::vector<cudaEvent_t>* evs = nullptr) {
+  for (const Op& op : p.program) {
+    if (evs) {
+      cudaEvent_t e;
+      CK(cudaEventCreate(&e));
+      CK(cudaEventRecord(e, stream));
+      evs->push_back(e);
+    }
+    if (op.kind == 0) {
+      const TensorInfo& t = p.tensors[p.stem_out];
+      StemParams q{};
+      q.x = x;
+      q.w = reinterpret_cast<const float*>(p.ws + p.stem_w_off);
+      q.bias = reinterpret_cast<const float*>(p.ws + p.stem_b_off);
+      q.out = p.view(p.stem_out, 0);
+      q.Hin = kPatchH, q.Win = kPatchW, q.H = t.H, q.W = t.W, q.Wp = t.Wp, q.Pimg = t.Pimg;
+      q.body = (long long)nb * t.Pimg;
+      CK(launch_stem(q, p.precision, stream));
+    } else if (op.kind == 1) {
+      ConvParams q = p.conv_params(p.convs[op.index], nb);
+      CK(launch_conv(q, p.precision, stream));
+    } else if (op.kind == 2) {
+      const PoolOpHost& po = p.pools[op.index];
+      const TensorInfo& ti = p.tensors[po.in_tensor];
+      const TensorInfo& to = p.tensors[po.out_tensor];
+      PoolParams q{};
+      q.in = p.view(po.in_tensor, 0), q.out = p.view(po.out_tensor, 0);
+      q.nchunks = ti.nchunks;
+      q.H = ti.H, q.W = ti.W, q.Wp = ti.Wp, q.Pimg = ti.Pimg;
+      q.Ho = to.H, q.Wo = to.W, q.Wpo = to.Wp, q.Pimgo = to.Pimg;
+      q.body_o = (long long)nb * to.Pimg;
+      CK(launch_pool(q, p.precision, stream));
+    } else {
+      const HeadOpHost& h = p.heads[op.index];
+      const TensorInfo& t = p.tensors[h.in_tensor];
+      HeadParams q{};
+      q.in = p.view(h.in_tensor, h.chunk0);
+      q.out = h.out_index == 0 ? out0 : out1;
+      q.nb = nb, q.classes = h.classes, q.npos = t.Pimg;
+      q.inv_count = 1.f / (float)(t.H * t.W * (128 / h.classes));
+      if (!q.out) {
+        set_error("forward: output %d is NULL", h.out_index);
+        return -1;
+      }
+      CK(launch_head(q, p.precision, stream));
+    }
+    ++p.last_launches;
+    if (evs) {
+      cudaEvent_t e;
+      CK(cudaEventCreate(&e));
+      CK(cudaEventRecord(e, stream));
+      evs->push_back(e);
+    }
+  }
+  return 0;
+}
+
+// One forward with a CUDA-event pair around every launch: ms_per_op[i] = device time of program op i summed
+// over the micro-batch passes (bench.py's live per-kernel durations for the roofline).
+int plan_profile_eval(Plan& p, const float* x, int n, float* out0, float* out1, cudaStream_t stream,
+                      float* ms_per_op, int cap) {
+  if (!p.ws || !p.packed) {
+    set_error("profile_eval: bind a workspace and pack weights first");
+    return -3;
+  }
+  const int nops = (int)p.program.size();
+  if (cap < nops) {
+    set_error("profile_eval: need room for %d ops", nops);
+    return -1;
+  }
+  for (int i = 0; i < nops; ++i) ms_per_op[i] = 0.f;
+  std::vector<cudaEvent_t> evs;
+  int c0 = p.heads[0].classes, c1 = p.heads.size() > 1 ? p.heads[1].classes : 0;
+  p.last_launches = 0;
+  int rc = 0;
+  for (int s = 0; s < n && !rc; s += p.mb) {
+    int nb = std::min(p.mb, n - s);
+    rc = run_pass(p, x + (size_t)s * kPatchH * kPatchW, nb, out0 + (size_t)s * c0,
+                  out1 ? out1 + (size_t)s * c1 : nullptr, stream, &evs);
+  }
+  if (!rc && cudaStreamSynchronize(stream) != cudaSuccess) rc = -2;
+  if (!rc)
+    for (size_t i = 0; i + 1 < evs.size(); i += 2) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, evs[i], evs[i + 1]);
+      ms_per_op[(i / 2) % nops] += ms;
+    }
+  for (cudaEvent_t e : evs) cudaEventDestroy(e);
+  return rc;
+}
+
+int plan_forward_eval(Plan& p, const float* x, int n, float* out0, float* out1, cudaStream_t stream) {
+  if (!p.ws || !p.packed) {
+    set_error("forward_eval: bind a workspace and pack weights first");
+    return -3;
+  }
+  p.last_launches = 0;
+  int c0 = p.heads[0].classes, c1 = p.heads.size() > 1 ? p.heads[1].classes : 0;
+  for (int s = 0; s < n; s += p.mb) {
+    int nb = std::min(p.mb, n - s);
+    int rc = run_pass(p, x + (size_t)s * kPatchH * kPatchW, nb, out0 + (size_t)s * c0,
+                      out1 ? out1 + (size_t)s * c1 : nullptr, stream);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// debug read-back and the single-convolution entry point (unit parity tests)
+// ---------------------------------------------------------------------------------------------
+int plan_read_tensor(Plan& p, const char* name, int nb, float* out_nchw, cudaStream_t stream) {
+  int ti = p.find_tensor(name);
+  if (ti < 0 || !p.ws) {
+    set_error("read_tensor: unknown tensor '%s' or no workspace", name);
+    return -1;
+  }
+  const TensorInfo& t = p.tensors[ti];
+  CK(launch_view_to_nchw(p.view(ti, 0), out_nchw, nb, t.C, t.H, t.W, p.precision, stream));
+  return 0;
+}
+
+int single_conv(const float* x, const float* x2, const float* weight, const float* bias, const float* aux,
+                float* out, int n, int cin, int cin2, int h, int w, int cout, int ksize, int stride, int epi,
+                int precision, int aux_phase_split, int swap_desc) {
+  if (n < 1 || (cin % 16) || (cin2 % 16) || (cout % 16) || cout > 256 || cin < 16 || (ksize != 1 && ksize != 3) ||
+      (stride != 1 && stride != 2) || (x2 && !(ksize == 1 && stride == 1 && cin2 == cin)) || (!x2 && cin2) ||
+      ((epi == EPI_ADD_RELU || epi == EPI_SIGMOID_MUL) && !aux)) {
+    set_error("conv2d_nchw: unsupported arguments");
+    return -1;
+  }
+  Plan p;
+  p.kind = -1, p.mb = n, p.precision = precision, p.ntasks = 1, p.gran = precision == 0 ? 16 : 32;
+  p.swap_desc = swap_desc;
+  Builder b(p);
+  const int Ho = stride == 1 ? h : (h + 1) / 2, Wo = stride == 1 ? w : (w + 1) / 2;
+  int tin = add_tensor(p, "x", cin, h, w, stride == 2 ? LAY_P8S2 : LAY_P8);
+  int tin2 = x2 ? add_tensor(p, "x2", cin2, h, w, LAY_P8) : -1;
+  int tout = add_tensor(p, "y", cout, Ho, Wo, LAY_P8);
+  int taux = aux ? add_tensor(p, "aux", cout, Ho, Wo, aux_phase_split ? LAY_P8S2 : LAY_P8) : -1;
+  ConvOpHost op = b.base("conv", Ho, Wo, cout, cin / 8, epi, 1);
+  if (ksize == 3 && stride == 1) {
+    b.taps_3x3_s1(op);
+    op.g[0].src[0] = SrcRef{tin, 0, -1};
+  } else if (ksize == 3) {
+    b.taps_3x3_s2(op);
+    for (int ph = 0; ph < 4; ++ph) op.g[0].src[ph] = SrcRef{tin, 0, ph};
+  } else if (stride == 2) {
+    b.taps_1x1(op, 1);
+    op.g[0].src[0] = SrcRef{tin, 0, 0};
+  } else {
+    b.taps_1x1(op, x2 ? 2 : 1);
+    op.g[0].src[0] = SrcRef{tin, 0, -1};
+    if (x2) op.g[0].src[1] = SrcRef{tin2, 0, -1};
+  }
+  op.g[0].out_tensor = tout;
+  op.g[0].aux_tensor = taux;
+  choose_tiling(op);
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    size_t o = off;
+    off = (size_t)round_up((long long)(off + bytes), 256);
+    return o;
+  };
+  for (auto& t : p.tensors) t.offset = take(t.bytes);
+  const size_t wbytes = (size_t)op.ntaps * op.nchunks * 8 * cout * (precision == 0 ? 2 : 4);
+  op.g[0].w_off = take(wbytes);
+  op.g[0].bias_off = take((size_t)cout * 4);
+  CK(cudaMalloc(&p.ws, off));
+  int rc = 0;
+  do {
+    cudaError_t e;
+#define CKB(call)                                                                          \
+  if ((e = (call)) != cudaSuccess) {                                                      \
+    set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e), __FILE__, __LINE__); \
+    rc = -2;                                                                              \
+    break;                                                                                \
+  }
+    CKB(cudaMemset(p.ws, 0, off));
+    CKB(launch_nchw_to_view(x, p.view(tin, 0), n, cin, h, w, precision, 0));
+    if (x2) CKB(launch_nchw_to_view(x2, p.view(tin2, 0), n, cin2, h, w, precision, 0));
+    if (aux) CKB(launch_nchw_to_view(aux, p.view(taux, 0), n, cout, Ho, Wo, precision, 0));
+    PackParams q{};
+    q.seg.w = weight;
+    q.seg.cout = cout, q.seg.cin = cin + cin2, q.seg.ksize = ksize;
+    q.seg.split = x2 ? cin : INT_MAX;
+    q.dst = p.ws + op.g[0].w_off;
+    q.bias_dst = reinterpret_cast<float*>(p.ws + op.g[0].bias_off);
+    q.Cout_p = cout, q.K_tap = op.nchunks * 8, q.fp32 = precision == 0 ? 0 : 1, q.fold = 0, q.eps = 0.f;
+    CKB(launch_pack(q, 0));
+    if (bias) CKB(cudaMemcpy(p.ws + op.g[0].bias_off, bias, (size_t)cout * 4, cudaMemcpyDeviceToDevice));
+    ConvParams cp = p.conv_params(op, n);
+    CKB(launch_conv(cp, precision, 0));
+    CKB(launch_view_to_nchw(p.view(tout, 0), out, n, cout, Ho, Wo, precision, 0));
+    CKB(cudaDeviceSynchronize());
+#undef CKB
+  } while (0);
+  cudaFree(p.ws);
+  p.ws = nullptr;
+  return rc;
+}
+
+// ---------------------------------------------------------------------------------------------
+// JSON description
+// ---------------------------------------------------------------------------------------------
+std::string Plan::describe() const {
+  std::ostringstream o;
+  o << "{\"kind\":" << kind << ",\"micro_batch\":" << mb << ",\"precision\":" << precision << ",\"gran\":" << gran
+    << ",\"workspace_bytes\":" << ws_bytes << ",\"stem_out\":\"" << tensors[stem_out].name << "\",\"layers\":[";
+  for (size_t i = 0; i < layers.size(); ++i) {
+    const LayerSpec& L = layers[i];
+    o << (i ? "," : "") << "{\"conv\":\"" << L.conv << "\",\"bn\":\"" << L.bn << "\",\"cin\":" << L.cin
+      << ",\"cout\":" << L.cout << ",\"k\":" << L.ksize << ",\"stride\":" << L.stride << ",\"pad\":" << L.pad
+      << ",\"bias\":" << (L.bias ? 1 : 0) << "}";
+  }
+  o << "],\"tensors\":[";
+  for (size_t i = 0; i < tensors.size(); ++i) {
+    const TensorInfo& t = tensors[i];
+    o << (i ? "," : "") << "{\"name\":\"" << t.name << "\",\"C\":" << t.C << ",\"H\":" << t.H << ",\"W\":" << t.W
+      << ",\"layout\":" << t.layout << ",\"Hs\":" << t.Hs << ",\"Ws\":" << t.Ws << ",\"Wp\":" << t.Wp
+      << ",\"Pimg\":" << t.Pimg << ",\"g_lo\":" << t.g_lo << ",\"plane\":" << t.plane << ",\"nchunks\":" << t.nchunks
+      << ",\"nphase\":" << t.nphase << ",\"offset\":" << t.offset << ",\"bytes\":" << t.bytes << "}";
+  }
+  o << "],\"program\":[";
+  for (size_t i = 0; i < program.size(); ++i) {
+    const Op& op = program[i];
+    o << (i ? "," : "");
+    if (op.kind == 0) {
+      o << "{\"op\":\"stem\",\"layer\":\"" << layers[stem_layer].conv << "\",\"out\":\"" << tensors[stem_out].name
+        << "\"}";
+    } else if (op.kind == 1) {
+      const ConvOpHost& c = convs[op.index];
+      o << "{\"op\":\"conv\",\"name\":\"" << c.name << "\",\"H\":" << c.H << ",\"W\":" << c.W << ",\"Cout\":" << c.Cout
+        << ",\"nchunks\":" << c.nchunks << ",\"nsrc\":" << c.nsrc << ",\"halo_lo\":" << c.halo_lo
+        << ",\"halo_hi\":" << c.halo_hi << ",\"epi\":" << c.epi << ",\"MT\":" << c.MT << ",\"tps\":" << c.tps
+        << ",\"NS\":" << c.NS << ",\"nstages\":" << c.nstages << ",\"tap_bytes\":" << c.tap_bytes
+        << ",\"tmem_cols\":" << c.tmem_cols << ",\"taps\":[";
+      for (int t = 0; t < c.ntaps; ++t) o << (t ? "," : "") << "[" << c.tap[t].src << "," << c.tap[t].off << "]";
+      o << "],\"groups\":[";
+      for (int gi = 0; gi < c.ngroups; ++gi) {
+        const ConvGroupHost& g = c.g[gi];
+        o << (gi ? "," : "") << "{\"src\":[";
+        for (int s = 0; s < c.nsrc; ++s)
+          o << (s ? "," : "") << "[\"" << tensors[g.src[s].tensor].name << "\"," << g.src[s].chunk0 << ","
+            << g.src[s].phase << "]";
+        o << "],\"out\":[\"" << tensors[g.out_tensor].name << "\"," << g.out_chunk0 << "],\"aux\":";
+        if (g.aux_tensor >= 0)
+          o << "[\"" << tensors[g.aux_tensor].name << "\"," << g.aux_chunk0 << "," << g.aux_nchunks << "]";
+        else
+          o << "null";
+        o << ",\"w_off\":" << g.w_off << ",\"bias_off\":" << g.bias_off << ",\"segs\":[";
+        for (size_t si = 0; si < g.segs.size(); ++si) {
+          const PackSegHost& s = g.segs[si];
+          o << (si ? "," : "") << "{\"layer\":\"" << layers[s.layer].conv << "\",\"split\":"
+            << (s.split == INT_MAX ? -1 : s.split) << ",\"k_off\":" << s.k_off << ",\"cout_off\":" << s.cout_off
+            << "}";
+        }
+        o << "]}";
+      }
+      o << "]}";
+    } else if (op.kind == 2) {
+      const PoolOpHost& po = pools[op.index];
+      o << "{\"op\":\"pool\",\"in\":\"" << tensors[po.in_tensor].name << "\",\"out\":\""
+        << tensors[po.out_tensor].name << "\"}";
+    } else {
+      const HeadOpHost& h = heads[op.index];
+      o << "{\"op\":\"head\",\"in\":\"" << tensors[h.in_tensor].name << "\",\"chunk0\":" << h.chunk0
+        << ",\"classes\":" << h.classes << ",\"out\":" << h.out_index << "}";
+    }
+  }
+  o << "]}";
+  return o.str();
+}
+
+}  // namespace mtldas

@@ -1,0 +1,108 @@
+// Host-side execution plan: the layer program of MTL_Net / Single_Task_Net expressed over the
+// P8 / P8S2 activation layouts (types.h), the workspace map, and the launch sequence.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "types.h"
+
+namespace mtldas {
+
+constexpr int kPatchH = 100, kPatchW = 250;  // utils.py:128 (input patch shape)
+constexpr int kMaxTile = 512;                // largest CTA tile in positions (guard sizing)
+
+struct LayerSpec {  // one (conv, bn) pair of the reference, in state_dict order
+  std::string conv, bn;
+  int cin, cout, ksize, stride, pad;
+  bool bias;
+  int i_w, i_b, i_gamma, i_beta, i_rm, i_rv, i_nbt;  // indices into the state_dict entry list
+};
+
+struct TensorInfo {
+  std::string name;
+  int C, H, W;     // logical (full resolution) shape per sample; C multiple of 16
+  int layout;      // LAY_P8 / LAY_P8S2
+  int Hs, Ws;      // stored plane geometry (== H,W for P8; ceil(H/2), ceil(W/2) for P8S2)
+  int Wp, Pimg;    // Ws+1, (Hs+1)*Wp
+  int g_lo;
+  long long plane; // positions per chunk plane
+  int nchunks, nphase;
+  size_t offset, bytes;
+};
+
+struct SrcRef {
+  int tensor, chunk0, phase;  // phase -1: P8 source
+};
+struct PackSegHost {
+  int layer;                  // index into layers
+  int split, k_off, cout_off;
+};
+struct ConvGroupHost {
+  SrcRef src[kMaxSrc];
+  int out_tensor, out_chunk0;
+  int aux_tensor, aux_chunk0, aux_nchunks;
+  size_t w_off, bias_off;     // into the workspace
+  std::vector<PackSegHost> segs;
+};
+struct ConvOpHost {
+  std::string name;
+  int H, W, Cout, nchunks, nsrc, ntaps, halo_lo, halo_hi, epi, ngroups;
+  ConvTapDev tap[kMaxTaps];
+  ConvGroupHost g[kMaxGroups];
+  int MT, tps, NS, nstages, tap_bytes, tmem_cols;
+};
+struct PoolOpHost {
+  std::string name;
+  int in_tensor, out_tensor;
+};
+struct HeadOpHost {
+  int in_tensor, chunk0, classes, out_index;
+};
+struct Op {
+  int kind;  // 0 stem, 1 conv, 2 pool, 3 head
+  int index;
+};
+
+struct Plan {
+  int kind, mb, precision, ntasks;
+  int gran;  // bytes per granule (16 bf16 / 32 fp32)
+  std::vector<std::string> state_keys;
+  std::vector<LayerSpec> layers;
+  std::vector<TensorInfo> tensors;
+  std::vector<ConvOpHost> convs;
+  std::vector<PoolOpHost> pools;
+  std::vector<HeadOpHost> heads;
+  std::vector<Op> program;
+  int stem_layer, stem_out;
+  size_t stem_w_off, stem_b_off;
+  size_t x_stage_off, out_stage_off;
+  size_t ws_bytes;
+  char* ws = nullptr;
+  bool packed = false;
+  int last_launches = 0;
+  int swap_desc = 0;
+
+  int find_tensor(const std::string& n) const;
+  ActView view(int tensor, int chunk0) const;
+  ConvParams conv_params(const ConvOpHost& op, int nb) const;
+  std::string describe() const;
+};
+
+Plan* build_plan(int kind, int mb, int precision);
+void choose_tiling(ConvOpHost& op);
+int plan_pack_eval(Plan& p, const void* const* state, cudaStream_t stream);
+int plan_forward_eval(Plan& p, const float* x, int n, float* out0, float* out1, cudaStream_t stream);
+
+int plan_profile_eval(Plan& p, const float* x, int n, float* out0, float* out1, cudaStream_t stream,
+                      float* ms_per_op, int cap);
+int plan_read_tensor(Plan& p, const char* name, int nb, float* out_nchw, cudaStream_t stream);
+int single_conv(const float* x, const float* x2, const float* weight, const float* bias, const float* aux,
+                float* out, int n, int cin, int cin2, int h, int w, int cout, int ksize, int stride, int epi,
+                int precision, int aux_phase_split, int swap_desc);
+
+void set_error(const char* fmt, ...);
+const char* last_error_text();
+
+}  // namespace mtldas

@@ -1,0 +1,153 @@
+"""Plan objects over the C ABI: device memory and streams come from torch, compute from the library."""
+import ctypes
+import json
+
+import torch
+
+from ._lib import lib, check, MtldasError
+
+KINDS = {"MTL": 0, "single_distance": 1, "single_event": 2}
+PRECISIONS = {"bf16": 0, "fp32": 1}
+
+
+def _stream_ptr(device):
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _require_b200(device):
+    if not torch.cuda.is_available():
+        raise MtldasError("mtldas_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+    with torch.cuda.device(device):
+        if not lib.mtldas_device_ok():
+            raise MtldasError("mtldas_b200 kernels are built for sm_100a (B200) only")
+
+
+class EvalPlan:
+    """Eval-mode forward of MTL_Net / Single_Task_Net (utils.py:249-272) through mtldas_plan_*."""
+
+    def __init__(self, kind="MTL", micro_batch=256, precision="bf16", device=None, need_device=True):
+        self.kind, self.precision = kind, precision
+        self.micro_batch = int(micro_batch)
+        self._h = lib.mtldas_plan_create(KINDS[kind], self.micro_batch, PRECISIONS[precision])
+        if not self._h:
+            raise MtldasError("plan_create: " + lib.mtldas_last_error().decode())
+        self.n_state = lib.mtldas_plan_num_state_entries(self._h)
+        self.keys = [lib.mtldas_plan_state_key(self._h, i).decode() for i in range(self.n_state)]
+        self.workspace_bytes = lib.mtldas_plan_workspace_bytes(self._h)
+        self.classes = {"MTL": (16, 2), "single_distance": (16,), "single_event": (2,)}[kind]
+        self.device = None
+        self._ws = None
+        self._state_keepalive = None
+        if need_device:
+            self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+            _require_b200(self.device)
+            with torch.cuda.device(self.device):
+                self._ws = torch.empty(self.workspace_bytes + 256, dtype=torch.uint8, device=self.device)
+                ptr = (self._ws.data_ptr() + 255) & ~255
+                check(lib.mtldas_plan_bind_workspace(self._h, ctypes.c_void_p(ptr), self.workspace_bytes,
+                                                     _stream_ptr(self.device)), "bind_workspace")
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            lib.mtldas_plan_destroy(h)
+            self._h = None
+
+    def describe(self):
+        n = lib.mtldas_plan_describe(self._h, None, 0)
+        buf = ctypes.create_string_buffer(n)
+        lib.mtldas_plan_describe(self._h, buf, n)
+        return json.loads(buf.value.decode())
+
+    def pack(self, state_dict):
+        """state_dict: {key: CUDA tensor} with the reference's keys (load_state_dict contract)."""
+        tensors = []
+        for k in self.keys:
+            t = state_dict[k]
+            if t.device != self.device:
+                raise MtldasError(f"state entry {k} is on {t.device}, plan on {self.device}")
+            want = torch.int64 if k.endswith("num_batches_tracked") else torch.float32
+            if t.dtype != want or not t.is_contiguous():
+                t = t.to(want).contiguous()
+            tensors.append(t)
+        arr = (ctypes.c_void_p * self.n_state)(*[t.data_ptr() for t in tensors])
+        with torch.cuda.device(self.device):
+            check(lib.mtldas_plan_pack_eval(self._h, arr, self.n_state, _stream_ptr(self.device)), "pack_eval")
+        self._state_keepalive = tensors
+
+    def forward(self, x):
+        if not x.is_cuda:
+            raise MtldasError("input must be a CUDA tensor; there is no CPU fallback")
+        if x.dim() != 4 or tuple(x.shape[1:]) != (1, 100, 250):
+            raise ValueError(f"expected [N,1,100,250], got {tuple(x.shape)}")
+        x = x.contiguous().float()
+        n = x.shape[0]
+        outs = [torch.empty((n, c), dtype=torch.float32, device=x.device) for c in self.classes]
+        with torch.cuda.device(self.device):
+            check(lib.mtldas_plan_forward_eval(self._h, ctypes.c_void_p(x.data_ptr()), n,
+                                               ctypes.c_void_p(outs[0].data_ptr()),
+                                               ctypes.c_void_p(outs[1].data_ptr()) if len(outs) > 1 else None,
+                                               _stream_ptr(self.device)), "forward_eval")
+        return tuple(outs)
+
+    def forward_host(self, x_host, outs_host=None):
+        """Host buffers in, host buffers out (H2D + forward + D2H + sync inside the call)."""
+        n = x_host.shape[0]
+        if outs_host is None:
+            outs_host = [torch.empty((n, c), dtype=torch.float32).pin_memory() for c in self.classes]
+        with torch.cuda.device(self.device):
+            check(lib.mtldas_plan_forward_eval_host(self._h, ctypes.c_void_p(x_host.data_ptr()), n,
+                                                    ctypes.c_void_p(outs_host[0].data_ptr()),
+                                                    ctypes.c_void_p(outs_host[1].data_ptr()) if len(outs_host) > 1 else None,
+                                                    _stream_ptr(self.device)), "forward_eval_host")
+        return tuple(outs_host)
+
+    def profile(self, x):
+        """Per-op device milliseconds of one forward (CUDA events around every launch)."""
+        n = x.shape[0]
+        outs = [torch.empty((n, c), dtype=torch.float32, device=x.device) for c in self.classes]
+        nops = len(self.describe()["program"])
+        ms = (ctypes.c_float * nops)()
+        with torch.cuda.device(self.device):
+            check(lib.mtldas_plan_profile_eval(self._h, ctypes.c_void_p(x.data_ptr()), n,
+                                               ctypes.c_void_p(outs[0].data_ptr()),
+                                               ctypes.c_void_p(outs[1].data_ptr()) if len(outs) > 1 else None,
+                                               _stream_ptr(self.device), ms, nops), "profile_eval")
+        return list(ms)
+
+    @property
+    def last_launch_count(self):
+        return lib.mtldas_plan_last_launch_count(self._h)
+
+    def read_tensor(self, name, nb):
+        d = self.describe()
+        t = next(t for t in d["tensors"] if t["name"] == name)
+        out = torch.empty((nb, t["C"], t["H"], t["W"]), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(lib.mtldas_plan_read_tensor(self._h, name.encode(), nb, ctypes.c_void_p(out.data_ptr()),
+                                              _stream_ptr(self.device)), "read_tensor")
+        return out
+
+
+def conv2d_nchw(x, weight, bias=None, aux=None, x2=None, stride=1, epilogue=0, precision="bf16",
+                aux_phase_split=False):
+    """One fused convolution through mtldas_conv2d_nchw (unit-parity entry point)."""
+    _require_b200(x.device)
+    n, cin, h, w = x.shape
+    cout, cin_tot, k, _ = weight.shape
+    cin2 = x2.shape[1] if x2 is not None else 0
+    assert cin_tot == cin + cin2
+    ho, wo = (h, w) if stride == 1 else ((h + 1) // 2, (w + 1) // 2)
+    out = torch.empty((n, cout, ho, wo), dtype=torch.float32, device=x.device)
+    p = lambda t: ctypes.c_void_p(t.contiguous().data_ptr()) if t is not None else None  # noqa: E731
+    keep = [t.contiguous().float() if t is not None else None for t in (x, x2, weight, bias, aux)]
+    with torch.cuda.device(x.device):
+        torch.cuda.synchronize()
+        check(lib.mtldas_conv2d_nchw(p(keep[0]), p(keep[1]), p(keep[2]), p(keep[3]), p(keep[4]), p(out), n, cin, cin2,
+                                     h, w, cout, k, stride, epilogue, PRECISIONS[precision], int(aux_phase_split)),
+              "conv2d_nchw")
+    return out
+
+
+def umma_selftest(n_cols=16, row_shift=0, swap=0):
+    return float(lib.mtldas_umma_selftest(n_cols, row_shift, swap))

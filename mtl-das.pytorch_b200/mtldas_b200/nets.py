@@ -1,0 +1,130 @@
+"""Drop-in modules for the reference's model A / model B.
+
+They own a parameter tree of stock ``nn.Conv2d`` / ``nn.BatchNorm2d`` objects created in the
+reference's registration order, so ``state_dict()`` has the reference's keys, shapes and dtypes
+(268 entries for MTL_Net incl. the ``att_mask_generato2`` typo),
+``load_state_dict(strict=True)`` works both ways, ``torch.manual_seed(s); MTL_Net()`` initialises
+bit-identically, and ``optim.Adam(model.parameters())`` sees ordinary leaf parameters
+(/root/reference/utils.py:85-96,122-125,133-134).  ``forward`` never calls those layers: it hands
+their tensors to the C-ABI library (mtldas_b200.engine).  Without the CUDA library / a B200 the
+forward raises -- there is deliberately no PyTorch fallback.
+
+forward returns what the reference returns (modelA_MTL.py:174, modelB_singleTask.py:178):
+MTL_Net -> (log-probs distance [N,16], log-probs event [N,2]); Single_Task_Net -> one tensor.
+"""
+import os
+
+import torch
+import torch.nn as nn
+
+from ._lib import MtldasError
+from .engine import EvalPlan
+
+_WIDTHS = (16, 16, 32, 64, 128)          # modelA_MTL.py:61-66
+_CLASSES = {"distance": 16, "event": 2}  # modelA_MTL.py:68-69
+
+
+def _seq(*mods):
+    return nn.Sequential(*mods)
+
+
+def _res_unit(cin, cout, stride):
+    """Parameter holder with the key layout of the reference ResBlock (left.{0,1,3,4}, shortcut.{0,1})."""
+    unit = nn.Module()
+    unit.left = _seq(nn.Conv2d(cin, cout, 3, stride, 1, bias=False), nn.BatchNorm2d(cout), nn.ReLU(inplace=True),
+                     nn.Conv2d(cout, cout, 3, 1, 1, bias=False), nn.BatchNorm2d(cout))
+    unit.shortcut = _seq()
+    if stride != 1 or cin != cout:
+        unit.shortcut = _seq(nn.Conv2d(cin, cout, 1, stride, bias=False), nn.BatchNorm2d(cout))
+    return unit
+
+
+def _mask_unit(cin, cmid, cout):
+    return _seq(nn.Conv2d(cin, cmid, 1), nn.BatchNorm2d(cmid), nn.ReLU(inplace=True),
+                nn.Conv2d(cmid, cout, 3, padding=1), nn.BatchNorm2d(cout), nn.Sigmoid())
+
+
+def _out_unit(cin, cout):
+    return _seq(nn.Conv2d(cin, cout, 3, 1, 1, bias=False), nn.BatchNorm2d(cout), nn.ReLU(inplace=True))
+
+
+class _DasNet(nn.Module):
+    """Shared implementation; `tasks` is ('distance','event') for model A, one task for model B."""
+
+    def __init__(self, tasks):
+        super().__init__()
+        w = _WIDTHS
+        self.tasks = list(tasks)
+        nt = len(self.tasks)
+        self.conv1 = _seq(nn.Conv2d(1, w[0], 7, 3, 2, bias=False), nn.BatchNorm2d(w[0]), nn.ReLU())
+        plan = [(w[0], w[1], 1), (w[1], w[1], 1), (w[1], w[2], 2), (w[2], w[2], 1),
+                (w[2], w[3], 2), (w[3], w[3], 1), (w[3], w[4], 2), (w[4], w[4], 1)]
+        for i, (ci, co, s) in enumerate(plan, start=1):
+            setattr(self, f"resblock{i}", _res_unit(ci, co, s))
+        names = ("att_mask_generator1", "att_mask_generato2", "att_mask_generator3", "att_mask_generator4")
+        for lvl, name in enumerate(names, start=1):
+            cin = w[lvl] if lvl == 1 else 2 * w[lvl]
+            setattr(self, name, nn.ModuleList([_mask_unit(cin, w[lvl] // 2, w[lvl]) for _ in range(nt)]))
+        for lvl in (1, 2, 3):
+            setattr(self, f"output_layer{lvl}", nn.ModuleList([_out_unit(w[lvl], w[lvl + 1]) for _ in range(nt)]))
+        # parameter-free members the reference also registers (no state_dict entries)
+        self.down_sampling = nn.MaxPool2d(kernel_size=2, stride=2, ceil_mode=True)
+        self._plans = {}
+        self._packed_sig = {}
+        self.precision = os.environ.get("MTLDAS_PRECISION", "bf16")
+        self.micro_batch = int(os.environ.get("MTLDAS_MICRO_BATCH", "256"))
+
+    # ---- engine plumbing -------------------------------------------------------------------
+    def _kind(self):
+        return "MTL" if len(self.tasks) == 2 else "single_" + self.tasks[0]
+
+    def _eval_plan(self, device):
+        key = (str(device), self.precision, self.micro_batch)
+        if key not in self._plans:
+            self._plans[key] = EvalPlan(self._kind(), self.micro_batch, self.precision, device)
+        plan = self._plans[key]
+        sd = {k: v for k, v in self.state_dict(keep_vars=True).items()}
+        sig = tuple((v.data_ptr(), v._version) for v in sd.values())
+        if self._packed_sig.get(key) != sig:
+            plan.pack({k: v.detach() for k, v in sd.items()})
+            self._packed_sig[key] = sig
+        return plan
+
+    def _forward_impl(self, x):
+        if not isinstance(x, torch.Tensor) or not x.is_cuda:
+            raise MtldasError("mtldas_b200 modules run on a B200 through the CUDA extension only; "
+                              "got a non-CUDA input and there is no CPU fallback")
+        if self.training:
+            raise MtldasError("training-mode forward/backward is not available in this build yet")
+        return self._eval_plan(x.device).forward(x)
+
+
+class MTL_Net(_DasNet):
+    """Drop-in for /root/reference/model/modelA_MTL.py:53 (constructor takes no arguments)."""
+
+    def __init__(self):
+        super().__init__(("distance", "event"))
+        self.task1pool = nn.AdaptiveAvgPool2d((1, 1))
+        self.task2pool = nn.AdaptiveAvgPool2d((1, 1))
+        self.task1pool1d = nn.AvgPool1d(kernel_size=_WIDTHS[-1] // 16, stride=_WIDTHS[-1] // 16)
+        self.task2pool1d = nn.AvgPool1d(kernel_size=_WIDTHS[-1] // 2, stride=_WIDTHS[-1] // 2)
+
+    def forward(self, x):
+        pred1, pred2 = self._forward_impl(x)
+        return pred1, pred2
+
+
+class Single_Task_Net(_DasNet):
+    """Drop-in for /root/reference/model/modelB_singleTask.py:53 (task='distance' | 'event')."""
+
+    def __init__(self, task="distance"):
+        if task not in _CLASSES:
+            raise ValueError  # modelB_singleTask.py:127-128
+        super().__init__((task,))
+        k = _WIDTHS[-1] // _CLASSES[task]
+        idx = 1 if task == "distance" else 2
+        setattr(self, f"task{idx}pool", nn.AdaptiveAvgPool2d((1, 1)))
+        setattr(self, f"task{idx}pool1d", nn.AvgPool1d(kernel_size=k, stride=k))
+
+    def forward(self, x):
+        return self._forward_impl(x)[0]

@@ -1,0 +1,100 @@
+"""Generate tests/golden/*.npz from the UNMODIFIED reference modules.
+
+Run in the build container only (needs /root/reference):
+
+    python tests/golden/make_golden.py
+
+It imports /root/reference/model/modelA_MTL.py::MTL_Net and
+modelB_singleTask.py::Single_Task_Net, loads the oracle's deterministic synthetic
+state_dict with strict=True (which also pins the state_dict key/shape contract),
+runs eval forward, train forward, the reference loss (NLLLoss per task, summed,
+utils.py:139,361,367) and backward, and stores the results.  The oracle
+(oracle/mtl_oracle.py) is then checked against these files by
+tests/test_oracle_golden.py on any machine; the GPU path is checked against the
+oracle.  Nothing at test time reads /root/reference.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, "/root/reference")
+
+from oracle import mtl_oracle as O  # noqa: E402
+from model.modelA_MTL import MTL_Net  # noqa: E402  (reference)
+from model.modelB_singleTask import Single_Task_Net  # noqa: E402  (reference)
+
+N = 6
+
+
+def build(kind):
+    if kind == "MTL":
+        return MTL_Net()
+    return Single_Task_Net(task=kind.split("_")[1])
+
+
+def run(kind, dtype):
+    torch.manual_seed(0)
+    torch.set_num_threads(8)
+    sd = O.synth_state_dict(kind, seed=0)
+    x, yd, ye = O.synth_patches(N, seed=1234)
+    m = build(kind)
+    assert [k for k in m.state_dict().keys()] == [k for k, _, _ in O.state_dict_keys(kind)], "key order"
+    m.load_state_dict(sd, strict=True)
+    if dtype == torch.float64:
+        m = m.double()
+    out = {}
+    # eval forward (utils.py:249-272)
+    m.eval()
+    with torch.no_grad():
+        o = m(x.to(dtype))
+    o = o if isinstance(o, tuple) else (o,)
+    for i, t in enumerate(o):
+        out[f"eval_out{i}"] = t.numpy()
+    # train forward + loss + backward (utils.py:344-373)
+    m.train()
+    m.zero_grad()
+    o = m(x.to(dtype))
+    o = o if isinstance(o, tuple) else (o,)
+    crit = torch.nn.NLLLoss()
+    labels = O.task_labels(kind, yd, ye)
+    losses = [crit(oi, li.long()) for oi, li in zip(o, labels)]
+    loss = sum(losses)
+    loss.backward()
+    for i, t in enumerate(o):
+        out[f"train_out{i}"] = t.detach().numpy()
+        out[f"loss{i}"] = losses[i].detach().numpy()
+    names, norms = [], []
+    for k, p in m.named_parameters():
+        names.append(k)
+        norms.append(float(p.grad.double().norm()))
+        # keep full gradients only for small tensors and a few anchor conv weights
+        if p.numel() <= 128 or k in ("conv1.0.weight", "resblock1.left.0.weight", "resblock3.shortcut.0.weight",
+                                     "att_mask_generato2.0.0.weight", "output_layer1.0.0.weight"):
+            out["grad:" + k] = p.grad.numpy()
+    out["grad_names"] = np.array(names)
+    out["grad_norms"] = np.array(norms, dtype=np.float64)
+    new_sd = m.state_dict()
+    for k in ("conv1.1", "resblock3.shortcut.1", "att_mask_generator4.0.4", "output_layer3.0.1"):
+        for leaf in ("running_mean", "running_var", "num_batches_tracked"):
+            out[f"stat:{k}.{leaf}"] = new_sd[f"{k}.{leaf}"].numpy()
+    return out
+
+
+def main():
+    for kind in ("MTL", "single_distance", "single_event"):
+        for dtype, tag in ((torch.float32, "f32"), (torch.float64, "f64")):
+            if kind != "MTL" and tag == "f64":
+                continue
+            res = run(kind, dtype)
+            path = os.path.join(HERE, f"{kind}_{tag}.npz")
+            np.savez_compressed(path, **res)
+            print(path, os.path.getsize(path) // 1024, "KiB", "loss", [float(res[k]) for k in res if k.startswith("loss")])
+
+
+if __name__ == "__main__":
+    main()
