@@ -28,7 +28,7 @@ for p in (ROOT, PKG):
     if p not in sys.path:
         sys.path.insert(0, p)
 
-METRIC = "MTL samples/sec (inference; train fwd+bwd) on synthetic DAS patches"
+METRIC = "MTL samples/sec (train fwd+bwd; inference) at 1/2/4/8 B200 vs CPU ref"
 UNIT = "samples/s"
 PATCH_BYTES = 100 * 250 * 4
 
@@ -159,8 +159,7 @@ def conv_algorithmic_elems_per_sample(desc):
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from oracle import mtl_oracle as O          # synthetic weights / patches generator (and CPU baseline leg)
-    from mtldas_b200 import EvalPlan
+    from mtldas_b200 import EvalPlan, synth as O   # product-side synthetic weights / patches generator
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))

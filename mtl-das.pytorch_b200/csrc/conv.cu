@@ -66,6 +66,18 @@ __device__ __forceinline__ void epilogue16(const ConvParams& p, const ConvGroupD
 // ---------------------------------------------------------------------------------------------
 constexpr int kSmemHeader = 256;  // barriers + TMEM slot
 
+__device__ __forceinline__ long long gtime() {
+  long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+// slot 0: globaltimer (ns) at CTA start; slots 1..7: SM clock at each stage
+#define DBG(slot)                                                                       \
+  if (p.dbg && blockIdx.y == 0) {                                                       \
+    if ((slot) == 0) p.dbg[(size_t)blockIdx.x * 8] = gtime();                           \
+    p.dbg[(size_t)blockIdx.x * 8 + (slot) + 1] = clock64();                             \
+  }
+
 __global__ void __launch_bounds__(128) conv_umma_kernel(const __grid_constant__ ConvParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   const ConvGroupDev& g = p.g[blockIdx.y];
@@ -84,6 +96,7 @@ __global__ void __launch_bounds__(128) conv_umma_kernel(const __grid_constant__ 
   const int tile_start = blockIdx.x * (p.MT * kTileM);
 
   if (threadIdx.x == 0) {
+    DBG(0)
     ptx::mbar_init(bar_slab, 1);
     ptx::mbar_init(bar_acc, 1);
     for (int i = 0; i < p.NS; ++i) {
@@ -100,6 +113,7 @@ __global__ void __launch_bounds__(128) conv_umma_kernel(const __grid_constant__ 
 
   if (warp == 0 && lane == 0) {
     // ---- producer: input slab, then the weight stages -------------------------------------
+    DBG(1)
     ptx::mbar_arrive_expect_tx(bar_slab, slab_bytes);
     for (int s = 0; s < p.nsrc; ++s) {
       const char* src = g.src[s].base + (long long)(tile_start - p.halo_lo) * 16;
@@ -127,11 +141,13 @@ __global__ void __launch_bounds__(128) conv_umma_kernel(const __grid_constant__ 
     const uint32_t b_sbo = p.swap_desc ? b_kstride : 128u;
     ptx::mbar_wait(bar_slab, 0);
     ptx::tc_fence_after();
+    DBG(2)
     bool first = true;
     for (int st = 0; st < p.nstages; ++st) {
       const int slot = st % p.NS;
       ptx::mbar_wait(bar_wfull + slot, (st / p.NS) & 1);
       ptx::tc_fence_after();
+      if (st == 0) DBG(3)
       const int ntap = min(p.tps, p.ntaps - st * p.tps);
       for (int ti = 0; ti < ntap; ++ti) {
         const ConvTapDev tp = p.tap[st * p.tps + ti];
@@ -151,12 +167,14 @@ __global__ void __launch_bounds__(128) conv_umma_kernel(const __grid_constant__ 
       ptx::umma_commit(bar_wempty + slot);  // stage may be refilled once these MMAs have read it
     }
     ptx::umma_commit(bar_acc);
+    DBG(4)
   }
   __syncwarp();
 
   // ---- epilogue: warp w owns TMEM lanes [32w, 32w+32) ----------------------------------------
   ptx::mbar_wait(bar_acc, 0);
   ptx::tc_fence_after();
+  if (threadIdx.x == 64) DBG(5)
   for (int mt = 0; mt < p.MT; ++mt) {
     const int f = tile_start + mt * kTileM + warp * 32 + lane;
     for (int c0 = 0; c0 < p.Cout; c0 += 16) {
@@ -167,6 +185,7 @@ __global__ void __launch_bounds__(128) conv_umma_kernel(const __grid_constant__ 
   }
   ptx::tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 64) DBG(6)
   if (warp == 1) ptx::tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
 }
 

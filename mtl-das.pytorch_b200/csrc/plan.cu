@@ -6,6 +6,7 @@
 #include <climits>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <sstream>
 
@@ -645,6 +646,36 @@ int single_conv(const float* x, const float* x2, const float* weight, const floa
     CKB(launch_pack(q, 0));
     if (bias) CKB(cudaMemcpy(p.ws + op.g[0].bias_off, bias, (size_t)cout * 4, cudaMemcpyDeviceToDevice));
     ConvParams cp = p.conv_params(op, n);
+    const char* dbg_env = getenv("MTLDAS_CONV_DEBUG");
+    if (dbg_env && precision == 0) {
+      // diagnostics: per-CTA timeline of a warm (second) launch
+      int ntile = (int)((cp.body + cp.MT * kTileM - 1) / (cp.MT * kTileM));
+      long long* dbg = nullptr;
+      CKB(cudaMalloc(&dbg, (size_t)ntile * 8 * sizeof(long long)));
+      CKB(cudaMemset(dbg, 0, (size_t)ntile * 8 * sizeof(long long)));
+      CKB(launch_conv(cp, precision, 0));
+      CKB(cudaDeviceSynchronize());
+      cp.dbg = dbg;
+      CKB(launch_conv(cp, precision, 0));
+      CKB(cudaDeviceSynchronize());
+      std::vector<long long> h((size_t)ntile * 8);
+      CKB(cudaMemcpy(h.data(), dbg, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+      cudaFree(dbg);
+      long long t0 = h[0], t1 = 0;
+      for (int i = 0; i < ntile; ++i) {
+        t0 = std::min(t0, h[(size_t)i * 8]);
+        t1 = std::max(t1, h[(size_t)i * 8]);
+      }
+      fprintf(stderr, "[convdbg] tiles=%d MT=%d NS=%d tps=%d smem=%zu last CTA start +%lld ns\n", ntile, cp.MT, cp.NS,
+              cp.tps, conv_umma_smem_bytes(cp), t1 - t0);
+      for (int i = 0; i < ntile; i += std::max(1, ntile / 6)) {
+        const long long* r = &h[(size_t)i * 8];
+        fprintf(stderr,
+                "[convdbg] cta %4d start+%lld ns | clk: setup %lld slab %lld w0 %lld issued %lld acc %lld epi %lld\n", i,
+                r[0] - t0, r[2] - r[1], r[3] - r[2], r[4] - r[3], r[5] - r[4], r[6] - r[5], r[7] - r[6]);
+      }
+      cp.dbg = nullptr;
+    }
     CKB(launch_conv(cp, precision, 0));
     CKB(launch_view_to_nchw(p.view(tout, 0), out, n, cout, Ho, Wo, precision, 0));
     CKB(cudaDeviceSynchronize());

@@ -71,6 +71,7 @@ struct ConvParams {
   int epi;
   int swap_desc;           // debug: swap the LBO/SBO roles in the UMMA descriptors
   int ngroups;
+  long long* dbg;          // optional [grid.x][8] timeline (globaltimer ns) for diagnostics, else null
   ConvTapDev tap[kMaxTaps];
   ConvGroupDev g[kMaxGroups];
 };

@@ -9,5 +9,6 @@ There is no CPU fallback: without the built library and a B200 the compute calls
 from ._lib import lib, MtldasError, library_path  # noqa: F401
 from .engine import EvalPlan, conv2d_nchw, umma_selftest  # noqa: F401
 from .nets import MTL_Net, Single_Task_Net  # noqa: F401
+from . import synth  # noqa: F401
 
 __all__ = ["MTL_Net", "Single_Task_Net", "EvalPlan", "conv2d_nchw", "umma_selftest", "lib", "MtldasError"]
