@@ -127,6 +127,10 @@ MTLDAS_API int mtldas_conv2d_nchw(const float* dev_x, const float* dev_x2, const
  * conventions the library uses and returns the max abs error (or <0 on error). */
 MTLDAS_API float mtldas_umma_selftest(int n_cols, int row_shift, int swap_lbo_sbo);
 
+/* tensor-pipe rate probe (diagnostics): cycles per 128 x n_cols x 16 MMA; host_out2[0] = to completion,
+ * host_out2[1] = issue only. mode 0 interleaved layout, 1 swizzle-128B, 2 interleaved + per-MMA address math. */
+MTLDAS_API int mtldas_umma_rate(int n_cols, int mode, int reps, float* host_out2);
+
 #ifdef __cplusplus
 }
 #endif

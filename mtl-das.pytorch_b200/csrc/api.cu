@@ -41,6 +41,10 @@ mtldas_plan* mtldas_plan_create(int model_kind, int micro_batch, int precision) 
   h->p = build_plan(model_kind, micro_batch, precision);
   const char* sw = getenv("MTLDAS_UMMA_SWAP_DESC");
   h->p->swap_desc = (sw && sw[0] == '1') ? 1 : 0;
+  const char* ng = getenv("MTLDAS_NO_GRAPH");
+  h->p->use_graphs = (ng && ng[0] == '1') ? 0 : 1;
+  const char* np = getenv("MTLDAS_NO_PDL");
+  h->p->use_pdl = (np && np[0] == '1') ? 0 : 1;
   return h;
 }
 void mtldas_plan_destroy(mtldas_plan* plan) {
@@ -173,6 +177,10 @@ int mtldas_conv2d_nchw(const float* dev_x, const float* dev_x2, const float* dev
 
 float mtldas_umma_selftest(int n_cols, int row_shift, int swap_lbo_sbo) {
   return umma_selftest(n_cols, row_shift, swap_lbo_sbo);
+}
+
+int mtldas_umma_rate(int n_cols, int mode, int reps, float* host_out2) {
+  return umma_rate(n_cols, mode, reps, host_out2);
 }
 
 }  // extern "C"

@@ -64,7 +64,9 @@ __device__ __forceinline__ void epilogue16(const ConvParams& p, const ConvGroupD
 // ---------------------------------------------------------------------------------------------
 // tcgen05 kernel
 // ---------------------------------------------------------------------------------------------
-constexpr int kSmemHeader = 256;  // barriers + TMEM slot
+// shared memory header: mbarriers [0,192), TMEM base slot at 192, bias (<= 128 floats... 256) at 256
+constexpr int kSmemHeader = 1280;
+constexpr int kBarSlab = 0, kBarAcc = 1, kBarWFull = 5, kBarWEmpty = 5 + kMaxRing;  // 8-byte slots
 
 __device__ __forceinline__ long long gtime() {
   long long t;
@@ -74,115 +76,241 @@ __device__ __forceinline__ long long gtime() {
 // slot 0: globaltimer (ns) at CTA start; slots 1..7: SM clock at each stage
 #define DBG(slot)                                                                       \
   if (p.dbg && blockIdx.y == 0) {                                                       \
-    if ((slot) == 0) p.dbg[(size_t)blockIdx.x * 8] = gtime();                           \
-    p.dbg[(size_t)blockIdx.x * 8 + (slot) + 1] = clock64();                             \
+    if ((slot) == 0) p.dbg[(size_t)blockIdx.x * 16] = gtime();                           \
+    p.dbg[(size_t)blockIdx.x * 16 + (slot) + 1] = clock64();                             \
   }
 
-__global__ void __launch_bounds__(128) conv_umma_kernel(const __grid_constant__ ConvParams p) {
+// Epilogue of 16 consecutive channels [c0, c0+16) of one output position held in registers.
+// Everything it needs is passed in registers (the asm "memory" clobbers of the pipeline would otherwise make
+// the compiler re-read the kernel parameter block for every use).
+template <typename T, int EPI>
+__device__ __forceinline__ void epilogue_cols(const float* bias_s, int c0, bool valid, float* v, const char* aux_addr0,
+                                              long long aux_plane_bytes, int aux_nchunks, char* out_addr0,
+                                              long long out_plane_bytes) {
+  const int ch = c0 >> 3;
+  if (valid) {
+    float a[16];
+    if (EPI == EPI_ADD_RELU || EPI == EPI_SIGMOID_MUL) {
+      const int ac = ch >= aux_nchunks ? ch - aux_nchunks : ch;  // tasks stacked along Cout share one feature map
+      load8<T>(aux_addr0 + ac * aux_plane_bytes, a);
+      load8<T>(aux_addr0 + (ac + 1) * aux_plane_bytes, a + 8);
+    }
+    const float4* b4 = reinterpret_cast<const float4*>(bias_s + c0);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float4 bb = b4[q];
+      v[4 * q + 0] += bb.x, v[4 * q + 1] += bb.y, v[4 * q + 2] += bb.z, v[4 * q + 3] += bb.w;
+    }
+    if (EPI == EPI_ADD_RELU) {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j] + a[j], 0.f);
+    } else if (EPI == EPI_SIGMOID_MUL) {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) v[j] = __fdividef(a[j], 1.f + __expf(-v[j]));
+    } else if (EPI == EPI_RELU) {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] = 0.f;
+  }
+  store8<T>(out_addr0 + ch * out_plane_bytes, v);
+  store8<T>(out_addr0 + (ch + 1) * out_plane_bytes, v + 8);
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(128, 6) conv_umma_kernel(const __grid_constant__ ConvParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   const ConvGroupDev& g = p.g[blockIdx.y];
-  uint64_t* bar_slab = reinterpret_cast<uint64_t*>(smem);
-  uint64_t* bar_acc = bar_slab + 1;
-  uint64_t* bar_wfull = bar_slab + 2;
-  uint64_t* bar_wempty = bar_slab + 2 + kMaxRing;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 192);
+  float* bias_s = reinterpret_cast<float*>(smem + 256);
   uint8_t* slab = smem + kSmemHeader;
-  const uint32_t chunk_bytes = (uint32_t)p.SP * 16u;                     // one channel chunk of the slab
+  const uint32_t chunk_bytes = (uint32_t)p.SP * 16u;  // one channel chunk of the slab
   const uint32_t slab_bytes = (uint32_t)(p.nsrc * p.nchunks) * chunk_bytes;
   uint8_t* wring = slab + ((slab_bytes + 127u) & ~127u);
   const uint32_t stage_bytes = (uint32_t)(p.tps * p.tap_bytes);
+  const bool resident = (p.nstages == 1);  // all taps in one stage: accumulators can finish one by one
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tile_start = blockIdx.x * (p.MT * kTileM);
 
+  ptx::pdl_launch_dependents();
   if (threadIdx.x == 0) {
     DBG(0)
-    ptx::mbar_init(bar_slab, 1);
-    ptx::mbar_init(bar_acc, 1);
+    ptx::mbar_init(bars + kBarSlab, 1);
+    for (int i = 0; i < 4; ++i) ptx::mbar_init(bars + kBarAcc + i, 1);
     for (int i = 0; i < p.NS; ++i) {
-      ptx::mbar_init(bar_wfull + i, 1);
-      ptx::mbar_init(bar_wempty + i, 1);
+      ptx::mbar_init(bars + kBarWFull + i, 1);
+      ptx::mbar_init(bars + kBarWEmpty + i, 1);
     }
     ptx::fence_mbar_init();
   }
   if (warp == 1) ptx::tmem_alloc(tmem_slot, (uint32_t)p.tmem_cols);
+  for (int i = threadIdx.x; i < p.Cout; i += 128) bias_s[i] = g.bias[i];
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 0 && lane == 0) {
-    // ---- producer: input slab, then the weight stages -------------------------------------
-    DBG(1)
-    ptx::mbar_arrive_expect_tx(bar_slab, slab_bytes);
-    for (int s = 0; s < p.nsrc; ++s) {
-      const char* src = g.src[s].base + (long long)(tile_start - p.halo_lo) * 16;
-      for (int c = 0; c < p.nchunks; ++c)
-        ptx::bulk_g2s(slab + (size_t)(s * p.nchunks + c) * chunk_bytes, src + (long long)c * g.src[s].plane_bytes,
-                      chunk_bytes, bar_slab);
+  if (warp == 0) {
+    // ---- producer warp: one elected thread issues the input slab, then the weight stages --------
+    if (ptx::elect_one()) {
+      // weights first (they do not depend on the previous kernel), then wait for it, then the input slab
+      const int pre = min(p.nstages, p.NS);
+      for (int st = 0; st < pre; ++st) {
+        const int ntap = min(p.tps, p.ntaps - st * p.tps);
+        const uint32_t bytes = (uint32_t)(ntap * p.tap_bytes);
+        ptx::mbar_arrive_expect_tx(bars + kBarWFull + st, bytes);
+        ptx::bulk_g2s(wring + (size_t)st * stage_bytes, g.w + (size_t)st * stage_bytes, bytes, bars + kBarWFull + st);
+      }
+      ptx::pdl_grid_wait();
+      DBG(1)
+      ptx::mbar_arrive_expect_tx(bars + kBarSlab, slab_bytes);
+      for (int s = 0; s < p.nsrc; ++s) {
+        const char* src = g.src[s].base + (long long)(tile_start - p.halo_lo) * 16;
+        for (int c = 0; c < p.nchunks; ++c)
+          ptx::bulk_g2s(slab + (size_t)(s * p.nchunks + c) * chunk_bytes, src + (long long)c * g.src[s].plane_bytes,
+                        chunk_bytes, bars + kBarSlab);
+      }
+      for (int st = pre; st < p.nstages; ++st) {
+        const int slot = st % p.NS;
+        ptx::mbar_wait(bars + kBarWEmpty + slot, ((st / p.NS) - 1) & 1);
+        const int ntap = min(p.tps, p.ntaps - st * p.tps);
+        const uint32_t bytes = (uint32_t)(ntap * p.tap_bytes);
+        ptx::mbar_arrive_expect_tx(bars + kBarWFull + slot, bytes);
+        ptx::bulk_g2s(wring + (size_t)slot * stage_bytes, g.w + (size_t)st * stage_bytes, bytes,
+                      bars + kBarWFull + slot);
+      }
     }
-    for (int st = 0; st < p.nstages; ++st) {
-      const int slot = st % p.NS;
-      if (st >= p.NS) ptx::mbar_wait(bar_wempty + slot, ((st / p.NS) - 1) & 1);
-      int ntap = min(p.tps, p.ntaps - st * p.tps);
-      uint32_t bytes = (uint32_t)(ntap * p.tap_bytes);
-      ptx::mbar_arrive_expect_tx(bar_wfull + slot, bytes);
-      ptx::bulk_g2s(wring + (size_t)slot * stage_bytes, g.w + (size_t)st * stage_bytes, bytes, bar_wfull + slot);
-    }
-  } else if (warp == 1 && lane == 0) {
-    // ---- MMA issuer -------------------------------------------------------------------------
-    const uint32_t idesc = ptx::umma_idesc_bf16(kTileM, p.Cout, 0, 0);
-    const uint32_t slab_a = ptx::smem_u32(slab);
-    const uint32_t wring_a = ptx::smem_u32(wring);
-    const uint32_t a_lbo = p.swap_desc ? 128u : chunk_bytes;
-    const uint32_t a_sbo = p.swap_desc ? chunk_bytes : 128u;
-    const uint32_t b_kstride = (uint32_t)p.Cout * 16u;  // bytes between 8-channel chunks of the weights
-    const uint32_t b_lbo = p.swap_desc ? 128u : b_kstride;
-    const uint32_t b_sbo = p.swap_desc ? b_kstride : 128u;
-    ptx::mbar_wait(bar_slab, 0);
-    ptx::tc_fence_after();
-    DBG(2)
-    bool first = true;
-    for (int st = 0; st < p.nstages; ++st) {
-      const int slot = st % p.NS;
-      ptx::mbar_wait(bar_wfull + slot, (st / p.NS) & 1);
+    __syncwarp();
+  } else if (warp == 1) {
+    // ---- MMA warp: ONE elected thread runs the whole issue loop (ptxas keeps the descriptors in uniform
+    // registers inside an elect.sync region).  Per MMA only the 14-bit start-address fields change, so the
+    // loop adds small constants to the low descriptor words.
+    if (ptx::elect_one()) {
+      const uint32_t idesc = ptx::umma_idesc_bf16(kTileM, p.Cout, 0, 0);
+      const uint32_t b_kstride = (uint32_t)p.Cout * 16u;  // bytes between 8-channel chunks of the weights
+      const uint64_t a_hi = (ptx::umma_desc(0, p.swap_desc ? 128u : chunk_bytes, p.swap_desc ? chunk_bytes : 128u));
+      const uint64_t b_hi = (ptx::umma_desc(0, p.swap_desc ? 128u : b_kstride, p.swap_desc ? b_kstride : 128u));
+      const uint32_t slab16 = ptx::smem_u32(slab) >> 4;        // all addresses below in 16-byte units
+      const uint32_t wring16 = ptx::smem_u32(wring) >> 4;
+      const uint32_t chunk16 = chunk_bytes >> 4;
+      const uint32_t a_kstep = 2u * chunk16, b_kstep = 2u * (uint32_t)p.Cout;
+      const uint32_t tap16 = (uint32_t)p.tap_bytes >> 4, stage16 = stage_bytes >> 4;
+      const int MT = p.MT, KC2 = p.nchunks >> 1, Cout = p.Cout, ntaps = p.ntaps;
+      ptx::mbar_wait(bars + kBarSlab, 0);
       ptx::tc_fence_after();
-      if (st == 0) DBG(3)
-      const int ntap = min(p.tps, p.ntaps - st * p.tps);
-      for (int ti = 0; ti < ntap; ++ti) {
-        const ConvTapDev tp = p.tap[st * p.tps + ti];
-        const uint32_t a_tap = slab_a + (uint32_t)(tp.src * p.nchunks) * chunk_bytes +
-                               (uint32_t)(p.halo_lo + tp.off) * 16u;
-        const uint32_t b_tap = wring_a + (uint32_t)slot * stage_bytes + (uint32_t)(ti * p.tap_bytes);
-        for (int kc = 0; kc < p.nchunks; kc += 2) {
-          const uint64_t bdesc = ptx::umma_desc(b_tap + (uint32_t)kc * b_kstride, b_lbo, b_sbo);
-          for (int mt = 0; mt < p.MT; ++mt) {
-            const uint64_t adesc =
-                ptx::umma_desc(a_tap + (uint32_t)kc * chunk_bytes + (uint32_t)(mt * kTileM) * 16u, a_lbo, a_sbo);
-            ptx::umma_bf16(tmem_base + (uint32_t)(mt * p.Cout), adesc, bdesc, idesc, first ? 0u : 1u);
+      DBG(2)
+      if (resident) {
+        ptx::mbar_wait(bars + kBarWFull, 0);
+        ptx::tc_fence_after();
+        DBG(3)
+        for (int mt = 0; mt < MT; ++mt) {
+          const uint32_t d_tmem = tmem_base + (uint32_t)(mt * Cout);
+          uint32_t acc = 0u;
+          uint32_t b_lo = wring16;
+          for (int t = 0; t < ntaps; ++t) {
+            const ConvTapDev tp = p.tap[t];
+            uint32_t a_lo = slab16 + (uint32_t)(tp.src * p.nchunks) * chunk16 +
+                            (uint32_t)(p.halo_lo + tp.off + mt * kTileM);
+            for (int k = 0; k < KC2; ++k) {
+              ptx::umma_bf16(d_tmem, a_hi | a_lo, b_hi | b_lo, idesc, acc);
+              acc = 1u;
+              a_lo += a_kstep;
+              b_lo += b_kstep;
+            }
           }
-          first = false;
+          ptx::umma_commit(bars + kBarAcc + mt);
+        }
+      } else {
+        uint32_t acc = 0u;
+        for (int st = 0; st < p.nstages; ++st) {
+          const int slot = st % p.NS;
+          ptx::mbar_wait(bars + kBarWFull + slot, (st / p.NS) & 1);
+          ptx::tc_fence_after();
+          if (st == 0) DBG(3)
+          const int ntap = min(p.tps, ntaps - st * p.tps);
+          for (int ti = 0; ti < ntap; ++ti) {
+            const ConvTapDev tp = p.tap[st * p.tps + ti];
+            uint32_t a_lo = slab16 + (uint32_t)(tp.src * p.nchunks) * chunk16 + (uint32_t)(p.halo_lo + tp.off);
+            uint32_t b_lo = wring16 + (uint32_t)slot * stage16 + (uint32_t)ti * tap16;
+            for (int k = 0; k < KC2; ++k) {
+              for (int mt = 0; mt < MT; ++mt)
+                ptx::umma_bf16(tmem_base + (uint32_t)(mt * Cout), a_hi | (a_lo + (uint32_t)(mt * kTileM)), b_hi | b_lo,
+                               idesc, acc);
+              acc = 1u;
+              a_lo += a_kstep;
+              b_lo += b_kstep;
+            }
+          }
+          ptx::umma_commit(bars + kBarWEmpty + slot);  // slot reusable once these MMAs are done
+        }
+        for (int mt = 0; mt < MT; ++mt) ptx::umma_commit(bars + kBarAcc + mt);
+      }
+      DBG(4)
+    }
+    __syncwarp();
+  }
+
+  // ---- epilogue: warp w owns TMEM lanes [32w, 32w+32); accumulator tiles are drained as they finish --
+  {
+    const ActView outv = g.out, auxv = g.aux;  // register copies (see epilogue_cols)
+    const long long out_plane_bytes = outv.plane * 16, aux_plane_bytes = auxv.plane * 16;
+    const int aux_nchunks = g.aux_nchunks;
+    const int Cout = p.Cout, MT = p.MT, H = p.H, W = p.W, Wp = p.Wp, Pimg = p.Pimg, body = (int)p.body;
+    for (int mt = 0; mt < MT; ++mt) {
+      const int f = tile_start + mt * kTileM + warp * 32 + lane;
+      const bool in_body = f < body;
+      int n = 0, h = 0, w = 0;
+      if (in_body) {
+        n = f / Pimg;
+        const int rem = f - n * Pimg;
+        h = rem / Wp;
+        w = rem - h * Wp;
+      }
+      const bool valid = in_body && (h < H) && (w < W);
+      const bool do_store = in_body && (valid || outv.layout == LAY_P8);
+      char* out_addr0 = view_addr<__nv_bfloat16>(outv, 0, f, n, h, w);
+      const char* aux_addr0 = view_addr<__nv_bfloat16>(auxv, 0, f, n, h, w);
+      ptx::mbar_wait(bars + kBarAcc + mt, 0);
+      ptx::tc_fence_after();
+      if (mt == 0 && threadIdx.x == 64) DBG(5)
+      const uint32_t trow = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(mt * Cout);
+      if (Cout >= 32) {
+        for (int c0 = 0; c0 < Cout; c0 += 32) {
+          uint32_t r[32];
+          ptx::tmem_ld32_issue(trow + (uint32_t)c0, r);
+          ptx::tmem_wait32(r);
+          if (mt == 0 && c0 == 0 && threadIdx.x == 64) DBG(7)
+          if (do_store) {
+#pragma unroll
+            for (int hlf = 0; hlf < 2; ++hlf) {
+              float v[16];
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[hlf * 16 + j]);
+              epilogue_cols<__nv_bfloat16, EPI>(bias_s, c0 + hlf * 16, valid, v, aux_addr0, aux_plane_bytes,
+                                                aux_nchunks, out_addr0, out_plane_bytes);
+            }
+          }
+          if (mt == 0 && c0 == 0 && threadIdx.x == 64) DBG(8)
+        }
+      } else {
+        uint32_t r[16];
+        ptx::tmem_ld16_issue(trow, r);
+        ptx::tmem_wait16(r);
+        if (do_store) {
+          float v[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+          epilogue_cols<__nv_bfloat16, EPI>(bias_s, 0, valid, v, aux_addr0, aux_plane_bytes, aux_nchunks, out_addr0,
+                                            out_plane_bytes);
         }
       }
-      ptx::umma_commit(bar_wempty + slot);  // stage may be refilled once these MMAs have read it
-    }
-    ptx::umma_commit(bar_acc);
-    DBG(4)
-  }
-  __syncwarp();
-
-  // ---- epilogue: warp w owns TMEM lanes [32w, 32w+32) ----------------------------------------
-  ptx::mbar_wait(bar_acc, 0);
-  ptx::tc_fence_after();
-  if (threadIdx.x == 64) DBG(5)
-  for (int mt = 0; mt < p.MT; ++mt) {
-    const int f = tile_start + mt * kTileM + warp * 32 + lane;
-    for (int c0 = 0; c0 < p.Cout; c0 += 16) {
-      float v[16];
-      ptx::tmem_ld16(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(mt * p.Cout + c0), v);
-      epilogue16<__nv_bfloat16>(p, g, f, c0, v);
     }
   }
+  if (threadIdx.x == 64) DBG(9)
   ptx::tc_fence_before();
   __syncthreads();
   if (threadIdx.x == 64) DBG(6)
@@ -196,6 +324,8 @@ constexpr int kFp32CoutBlock = 32;
 
 __global__ void __launch_bounds__(128) conv_fp32_kernel(const __grid_constant__ ConvParams p) {
   extern __shared__ __align__(16) float ws[];  // [K_tap][32]
+  ptx::pdl_launch_dependents();
+  ptx::pdl_grid_wait();
   const ConvGroupDev& g = p.g[blockIdx.y];
   const int f = blockIdx.x * 128 + threadIdx.x;
   const int cb = blockIdx.z * kFp32CoutBlock;
@@ -243,22 +373,42 @@ size_t conv_umma_smem_bytes(const ConvParams& p) {
   return kSmemHeader + slab + (size_t)p.NS * p.tps * p.tap_bytes;
 }
 
-cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream) {
+template <typename K, typename P>
+static cudaError_t launch_ex(K kernel, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, bool pdl, const P& params) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid, cfg.blockDim = block, cfg.dynamicSmemBytes = smem, cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr, cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, params);
+}
+
+cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream, bool pdl) {
   if (precision == 0) {
     size_t smem = conv_umma_smem_bytes(p);
     static size_t configured = 0;
     if (smem > configured) {
-      cudaError_t e = cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaError_t e = cudaSuccess;
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_kernel<EPI_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_kernel<EPI_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_kernel<EPI_ADD_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_kernel<EPI_SIGMOID_MUL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e != cudaSuccess) return e;
       configured = smem;
     }
     int tile = p.MT * kTileM;
     dim3 grid((unsigned)((p.body + tile - 1) / tile), p.ngroups, 1);
-    conv_umma_kernel<<<grid, 128, smem, stream>>>(p);
+    switch (p.epi) {
+      case EPI_NONE: return launch_ex(conv_umma_kernel<EPI_NONE>, grid, dim3(128), smem, stream, pdl, p);
+      case EPI_RELU: return launch_ex(conv_umma_kernel<EPI_RELU>, grid, dim3(128), smem, stream, pdl, p);
+      case EPI_ADD_RELU: return launch_ex(conv_umma_kernel<EPI_ADD_RELU>, grid, dim3(128), smem, stream, pdl, p);
+      default: return launch_ex(conv_umma_kernel<EPI_SIGMOID_MUL>, grid, dim3(128), smem, stream, pdl, p);
+    }
   } else {
     size_t smem = (size_t)p.nchunks * 8 * kFp32CoutBlock * sizeof(float);
     dim3 grid((unsigned)((p.body + 127) / 128), p.ngroups, (p.Cout + kFp32CoutBlock - 1) / kFp32CoutBlock);
-    conv_fp32_kernel<<<grid, 128, smem, stream>>>(p);
+    return launch_ex(conv_fp32_kernel, grid, dim3(128), smem, stream, pdl, p);
   }
   return cudaGetLastError();
 }
@@ -337,6 +487,74 @@ float umma_selftest(int n_cols, int row_shift, int swap) {
     return -3.f;
   }
   return h;
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// tensor-pipe rate probe: `reps` x 16 back-to-back 128 x N x 16 MMAs on fixed operands.
+// mode 0: interleaved (no swizzle) descriptors as used by the conv kernel; mode 1: 128B-swizzle descriptors;
+// mode 2: interleaved, descriptor start address advanced every MMA (register arithmetic in the loop).
+// Returns SM cycles per MMA as seen by the issuing thread (issue start -> commit observed).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) umma_rate_kernel(int N, int mode, int reps, float* out) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
+  uint32_t* slot = reinterpret_cast<uint32_t*>(smem + 64);
+  uint8_t* A = smem + 1024;            // 16 KB region
+  uint8_t* B = smem + 1024 + 16384;    // 16 KB region
+  for (int i = threadIdx.x; i < 8192; i += 128) reinterpret_cast<uint32_t*>(A)[i] = 0x3c003c00u;  // both regions
+  const int warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) {
+    ptx::mbar_init(bar, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 1) ptx::tmem_alloc(slot, 256);
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *slot;
+  if (threadIdx.x == 32) {
+    const uint32_t idesc = ptx::umma_idesc_bf16(128, N, 0, 0);
+    uint64_t ad, bd;
+    if (mode == 1) {  // SWIZZLE_128B K-major: SBO = 1024, layout type 2
+      ad = ptx::umma_desc(ptx::smem_u32(A), 16, 1024) | (2ull << 61);
+      bd = ptx::umma_desc(ptx::smem_u32(B), 16, 1024) | (2ull << 61);
+    } else {
+      ad = ptx::umma_desc(ptx::smem_u32(A), 4096, 128);
+      bd = ptx::umma_desc(ptx::smem_u32(B), (uint32_t)N * 16u, 128);
+    }
+    const long long t0 = clock64();
+    for (int r = 0; r < reps; ++r) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        uint64_t a2 = ad;
+        if (mode == 2) a2 = ad + (uint64_t)((r * 16 + i) & 7);
+        ptx::umma_bf16(tmem, a2, bd, idesc, 1u);
+      }
+    }
+    const long long t1 = clock64();
+    ptx::umma_commit(bar);
+    ptx::mbar_wait(bar, 0);
+    const long long t2 = clock64();
+    out[0] = (float)(t2 - t0) / (float)(reps * 16);
+    out[1] = (float)(t1 - t0) / (float)(reps * 16);
+  }
+  __syncthreads();
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem, 256);
+}
+
+int umma_rate(int n_cols, int mode, int reps, float* host_out2) {
+  float* d = nullptr;
+  if (cudaMalloc(&d, 2 * sizeof(float)) != cudaSuccess) return -2;
+  size_t smem = 1024 + 32768;
+  umma_rate_kernel<<<1, 128, smem>>>(n_cols, mode, reps, d);
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e == cudaSuccess) e = cudaMemcpy(host_out2, d, 2 * sizeof(float), cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  return e == cudaSuccess ? 0 : -2;
 }
 
 }  // namespace mtldas

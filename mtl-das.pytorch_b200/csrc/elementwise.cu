@@ -6,64 +6,97 @@
 
 #include "gran.cuh"
 #include "kernels.h"
+#include "ptx.cuh"
 
 namespace mtldas {
+
+template <typename K, typename P>
+static cudaError_t launch_ex(K kernel, dim3 grid, dim3 block, cudaStream_t stream, bool pdl, const P& params) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid, cfg.blockDim = block, cfg.dynamicSmemBytes = 0, cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr, cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, params);
+}
 
 // ---------------------------------------------------------------------------------------------
 // stem: Conv2d(1,16,7x7,stride 3,pad 2,bias=False)+BN(eval, folded)+ReLU -- modelA_MTL.py:73-77,128
 // thread = one flattened output position, 16 output channels in registers.
 // ---------------------------------------------------------------------------------------------
+// thread = two horizontally adjacent output positions (Wp = 84 is even, so a pair never straddles a row):
+// the 7x10 input window is read once for both, every weight float4 fetched from shared memory feeds two
+// positions, and the FMAs are issued as packed fma.rn.f32x2 (two channels per instruction).
 template <typename T>
 __global__ void __launch_bounds__(128) stem_kernel(const __grid_constant__ StemParams p) {
-  __shared__ float ws[49 * 16];
+  __shared__ __align__(16) float ws[49 * 16];
   __shared__ float bs[16];
+  ptx::pdl_launch_dependents();
   for (int i = threadIdx.x; i < 49 * 16; i += 128) ws[i] = p.w[i];
   if (threadIdx.x < 16) bs[threadIdx.x] = p.bias[threadIdx.x];
   __syncthreads();
-  const int f = blockIdx.x * 128 + threadIdx.x;
+  ptx::pdl_grid_wait();  // the output tensor may still be read by the previous pass's kernels
+  const int f = (blockIdx.x * 128 + threadIdx.x) * 2;
   if (f >= p.body) return;
   const int n = f / p.Pimg;
   const int rem = f - n * p.Pimg;
   const int h = rem / p.Wp, w = rem - (rem / p.Wp) * p.Wp;
-  float acc[16];
+  float2 acc[2][8];
 #pragma unroll
-  for (int j = 0; j < 16; ++j) acc[j] = 0.f;
-  if (h < p.H && w < p.W) {
+  for (int q = 0; q < 8; ++q) acc[0][q] = acc[1][q] = make_float2(0.f, 0.f);
+  const bool row_ok = h < p.H;
+  const bool v0 = row_ok && w < p.W, v1 = row_ok && (w + 1) < p.W;
+  if (v0) {
     const float* xin = p.x + (size_t)n * p.Hin * p.Win;
+    const int ix0 = 3 * w - 2;
 #pragma unroll 1
     for (int r = 0; r < 7; ++r) {
       const int iy = 3 * h - 2 + r;
       if (iy < 0 || iy >= p.Hin) continue;
+      const float* row = xin + iy * p.Win;
+      float xv[10];
+#pragma unroll
+      for (int s = 0; s < 10; ++s) {
+        const int ix = ix0 + s;
+        xv[s] = (ix >= 0 && ix < p.Win) ? __ldg(row + ix) : 0.f;
+      }
 #pragma unroll
       for (int s = 0; s < 7; ++s) {
-        const int ix = 3 * w - 2 + s;
-        if (ix < 0 || ix >= p.Win) continue;
-        const float xv = __ldg(xin + iy * p.Win + ix);
         const float4* wr = reinterpret_cast<const float4*>(ws + (r * 7 + s) * 16);
+        const float2 xa = make_float2(xv[s], xv[s]), xb = make_float2(xv[s + 3], xv[s + 3]);
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          float4 w4 = wr[q];
-          acc[4 * q + 0] = fmaf(xv, w4.x, acc[4 * q + 0]);
-          acc[4 * q + 1] = fmaf(xv, w4.y, acc[4 * q + 1]);
-          acc[4 * q + 2] = fmaf(xv, w4.z, acc[4 * q + 2]);
-          acc[4 * q + 3] = fmaf(xv, w4.w, acc[4 * q + 3]);
+          const float4 w4 = wr[q];
+          const float2 wlo = make_float2(w4.x, w4.y), whi = make_float2(w4.z, w4.w);
+          acc[0][2 * q] = __ffma2_rn(xa, wlo, acc[0][2 * q]);
+          acc[0][2 * q + 1] = __ffma2_rn(xa, whi, acc[0][2 * q + 1]);
+          acc[1][2 * q] = __ffma2_rn(xb, wlo, acc[1][2 * q]);
+          acc[1][2 * q + 1] = __ffma2_rn(xb, whi, acc[1][2 * q + 1]);
         }
       }
     }
-#pragma unroll
-    for (int j = 0; j < 16; ++j) acc[j] = fmaxf(acc[j] + bs[j], 0.f);
   }
-  store8<T>(view_addr<T>(p.out, 0, f, n, h, w), acc);
-  store8<T>(view_addr<T>(p.out, 1, f, n, h, w), acc + 8);
+#pragma unroll
+  for (int pos = 0; pos < 2; ++pos) {
+    const bool valid = pos == 0 ? v0 : v1;
+    float o[16];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      o[2 * q] = valid ? fmaxf(acc[pos][q].x + bs[2 * q], 0.f) : 0.f;
+      o[2 * q + 1] = valid ? fmaxf(acc[pos][q].y + bs[2 * q + 1], 0.f) : 0.f;
+    }
+    if (f + pos < p.body) {
+      store8<T>(view_addr<T>(p.out, 0, f + pos, n, h, w + pos), o);
+      store8<T>(view_addr<T>(p.out, 1, f + pos, n, h, w + pos), o + 8);
+    }
+  }
 }
 
-cudaError_t launch_stem(const StemParams& p, int precision, cudaStream_t stream) {
-  unsigned grid = (unsigned)((p.body + 127) / 128);
-  if (precision == 0)
-    stem_kernel<__nv_bfloat16><<<grid, 128, 0, stream>>>(p);
-  else
-    stem_kernel<float><<<grid, 128, 0, stream>>>(p);
-  return cudaGetLastError();
+cudaError_t launch_stem(const StemParams& p, int precision, cudaStream_t stream, bool pdl) {
+  unsigned grid = (unsigned)((p.body + 255) / 256);
+  if (precision == 0) return launch_ex(stem_kernel<__nv_bfloat16>, dim3(grid), dim3(128), stream, pdl, p);
+  return launch_ex(stem_kernel<float>, dim3(grid), dim3(128), stream, pdl, p);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -72,6 +105,8 @@ cudaError_t launch_stem(const StemParams& p, int precision, cudaStream_t stream)
 // ---------------------------------------------------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(256) pool_kernel(const __grid_constant__ PoolParams p) {
+  ptx::pdl_launch_dependents();
+  ptx::pdl_grid_wait();
   const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
   const long long total = p.body_o * p.nchunks;
   if (idx >= total) return;
@@ -104,14 +139,11 @@ __global__ void __launch_bounds__(256) pool_kernel(const __grid_constant__ PoolP
   store8<T>(view_addr<T>(p.out, c, fo, n, ho, wo), m);
 }
 
-cudaError_t launch_pool(const PoolParams& p, int precision, cudaStream_t stream) {
+cudaError_t launch_pool(const PoolParams& p, int precision, cudaStream_t stream, bool pdl) {
   long long total = p.body_o * p.nchunks;
   unsigned grid = (unsigned)((total + 255) / 256);
-  if (precision == 0)
-    pool_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(p);
-  else
-    pool_kernel<float><<<grid, 256, 0, stream>>>(p);
-  return cudaGetLastError();
+  if (precision == 0) return launch_ex(pool_kernel<__nv_bfloat16>, dim3(grid), dim3(256), stream, pdl, p);
+  return launch_ex(pool_kernel<float>, dim3(grid), dim3(256), stream, pdl, p);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -123,6 +155,8 @@ template <typename T>
 __global__ void __launch_bounds__(128) head_kernel(const __grid_constant__ HeadParams p) {
   __shared__ float part[8][128];
   __shared__ float z[16];
+  ptx::pdl_launch_dependents();
+  ptx::pdl_grid_wait();
   const int n = blockIdx.x;
   const int c = threadIdx.x & 15, pl = threadIdx.x >> 4;
   float s[8];
@@ -155,12 +189,9 @@ __global__ void __launch_bounds__(128) head_kernel(const __grid_constant__ HeadP
   }
 }
 
-cudaError_t launch_head(const HeadParams& p, int precision, cudaStream_t stream) {
-  if (precision == 0)
-    head_kernel<__nv_bfloat16><<<p.nb, 128, 0, stream>>>(p);
-  else
-    head_kernel<float><<<p.nb, 128, 0, stream>>>(p);
-  return cudaGetLastError();
+cudaError_t launch_head(const HeadParams& p, int precision, cudaStream_t stream, bool pdl) {
+  if (precision == 0) return launch_ex(head_kernel<__nv_bfloat16>, dim3(p.nb), dim3(128), stream, pdl, p);
+  return launch_ex(head_kernel<float>, dim3(p.nb), dim3(128), stream, pdl, p);
 }
 
 // ---------------------------------------------------------------------------------------------

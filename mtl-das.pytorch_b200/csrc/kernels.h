@@ -7,13 +7,14 @@
 namespace mtldas {
 
 // precision: 0 = bf16 (tcgen05), 1 = fp32 (CUDA cores)
-cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream);
+cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream, bool pdl = false);
 size_t conv_umma_smem_bytes(const ConvParams& p);
 float umma_selftest(int n_cols, int row_shift, int swap);
+int umma_rate(int n_cols, int mode, int reps, float* host_out2);
 
-cudaError_t launch_stem(const StemParams& p, int precision, cudaStream_t stream);
-cudaError_t launch_pool(const PoolParams& p, int precision, cudaStream_t stream);
-cudaError_t launch_head(const HeadParams& p, int precision, cudaStream_t stream);
+cudaError_t launch_stem(const StemParams& p, int precision, cudaStream_t stream, bool pdl = false);
+cudaError_t launch_pool(const PoolParams& p, int precision, cudaStream_t stream, bool pdl = false);
+cudaError_t launch_head(const HeadParams& p, int precision, cudaStream_t stream, bool pdl = false);
 cudaError_t launch_pack(const PackParams& p, cudaStream_t stream);
 
 // layout conversion (tests, debugging, and the autograd boundary): fp32 NCHW <-> P8 / P8S2 views

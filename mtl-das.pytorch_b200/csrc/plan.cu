@@ -455,8 +455,13 @@ int plan_pack_eval(Plan& p, const void* const* state, cudaStream_t stream) {
 // forward (eval)
 // ---------------------------------------------------------------------------------------------
 static int run_pass(Plan& p, const float* x, int nb, float* out0, float* out1, cudaStream_t stream,
-                    std::vector<cudaEvent_t>* evs = nullptr) {
+                    std::vector<cudaEvent_t>* evs = nullptr, bool first_pass = true) {
+  bool first_op = true;
   for (const Op& op : p.program) {
+    // programmatic dependent launch for everything but the first kernel of a forward (what runs before it on the
+    // stream is not ours); not under the per-launch event instrumentation
+    const bool pdl = p.use_pdl && !evs && !(first_pass && first_op);
+    first_op = false;
     if (evs) {
       cudaEvent_t e;
       CK(cudaEventCreate(&e));
@@ -472,10 +477,10 @@ static int run_pass(Plan& p, const float* x, int nb, float* out0, float* out1, c
       q.out = p.view(p.stem_out, 0);
       q.Hin = kPatchH, q.Win = kPatchW, q.H = t.H, q.W = t.W, q.Wp = t.Wp, q.Pimg = t.Pimg;
       q.body = (long long)nb * t.Pimg;
-      CK(launch_stem(q, p.precision, stream));
+      CK(launch_stem(q, p.precision, stream, pdl));
     } else if (op.kind == 1) {
       ConvParams q = p.conv_params(p.convs[op.index], nb);
-      CK(launch_conv(q, p.precision, stream));
+      CK(launch_conv(q, p.precision, stream, pdl));
     } else if (op.kind == 2) {
       const PoolOpHost& po = p.pools[op.index];
       const TensorInfo& ti = p.tensors[po.in_tensor];
@@ -486,7 +491,7 @@ static int run_pass(Plan& p, const float* x, int nb, float* out0, float* out1, c
       q.H = ti.H, q.W = ti.W, q.Wp = ti.Wp, q.Pimg = ti.Pimg;
       q.Ho = to.H, q.Wo = to.W, q.Wpo = to.Wp, q.Pimgo = to.Pimg;
       q.body_o = (long long)nb * to.Pimg;
-      CK(launch_pool(q, p.precision, stream));
+      CK(launch_pool(q, p.precision, stream, pdl));
     } else {
       const HeadOpHost& h = p.heads[op.index];
       const TensorInfo& t = p.tensors[h.in_tensor];
@@ -499,7 +504,7 @@ static int run_pass(Plan& p, const float* x, int nb, float* out0, float* out1, c
         set_error("forward: output %d is NULL", h.out_index);
         return -1;
       }
-      CK(launch_head(q, p.precision, stream));
+      CK(launch_head(q, p.precision, stream, pdl));
     }
     ++p.last_launches;
     if (evs) {
@@ -546,19 +551,79 @@ int plan_profile_eval(Plan& p, const float* x, int n, float* out0, float* out1, 
   return rc;
 }
 
-int plan_forward_eval(Plan& p, const float* x, int n, float* out0, float* out1, cudaStream_t stream) {
-  if (!p.ws || !p.packed) {
-    set_error("forward_eval: bind a workspace and pack weights first");
-    return -3;
-  }
+static int forward_eager(Plan& p, const float* x, int n, float* out0, float* out1, cudaStream_t stream) {
   p.last_launches = 0;
   int c0 = p.heads[0].classes, c1 = p.heads.size() > 1 ? p.heads[1].classes : 0;
   for (int s = 0; s < n; s += p.mb) {
     int nb = std::min(p.mb, n - s);
     int rc = run_pass(p, x + (size_t)s * kPatchH * kPatchW, nb, out0 + (size_t)s * c0,
-                      out1 ? out1 + (size_t)s * c1 : nullptr, stream);
+                      out1 ? out1 + (size_t)s * c1 : nullptr, stream, nullptr, s == 0);
     if (rc) return rc;
   }
+  return 0;
+}
+
+Plan::~Plan() {
+  for (auto& g : graphs)
+    if (g.exec) cudaGraphExecDestroy(g.exec);
+  if (cap_stream) cudaStreamDestroy(cap_stream);
+}
+
+// The layer program is ~36 launches per micro-batch pass (576 for a 4096 batch): replaying it as one CUDA graph
+// removes the per-launch host cost.  First use of a buffer set runs eagerly, the second is captured, later ones replay.
+int plan_forward_eval(Plan& p, const float* x, int n, float* out0, float* out1, cudaStream_t stream) {
+  if (!p.ws || !p.packed) {
+    set_error("forward_eval: bind a workspace and pack weights first");
+    return -3;
+  }
+  if (!p.use_graphs) return forward_eager(p, x, n, out0, out1, stream);
+  Plan::GraphEntry* e = nullptr;
+  for (auto& g : p.graphs)
+    if (g.x == x && g.n == n && g.o0 == out0 && g.o1 == out1) e = &g;
+  if (!e) {
+    if (p.graphs.size() >= 8) {  // evict the least recently used entry
+      size_t victim = 0;
+      for (size_t i = 1; i < p.graphs.size(); ++i)
+        if (p.graphs[i].stamp < p.graphs[victim].stamp) victim = i;
+      if (p.graphs[victim].exec) cudaGraphExecDestroy(p.graphs[victim].exec);
+      p.graphs.erase(p.graphs.begin() + victim);
+    }
+    p.graphs.push_back(Plan::GraphEntry{x, n, out0, out1, nullptr, 0, 0, 0});
+    e = &p.graphs.back();
+  }
+  e->stamp = ++p.graph_clock;
+  e->uses++;
+  if (e->exec) {
+    CK(cudaGraphLaunch(e->exec, stream));
+    p.last_launches = e->launches;
+    return 0;
+  }
+  if (e->uses < 2) return forward_eager(p, x, n, out0, out1, stream);
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream, &st) != cudaSuccess) cudaGetLastError();
+  if (st != cudaStreamCaptureStatusNone) return forward_eager(p, x, n, out0, out1, stream);  // caller is capturing
+  // capture on a private stream (the caller's may be the legacy default stream, which cannot be captured);
+  // the instantiated graph is then launched on the caller's stream.
+  if (!p.cap_stream) CK(cudaStreamCreateWithFlags(&p.cap_stream, cudaStreamNonBlocking));
+  CK(cudaStreamBeginCapture(p.cap_stream, cudaStreamCaptureModeThreadLocal));
+  int rc = forward_eager(p, x, n, out0, out1, p.cap_stream);
+  cudaGraph_t graph = nullptr;
+  cudaError_t ce = cudaStreamEndCapture(p.cap_stream, &graph);
+  if (rc || ce != cudaSuccess) {
+    if (graph) cudaGraphDestroy(graph);
+    cudaGetLastError();
+    if (!rc) set_error("graph capture failed: %s", cudaGetErrorString(ce));
+    return rc ? rc : -2;
+  }
+  e->launches = p.last_launches;
+  ce = cudaGraphInstantiate(&e->exec, graph, 0);
+  cudaGraphDestroy(graph);
+  if (ce != cudaSuccess) {
+    e->exec = nullptr;
+    set_error("graph instantiate failed: %s", cudaGetErrorString(ce));
+    return -2;
+  }
+  CK(cudaGraphLaunch(e->exec, stream));
   return 0;
 }
 
@@ -651,28 +716,30 @@ int single_conv(const float* x, const float* x2, const float* weight, const floa
       // diagnostics: per-CTA timeline of a warm (second) launch
       int ntile = (int)((cp.body + cp.MT * kTileM - 1) / (cp.MT * kTileM));
       long long* dbg = nullptr;
-      CKB(cudaMalloc(&dbg, (size_t)ntile * 8 * sizeof(long long)));
-      CKB(cudaMemset(dbg, 0, (size_t)ntile * 8 * sizeof(long long)));
+      CKB(cudaMalloc(&dbg, (size_t)ntile * 16 * sizeof(long long)));
+      CKB(cudaMemset(dbg, 0, (size_t)ntile * 16 * sizeof(long long)));
       CKB(launch_conv(cp, precision, 0));
       CKB(cudaDeviceSynchronize());
       cp.dbg = dbg;
       CKB(launch_conv(cp, precision, 0));
       CKB(cudaDeviceSynchronize());
-      std::vector<long long> h((size_t)ntile * 8);
+      std::vector<long long> h((size_t)ntile * 16);
       CKB(cudaMemcpy(h.data(), dbg, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
       cudaFree(dbg);
       long long t0 = h[0], t1 = 0;
       for (int i = 0; i < ntile; ++i) {
-        t0 = std::min(t0, h[(size_t)i * 8]);
-        t1 = std::max(t1, h[(size_t)i * 8]);
+        t0 = std::min(t0, h[(size_t)i * 16]);
+        t1 = std::max(t1, h[(size_t)i * 16]);
       }
       fprintf(stderr, "[convdbg] tiles=%d MT=%d NS=%d tps=%d smem=%zu last CTA start +%lld ns\n", ntile, cp.MT, cp.NS,
               cp.tps, conv_umma_smem_bytes(cp), t1 - t0);
       for (int i = 0; i < ntile; i += std::max(1, ntile / 6)) {
-        const long long* r = &h[(size_t)i * 8];
+        const long long* r = &h[(size_t)i * 16];
         fprintf(stderr,
-                "[convdbg] cta %4d start+%lld ns | clk: setup %lld slab %lld w0 %lld issued %lld acc %lld epi %lld\n", i,
-                r[0] - t0, r[2] - r[1], r[3] - r[2], r[4] - r[3], r[5] - r[4], r[6] - r[5], r[7] - r[6]);
+                "[convdbg] cta %4d start+%lld ns | clk: setup %lld slab %lld w0 %lld issued %lld acc %lld epi %lld | "
+                "detail: first-ld %lld first-cols %lld loop-end %lld final-sync %lld\n",
+                i, r[0] - t0, r[2] - r[1], r[3] - r[2], r[4] - r[3], r[5] - r[4], r[6] - r[5], r[7] - r[6], r[8] - r[6],
+                r[9] - r[8], r[10] - r[6], r[7] - r[10]);
       }
       cp.dbg = nullptr;
     }

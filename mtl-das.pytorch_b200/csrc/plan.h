@@ -83,6 +83,21 @@ struct Plan {
   bool packed = false;
   int last_launches = 0;
   int swap_desc = 0;
+  // CUDA graphs of whole forwards, keyed by the caller's buffers (replayed when the same buffers come back)
+  struct GraphEntry {
+    const float* x;
+    int n;
+    float *o0, *o1;
+    cudaGraphExec_t exec;
+    int uses, launches;
+    unsigned long long stamp;
+  };
+  std::vector<GraphEntry> graphs;
+  unsigned long long graph_clock = 0;
+  int use_graphs = 1;
+  int use_pdl = 1;
+  cudaStream_t cap_stream = nullptr;
+  ~Plan();
 
   int find_tensor(const std::string& n) const;
   ActView view(int tensor, int chunk0) const;

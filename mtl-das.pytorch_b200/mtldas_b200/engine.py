@@ -75,14 +75,15 @@ class EvalPlan:
             check(lib.mtldas_plan_pack_eval(self._h, arr, self.n_state, _stream_ptr(self.device)), "pack_eval")
         self._state_keepalive = tensors
 
-    def forward(self, x):
+    def forward(self, x, outs=None):
         if not x.is_cuda:
             raise MtldasError("input must be a CUDA tensor; there is no CPU fallback")
         if x.dim() != 4 or tuple(x.shape[1:]) != (1, 100, 250):
             raise ValueError(f"expected [N,1,100,250], got {tuple(x.shape)}")
         x = x.contiguous().float()
         n = x.shape[0]
-        outs = [torch.empty((n, c), dtype=torch.float32, device=x.device) for c in self.classes]
+        if outs is None:
+            outs = [torch.empty((n, c), dtype=torch.float32, device=x.device) for c in self.classes]
         with torch.cuda.device(self.device):
             check(lib.mtldas_plan_forward_eval(self._h, ctypes.c_void_p(x.data_ptr()), n,
                                                ctypes.c_void_p(outs[0].data_ptr()),

@@ -72,7 +72,7 @@ class _DasNet(nn.Module):
         self._plans = {}
         self._packed_sig = {}
         self.precision = os.environ.get("MTLDAS_PRECISION", "bf16")
-        self.micro_batch = int(os.environ.get("MTLDAS_MICRO_BATCH", "256"))
+        self.micro_batch = int(os.environ.get("MTLDAS_MICRO_BATCH", "512"))
 
     # ---- engine plumbing -------------------------------------------------------------------
     def _kind(self):
