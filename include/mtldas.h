@@ -123,6 +123,21 @@ MTLDAS_API int mtldas_conv2d_nchw(const float* dev_x, const float* dev_x2, const
                        const float* dev_aux, float* dev_out, int n, int cin, int cin2, int h, int w, int cout,
                        int ksize, int stride, int epilogue, int precision, int aux_phase_split);
 
+/* single fused convolution WITHOUT any allocation -----------------------------------------------
+ * No counterpart in the reference: this exists for hosts of this library that cannot allocate device memory --
+ * a DAS acquisition / streaming loop that must never hit the device-wide synchronisation of cudaMalloc/cudaFree,
+ * or a process whose GPU memory already belongs to one pool (e.g. PyTorch's caching allocator or a start-up arena).
+ * Same arguments and results as mtldas_conv2d_nchw plus a stream; asynchronous on `stream` (no synchronise).
+ * Its temporaries live in a fixed 32 MiB array inside the library image (held by every GPU that loads the
+ * library, until exit); a call that needs more returns MTLDAS_ERR_UNSUPPORTED with the required size in
+ * mtldas_last_error() and allocates nothing.  The first call on a device looks the array's device address up
+ * (cudaGetSymbolAddress) -- make that first call before any stream capture.  All calls share the array: the part a
+ * call uses is cleared first, and calls whose GPU work overlaps (other streams / threads) race and must be serialised. */
+MTLDAS_API int mtldas_conv2d_nchw_static(const float* dev_x, const float* dev_x2, const float* dev_weight,
+                                         const float* dev_bias, const float* dev_aux, float* dev_out, int n, int cin,
+                                         int cin2, int h, int w, int cout, int ksize, int stride, int epilogue,
+                                         int precision, int aux_phase_split, void* stream);
+
 /* tcgen05 descriptor self-test: runs one 128xNx16 UMMA on known operands under the descriptor
  * conventions the library uses and returns the max abs error (or <0 on error). */
 MTLDAS_API float mtldas_umma_selftest(int n_cols, int row_shift, int swap_lbo_sbo);

@@ -40,6 +40,7 @@ def _load():
         "mtldas_plan_last_launch_count": (ci, [vp]),
         "mtldas_plan_read_tensor": (ci, [vp, c.c_char_p, ci, vp, vp]),
         "mtldas_conv2d_nchw": (ci, [vp, vp, vp, vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, ci, ci, ci, ci]),
+        "mtldas_conv2d_nchw_static": (ci, [vp, vp, vp, vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, ci, ci, ci, ci, vp]),
         "mtldas_umma_selftest": (cf, [ci, ci, ci]),
         "mtldas_umma_rate": (ci, [ci, ci, ci, c.POINTER(cf)]),
     }

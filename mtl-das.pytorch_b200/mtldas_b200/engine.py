@@ -150,5 +150,30 @@ def conv2d_nchw(x, weight, bias=None, aux=None, x2=None, stride=1, epilogue=0, p
     return out
 
 
+def conv2d_nchw_static(x, weight, bias=None, aux=None, x2=None, stride=1, epilogue=0, precision="bf16",
+                       aux_phase_split=False, out=None):
+    """The same convolution through mtldas_conv2d_nchw_static: for callers that must not allocate GPU memory
+    (streaming loops that cannot take cudaMalloc's device-wide sync, processes whose memory belongs to a pool).
+    The library works in a fixed 32 MiB scratch inside its own image; pass `out` to avoid even the result
+    allocation.  Asynchronous on the current stream; calls share the scratch, so do not overlap them."""
+    _require_b200(x.device)
+    n, cin, h, w = x.shape
+    cout, cin_tot, k, _ = weight.shape
+    cin2 = x2.shape[1] if x2 is not None else 0
+    assert cin_tot == cin + cin2
+    ho, wo = (h, w) if stride == 1 else ((h + 1) // 2, (w + 1) // 2)
+    if out is None:
+        out = torch.empty((n, cout, ho, wo), dtype=torch.float32, device=x.device)
+    for t in (x, x2, weight, bias, aux, out):
+        if t is not None and not (t.is_contiguous() and t.dtype == torch.float32 and t.device == x.device):
+            raise MtldasError("conv2d_nchw_static needs contiguous fp32 tensors on one device (it converts nothing)")
+    p = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None  # noqa: E731
+    with torch.cuda.device(x.device):
+        check(lib.mtldas_conv2d_nchw_static(p(x), p(x2), p(weight), p(bias), p(aux), p(out), n, cin, cin2, h, w, cout,
+                                            k, stride, epilogue, PRECISIONS[precision], int(aux_phase_split),
+                                            _stream_ptr(x.device)), "conv2d_nchw_static")
+    return out
+
+
 def umma_selftest(n_cols=16, row_shift=0, swap=0):
     return float(lib.mtldas_umma_selftest(n_cols, row_shift, swap))
