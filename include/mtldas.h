@@ -138,6 +138,34 @@ MTLDAS_API int mtldas_conv2d_nchw_static(const float* dev_x, const float* dev_x2
                                          int cin2, int h, int w, int cout, int ksize, int stride, int epilogue,
                                          int precision, int aux_phase_split, void* stream);
 
+/* training: forward with batch-statistics BatchNorm + backward -------------------------------------
+ * Replaces the reference training step's model calls (utils.py:344,359,372-373):
+ *     model.train(); out1, out2 = model(x); ...; loss_balance.backward()
+ * i.e. MTL_Net.forward in train mode (modelA_MTL.py:127-174, nn.BatchNorm2d batch statistics, running-stat update
+ * with momentum 0.1) and the autograd backward of it.  The loss (NLLLoss per task, utils.py:139,361,367) stays
+ * outside: backward takes d(loss)/d(log-probs).
+ * `batch` is the largest batch the plan accepts (BatchNorm couples the batch, so one pass holds it all). */
+typedef struct mtldas_train mtldas_train;
+MTLDAS_API mtldas_train* mtldas_train_create(int model_kind, int batch, int precision);
+MTLDAS_API void mtldas_train_destroy(mtldas_train* t);
+MTLDAS_API int mtldas_train_num_state_entries(const mtldas_train* t);
+/* number of fp32 elements of the flat gradient buffer = sum of parameter sizes in named_parameters() order */
+MTLDAS_API size_t mtldas_train_num_params(const mtldas_train* t);
+MTLDAS_API size_t mtldas_train_workspace_bytes(const mtldas_train* t);
+MTLDAS_API int mtldas_train_bind_workspace(mtldas_train* t, void* dev_workspace, size_t bytes, void* stream);
+/* dev_state: the module's state_dict entries (reference order). Parameters are read; running_mean / running_var /
+ * num_batches_tracked are UPDATED IN PLACE as nn.BatchNorm2d does in train mode. Outputs as forward_eval. */
+MTLDAS_API int mtldas_train_forward(mtldas_train* t, const void* const* dev_state, int n_entries, const float* dev_x,
+                                    int n, float* dev_out0, float* dev_out1, void* stream);
+/* Gradients of the LAST train_forward: dev_dout0/1 = d loss / d log-probs ([n,16] / [n,2]); writes every parameter
+ * gradient into dev_flat_grads (fp32, named_parameters() order: conv weight, [conv bias], BN weight, BN bias per
+ * layer).  Pre-BatchNorm conv biases get exactly 0 (their gradient cancels). */
+MTLDAS_API int mtldas_train_backward(mtldas_train* t, const void* const* dev_state, int n_entries,
+                                     const float* dev_dout0, const float* dev_dout1, float* dev_flat_grads, void* stream);
+MTLDAS_API int mtldas_train_last_launch_count(const mtldas_train* t);
+MTLDAS_API int mtldas_train_read_tensor(mtldas_train* t, const char* name, int nb, float* dev_out_nchw, void* stream);
+MTLDAS_API size_t mtldas_train_describe(const mtldas_train* t, char* buf, size_t cap);
+
 /* tcgen05 descriptor self-test: runs one 128xNx16 UMMA on known operands under the descriptor
  * conventions the library uses and returns the max abs error (or <0 on error). */
 MTLDAS_API float mtldas_umma_selftest(int n_cols, int row_shift, int swap_lbo_sbo);

@@ -5,6 +5,7 @@
 #include "../../include/mtldas.h"
 #include "kernels.h"
 #include "plan.h"
+#include "train.h"
 
 using namespace mtldas;
 
@@ -181,6 +182,78 @@ float mtldas_umma_selftest(int n_cols, int row_shift, int swap_lbo_sbo) {
 
 int mtldas_umma_rate(int n_cols, int mode, int reps, float* host_out2) {
   return umma_rate(n_cols, mode, reps, host_out2);
+}
+
+struct mtldas_train {
+  TrainPlan* tp;
+};
+
+mtldas_train* mtldas_train_create(int model_kind, int batch, int precision) {
+  if (model_kind < 0 || model_kind > 2 || batch < 1 || batch > 1024 || precision < 0 || precision > 1) {
+    set_error("train_create: bad arguments (kind %d, batch %d, precision %d)", model_kind, batch, precision);
+    return nullptr;
+  }
+  mtldas_train* h = new mtldas_train();
+  h->tp = build_train_plan(model_kind, batch, precision);
+  return h;
+}
+void mtldas_train_destroy(mtldas_train* t) {
+  if (!t) return;
+  delete t->tp;
+  delete t;
+}
+int mtldas_train_num_state_entries(const mtldas_train* t) { return t ? (int)t->tp->p->state_keys.size() : -1; }
+size_t mtldas_train_num_params(const mtldas_train* t) { return t ? t->tp->n_params : 0; }
+size_t mtldas_train_workspace_bytes(const mtldas_train* t) { return t ? t->tp->p->ws_bytes : 0; }
+int mtldas_train_bind_workspace(mtldas_train* t, void* dev_workspace, size_t bytes, void* stream) {
+  if (!t || !dev_workspace || bytes < t->tp->p->ws_bytes || ((uintptr_t)dev_workspace & 255)) {
+    set_error("train_bind_workspace: need %zu bytes, 256-byte aligned", t ? t->tp->p->ws_bytes : (size_t)0);
+    return MTLDAS_ERR_ARG;
+  }
+  cudaError_t e = cudaMemsetAsync(dev_workspace, 0, t->tp->p->ws_bytes, (cudaStream_t)stream);
+  if (e != cudaSuccess) {
+    set_error("train_bind_workspace: %s", cudaGetErrorString(e));
+    return MTLDAS_ERR_CUDA;
+  }
+  t->tp->p->ws = (char*)dev_workspace;
+  t->tp->have_forward = false;
+  return 0;
+}
+int mtldas_train_forward(mtldas_train* t, const void* const* dev_state, int n_entries, const float* dev_x, int n,
+                         float* dev_out0, float* dev_out1, void* stream) {
+  if (!t || !dev_state || !dev_x || !dev_out0 || n_entries != (int)t->tp->p->state_keys.size()) {
+    set_error("train_forward: bad arguments (expected %d state entries)", t ? (int)t->tp->p->state_keys.size() : -1);
+    return MTLDAS_ERR_ARG;
+  }
+  for (int i = 0; i < n_entries; ++i)
+    if (!dev_state[i]) {
+      set_error("train_forward: state entry %d (%s) is NULL", i, t->tp->p->state_keys[i].c_str());
+      return MTLDAS_ERR_ARG;
+    }
+  return train_forward(*t->tp, dev_state, dev_x, n, dev_out0, dev_out1, (cudaStream_t)stream);
+}
+int mtldas_train_backward(mtldas_train* t, const void* const* dev_state, int n_entries, const float* dev_dout0,
+                          const float* dev_dout1, float* dev_flat_grads, void* stream) {
+  if (!t || !dev_state || !dev_dout0 || !dev_flat_grads || n_entries != (int)t->tp->p->state_keys.size()) {
+    set_error("train_backward: bad arguments");
+    return MTLDAS_ERR_ARG;
+  }
+  return train_backward(*t->tp, dev_state, dev_dout0, dev_dout1, dev_flat_grads, (cudaStream_t)stream);
+}
+int mtldas_train_last_launch_count(const mtldas_train* t) { return t ? t->tp->launches : -1; }
+int mtldas_train_read_tensor(mtldas_train* t, const char* name, int nb, float* dev_out_nchw, void* stream) {
+  if (!t || !name || !dev_out_nchw) return MTLDAS_ERR_ARG;
+  return plan_read_tensor(*t->tp->p, name, nb, dev_out_nchw, (cudaStream_t)stream);
+}
+size_t mtldas_train_describe(const mtldas_train* t, char* buf, size_t cap) {
+  if (!t) return 0;
+  std::string s = t->tp->p->describe();
+  if (buf && cap) {
+    size_t n = s.size() < cap - 1 ? s.size() : cap - 1;
+    memcpy(buf, s.data(), n);
+    buf[n] = 0;
+  }
+  return s.size() + 1;
 }
 
 }  // extern "C"

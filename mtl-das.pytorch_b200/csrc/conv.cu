@@ -21,6 +21,7 @@
 #include "gran.cuh"
 #include "kernels.h"
 #include "ptx.cuh"
+#include "train_types.h"
 
 namespace mtldas {
 
@@ -51,9 +52,15 @@ __device__ __forceinline__ void epilogue16(const ConvParams& p, const ConvGroupD
     } else if (p.epi == EPI_RELU) {
 #pragma unroll
       for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
+    } else if (p.epi == EPI_ACCUM) {
+      float a[16];
+      load8<T>(view_addr<T>(g.out, c0 >> 3, f, n, h, w), a);
+      load8<T>(view_addr<T>(g.out, (c0 >> 3) + 1, f, n, h, w), a + 8);
+#pragma unroll
+      for (int j = 0; j < 16; ++j) v[j] += a[j];
     }
   } else {
-    if (g.out.layout != LAY_P8) return;  // phase-split tensors keep their (pre-zeroed) pads untouched
+    if (g.out.layout != LAY_P8 || p.epi == EPI_ACCUM) return;  // pre-zeroed pads stay untouched
 #pragma unroll
     for (int j = 0; j < 16; ++j) v[j] = 0.f;
   }
@@ -110,8 +117,14 @@ __device__ __forceinline__ void epilogue_cols(const float* bias_s, int c0, bool 
     } else if (EPI == EPI_RELU) {
 #pragma unroll
       for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
+    } else if (EPI == EPI_ACCUM) {  // gradient accumulation: out += conv
+      load8<T>(out_addr0 + ch * out_plane_bytes, a);
+      load8<T>(out_addr0 + (ch + 1) * out_plane_bytes, a + 8);
+#pragma unroll
+      for (int j = 0; j < 16; ++j) v[j] += a[j];
     }
   } else {
+    if (EPI == EPI_ACCUM) return;  // pads of an accumulated tensor are already zero
 #pragma unroll
     for (int j = 0; j < 16; ++j) v[j] = 0.f;
   }
@@ -394,6 +407,7 @@ cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream,
       if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_kernel<EPI_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_kernel<EPI_ADD_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_kernel<EPI_SIGMOID_MUL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_kernel<EPI_ACCUM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e != cudaSuccess) return e;
       configured = smem;
     }
@@ -403,6 +417,7 @@ cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream,
       case EPI_NONE: return launch_ex(conv_umma_kernel<EPI_NONE>, grid, dim3(128), smem, stream, pdl, p);
       case EPI_RELU: return launch_ex(conv_umma_kernel<EPI_RELU>, grid, dim3(128), smem, stream, pdl, p);
       case EPI_ADD_RELU: return launch_ex(conv_umma_kernel<EPI_ADD_RELU>, grid, dim3(128), smem, stream, pdl, p);
+      case EPI_ACCUM: return launch_ex(conv_umma_kernel<EPI_ACCUM>, grid, dim3(128), smem, stream, pdl, p);
       default: return launch_ex(conv_umma_kernel<EPI_SIGMOID_MUL>, grid, dim3(128), smem, stream, pdl, p);
     }
   } else {

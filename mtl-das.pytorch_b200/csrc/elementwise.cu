@@ -83,8 +83,9 @@ __global__ void __launch_bounds__(128) stem_kernel(const __grid_constant__ StemP
     float o[16];
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
-      o[2 * q] = valid ? fmaxf(acc[pos][q].x + bs[2 * q], 0.f) : 0.f;
-      o[2 * q + 1] = valid ? fmaxf(acc[pos][q].y + bs[2 * q + 1], 0.f) : 0.f;
+      const float lo = p.raw ? -INFINITY : 0.f;
+      o[2 * q] = valid ? fmaxf(acc[pos][q].x + bs[2 * q], lo) : 0.f;
+      o[2 * q + 1] = valid ? fmaxf(acc[pos][q].y + bs[2 * q + 1], lo) : 0.f;
     }
     if (f + pos < p.body) {
       store8<T>(view_addr<T>(p.out, 0, f + pos, n, h, w + pos), o);
@@ -215,13 +216,21 @@ __global__ void __launch_bounds__(256) pack_kernel(const __grid_constant__ PackP
     p.bias_dst[s.cout_off + co] = s.beta[co] + (b - s.rmean[co]) * scale;
   }
   const float v = s.w[i] * scale;
-  int tap = rs, k = ci;
-  if (ci >= s.split) {
-    tap += 1;
-    k -= s.split;
+  int tap = rs, k = ci, cop;
+  if (s.transpose) {
+    if (ci < s.ci_lo || ci >= s.ci_lo + s.ci_n) return;
+    tap = s.tap_map[rs];
+    if (tap < 0) return;
+    k = s.k_off + co;
+    cop = s.cout_off + (ci - s.ci_lo);
+  } else {
+    if (ci >= s.split) {
+      tap += 1;
+      k -= s.split;
+    }
+    k += s.k_off;
+    cop = s.cout_off + co;
   }
-  k += s.k_off;
-  const int cop = s.cout_off + co;
   if (p.fp32) {
     reinterpret_cast<float*>(p.dst)[((size_t)tap * p.K_tap + k) * p.Cout_p + cop] = v;
   } else {

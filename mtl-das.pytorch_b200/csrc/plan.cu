@@ -84,7 +84,7 @@ static void build_layers(Plan& p) {
 // ---------------------------------------------------------------------------------------------
 // tensors
 // ---------------------------------------------------------------------------------------------
-static int add_tensor(Plan& p, const std::string& name, int C, int H, int W, int layout) {
+int add_tensor(Plan& p, const std::string& name, int C, int H, int W, int layout) {
   TensorInfo t;
   t.name = name, t.C = C, t.H = H, t.W = W, t.layout = layout;
   t.Hs = layout == LAY_P8 ? H : (H + 1) / 2;
@@ -365,7 +365,7 @@ Plan* build_plan(int kind, int mb, int precision) {
 // ---------------------------------------------------------------------------------------------
 ConvParams Plan::conv_params(const ConvOpHost& op, int nb) const {
   ConvParams q{};
-  q.H = op.H, q.W = op.W, q.Wp = op.W + 1, q.Pimg = (op.H + 1) * (op.W + 1);
+  q.H = op.Hv ? op.Hv : op.H, q.W = op.Wv ? op.Wv : op.W, q.Wp = op.W + 1, q.Pimg = (op.H + 1) * (op.W + 1);
   q.body = (long long)nb * q.Pimg;
   q.Cout = op.Cout, q.nchunks = op.nchunks, q.nsrc = op.nsrc, q.ntaps = op.ntaps;
   q.halo_lo = op.halo_lo, q.halo_hi = op.halo_hi;
@@ -386,6 +386,10 @@ ConvParams Plan::conv_params(const ConvOpHost& op, int nb) const {
     d.w = ws + g.w_off;
     d.bias = reinterpret_cast<const float*>(ws + g.bias_off);
     d.out = view(g.out_tensor, g.out_chunk0);
+    if (g.out_phase >= 0) {  // one phase plane of a phase-split tensor, addressed as a plain P8 tensor
+      d.out.base += (size_t)g.out_phase * d.out.phase_stride * gran;
+      d.out.layout = LAY_P8;
+    }
     if (g.aux_tensor >= 0) d.aux = view(g.aux_tensor, g.aux_chunk0);
     d.aux_nchunks = g.aux_nchunks;
   }
@@ -404,7 +408,7 @@ ConvParams Plan::conv_params(const ConvOpHost& op, int nb) const {
     }                                                                                 \
   } while (0)
 
-static PackSeg make_seg(const Plan& p, const PackSegHost& h, const void* const* state) {
+PackSeg make_seg(const Plan& p, const PackSegHost& h, const void* const* state) {
   const LayerSpec& L = p.layers[h.layer];
   PackSeg s{};
   s.w = (const float*)state[L.i_w];

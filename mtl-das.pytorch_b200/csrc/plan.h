@@ -42,6 +42,7 @@ struct PackSegHost {
 struct ConvGroupHost {
   SrcRef src[kMaxSrc];
   int out_tensor, out_chunk0;
+  int out_phase = -1;         // >= 0: write one phase plane of a P8S2 tensor (stride-2 dgrad)
   int aux_tensor, aux_chunk0, aux_nchunks;
   size_t w_off, bias_off;     // into the workspace
   std::vector<PackSegHost> segs;
@@ -49,6 +50,7 @@ struct ConvGroupHost {
 struct ConvOpHost {
   std::string name;
   int H, W, Cout, nchunks, nsrc, ntaps, halo_lo, halo_hi, epi, ngroups;
+  int Hv = 0, Wv = 0;         // valid extents when they differ from the plane geometry (0 = H, W)
   ConvTapDev tap[kMaxTaps];
   ConvGroupHost g[kMaxGroups];
   int MT, tps, NS, nstages, tap_bytes, tmem_cols;
@@ -106,6 +108,8 @@ struct Plan {
 };
 
 Plan* build_plan(int kind, int mb, int precision);
+int add_tensor(Plan& p, const std::string& name, int C, int H, int W, int layout);
+PackSeg make_seg(const Plan& p, const PackSegHost& h, const void* const* state);
 void choose_tiling(ConvOpHost& op);
 int plan_pack_eval(Plan& p, const void* const* state, cudaStream_t stream);
 int plan_forward_eval(Plan& p, const float* x, int n, float* out0, float* out1, cudaStream_t stream);

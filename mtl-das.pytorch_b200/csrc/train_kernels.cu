@@ -1,0 +1,633 @@
+// Training-mode kernels of the MTL-DAS hot path: batch-statistics BatchNorm (stats / finalize / fused apply),
+// fused elementwise backward (ReLU / residual / sigmoid*feature / ReLU+maxpool with BN backward), weight gradients,
+// head backward.  All streaming kernels move 16/32-byte granules with consecutive threads on consecutive positions.
+//
+// Reference semantics restated (autograd of /root/reference/model/modelA_MTL.py:127-174 under utils.py:359-373):
+//   BatchNorm2d train: y_hat = (y - mean) * invstd (biased batch variance), out = gamma*y_hat + beta;
+//     running_mean/var updated with momentum 0.1 (unbiased variance), num_batches_tracked += 1;
+//   backward: dgamma = sum(g*y_hat), dbeta = sum(g), dy = gamma*invstd*(g - mean(g) - y_hat*mean(g*y_hat));
+//   ReLU' = [out > 0]; sigmoid' = s(1-s); mask multiply: d mask = dz*feat, d feat = dz*mask;
+//   MaxPool2d(2,2,ceil): gradient to the first maximal element of the window (scan order h, w).
+#include <cstdio>
+
+#include "gran.cuh"
+#include "ptx.cuh"
+#include "train_kernels.h"
+
+namespace mtldas {
+
+namespace {
+
+struct Pos {
+  int n, h, w;
+  bool valid;
+};
+__device__ __forceinline__ Pos decode(int f, int Pimg, int Wp, int H, int W) {
+  Pos p;
+  p.n = f / Pimg;
+  const int rem = f - p.n * Pimg;
+  p.h = rem / Wp;
+  p.w = rem - p.h * Wp;
+  p.valid = p.h < H && p.w < W;
+  return p;
+}
+
+__device__ __forceinline__ void load_affine(const float* a, int c0, float* v) {
+  const float4 x = reinterpret_cast<const float4*>(a + c0)[0], y = reinterpret_cast<const float4*>(a + c0)[1];
+  v[0] = x.x, v[1] = x.y, v[2] = x.z, v[3] = x.w, v[4] = y.x, v[5] = y.y, v[6] = y.z, v[7] = y.w;
+}
+
+__device__ __forceinline__ void load_affine_d(const double* a, int c0, float k, float* v) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] = (float)(a[c0 + j] * (double)k);
+}
+
+// block-wide sum of 8 per-thread values -> atomicAdd(double) by warp 0; blockDim.x == 256
+__device__ __forceinline__ void block_reduce8_atomic(float* v, double* dst, float (*sh)[8]) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v[j] += __shfl_xor_sync(0xffffffffu, v[j], o);
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sh[warp][j] = v[j];
+  }
+  __syncthreads();
+  if (threadIdx.x < 8) {
+    float s = 0.f;
+    for (int wv = 0; wv < 8; ++wv) s += sh[wv][threadIdx.x];
+    atomicAdd(dst + threadIdx.x, (double)s);
+  }
+  __syncthreads();
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// batch statistics: per-channel sum and sum of squares (pads and guards are zero -> planes are summed whole)
+// grid (ceil(body/1024), nchunks), block 256
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) stats_kernel(const __grid_constant__ StatsParams p) {
+  __shared__ float sh[8][8];
+  const int c = blockIdx.y;
+  float s[8], q[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
+  const long long base = (long long)blockIdx.x * 1024 + threadIdx.x;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const long long f = base + i * 256;
+    if (f < p.body) {
+      float v[8];
+      load8<T>(p.y.base + ((long long)c * p.y.plane + p.y.g_lo + f) * Gran<T>::bytes, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s[j] += v[j], q[j] = fmaf(v[j], v[j], q[j]);
+    }
+  }
+  block_reduce8_atomic(s, p.sum + c * 8, sh);
+  block_reduce8_atomic(q, p.sumsq + c * 8, sh);
+}
+
+cudaError_t launch_stats(const StatsParams& p, int precision, cudaStream_t st) {
+  dim3 grid((unsigned)((p.body + 1023) / 1024), p.nchunks);
+  if (precision == 0)
+    stats_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(p);
+  else
+    stats_kernel<float><<<grid, 256, 0, st>>>(p);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// finalize: mean / invstd / scale / shift, running statistics (one block, one thread per channel)
+// ---------------------------------------------------------------------------------------------
+__global__ void finalize_kernel(const __grid_constant__ FinalizeParams p) {
+  const int c = threadIdx.x;
+  if (c >= p.C) return;
+  const double mean = p.bn.sum[c] / p.n;
+  double var = p.bn.sumsq[c] / p.n - mean * mean;
+  if (var < 0.0) var = 0.0;
+  const double invstd = rsqrt(var + (double)p.eps);
+  float scale = 0.f, shift = 0.f, fm = 0.f, fi = 0.f;
+  for (int s = 0; s < p.nseg; ++s) {
+    const FinalizeSeg& g = p.seg[s];
+    if (c >= g.ch_off && c < g.ch_off + g.count) {
+      const int i = c - g.ch_off;
+      fm = (float)mean, fi = (float)invstd;
+      scale = (float)((double)g.gamma[i] * invstd);
+      shift = (float)((double)g.beta[i] - mean * (double)g.gamma[i] * invstd);
+      const double bias = g.conv_bias ? (double)g.conv_bias[i] : 0.0;
+      const double unbiased = p.n > 1.0 ? var * p.n / (p.n - 1.0) : var;
+      g.running_mean[i] = (float)((1.0 - p.momentum) * (double)g.running_mean[i] + p.momentum * (mean + bias));
+      g.running_var[i] = (float)((1.0 - p.momentum) * (double)g.running_var[i] + p.momentum * unbiased);
+      if (i == 0) *g.num_batches_tracked += 1;
+    }
+  }
+  p.bn.scale[c] = scale, p.bn.shift[c] = shift, p.bn.mean[c] = fm, p.bn.invstd[c] = fi;
+}
+
+cudaError_t launch_finalize(const FinalizeParams& p, cudaStream_t st) {
+  finalize_kernel<<<1, 256, 0, st>>>(p);
+  return cudaGetLastError();
+}
+
+__global__ void bn_grad_kernel(const __grid_constant__ BnGradParams p) {
+  const int c = threadIdx.x;
+  for (int s = 0; s < p.nseg; ++s) {
+    const BnGradSeg& g = p.seg[s];
+    if (c >= g.ch_off && c < g.ch_off + g.count) {
+      g.dgamma[c - g.ch_off] = (float)p.bn.red_gy[c];
+      g.dbeta[c - g.ch_off] = (float)p.bn.red_g[c];
+    }
+  }
+}
+cudaError_t launch_bn_grad(const BnGradParams& p, cudaStream_t st) {
+  bn_grad_kernel<<<1, 256, 0, st>>>(p);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// fused BatchNorm apply + activation (forward)
+// thread = (position, chunk-of-a-task); EW_SIGMOID_MUL loops over the tasks that share the feature map;
+// EW_RELU_POOL: thread = (pooled position, chunk).
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) ew_fwd_kernel(const __grid_constant__ EwParams p) {
+  const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= p.body * p.nchunks) return;
+  const int c = (int)(idx / p.body);
+  const int f = (int)(idx - (long long)c * p.body);
+  constexpr int G = Gran<T>::bytes;
+  if (p.mode == EW_RELU_POOL) {
+    const Pos o = decode(f, p.Pimgo, p.Wpo, p.Ho, p.Wo);
+    float m[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) m[j] = 0.f;
+    if (o.valid) {
+      float sc[8], sh[8];
+      load_affine(p.bn.scale, c * 8, sc);
+      load_affine(p.bn.shift, c * 8, sh);
+#pragma unroll
+      for (int dy = 0; dy < 2; ++dy) {
+        const int h = 2 * o.h + dy;
+        if (h >= p.H) continue;
+#pragma unroll
+        for (int dx = 0; dx < 2; ++dx) {
+          const int w = 2 * o.w + dx;
+          if (w >= p.W) continue;
+          float v[8];
+          load8<T>(view_addr<T>(p.y, c, o.n * p.Pimg + h * p.Wp + w, o.n, h, w), v);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) m[j] = fmaxf(m[j], fmaf(v[j], sc[j], sh[j]));  // relu folded into max with 0
+        }
+      }
+    }
+    store8<T>(view_addr<T>(p.out, c, f, o.n, o.h, o.w), m);
+    return;
+  }
+  const Pos q = decode(f, p.Pimg, p.Wp, p.H, p.W);
+  if (!q.valid && p.out.layout != LAY_P8) return;
+  float aux[8];
+  if (q.valid && (p.mode == EW_ADD_RELU_ID || p.mode == EW_SIGMOID_MUL)) load8<T>(view_addr<T>(p.aux, c, f, q.n, q.h, q.w), aux);
+  for (int t = 0; t < p.ntasks; ++t) {
+    const int ch = t * p.nchunks + c;
+    float z[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) z[j] = 0.f;
+    if (q.valid) {
+      float v[8], sc[8], sh[8];
+      load8<T>(p.y.base + ((long long)ch * p.y.plane + p.y.g_lo + f) * G, v);
+      load_affine(p.bn.scale, ch * 8, sc);
+      load_affine(p.bn.shift, ch * 8, sh);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = fmaf(v[j], sc[j], sh[j]);
+      if (p.mode == EW_RELU) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) z[j] = fmaxf(v[j], 0.f);
+      } else if (p.mode == EW_ADD_RELU_ID) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) z[j] = fmaxf(v[j] + aux[j], 0.f);
+      } else if (p.mode == EW_ADD_RELU_SC) {
+        float v2[8];
+        load8<T>(p.y2.base + ((long long)ch * p.y2.plane + p.y2.g_lo + f) * G, v2);
+        load_affine(p.bn2.scale, ch * 8, sc);
+        load_affine(p.bn2.shift, ch * 8, sh);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) z[j] = fmaxf(v[j] + fmaf(v2[j], sc[j], sh[j]), 0.f);
+      } else {  // EW_SIGMOID_MUL
+#pragma unroll
+        for (int j = 0; j < 8; ++j) z[j] = aux[j] / (1.f + expf(-v[j]));
+      }
+    }
+    store8<T>(view_addr<T>(p.out, ch, f, q.n, q.h, q.w), z);
+  }
+}
+
+cudaError_t launch_ew_fwd(const EwParams& p, int precision, cudaStream_t st) {
+  const long long total = p.body * p.nchunks;
+  const unsigned grid = (unsigned)((total + 255) / 256);
+  if (precision == 0)
+    ew_fwd_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(p);
+  else
+    ew_fwd_kernel<float><<<grid, 256, 0, st>>>(p);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// fused elementwise backward.  PASS 0: reductions sum(g), sum(g*y_hat); PASS 1: dy (and d aux).
+// g = dz * activation'(.) is recomputed in both passes from dz and the saved raw tensors.
+// ---------------------------------------------------------------------------------------------
+template <typename T, int PASS>
+__global__ void __launch_bounds__(256) ew_bwd_kernel(const __grid_constant__ EwParams p) {
+  __shared__ float sh[8][8];
+  // a block never straddles two chunks: the launcher pads body to a multiple of 256 per chunk (see launch)
+  const long long per_chunk = (p.body + 255) / 256 * 256;
+  const long long idx2 = (long long)blockIdx.x * 256 + threadIdx.x;
+  const int c = (int)(idx2 / per_chunk);
+  const int f = (int)(idx2 - (long long)c * per_chunk);
+  const bool in_range = f < p.body;
+  constexpr int G = Gran<T>::bytes;
+  const BnArrays& bn = p.second ? p.bn2 : p.bn;     // the BatchNorm whose input gradient this launch produces
+  const ActView& ym = p.second ? p.y2 : p.y;
+
+  if (p.mode == EW_RELU_POOL) {
+    // thread = pooled position; the 2x2 window's four full-resolution positions belong to this thread alone
+    float rg[8], rgy[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) rg[j] = rgy[j] = 0.f;
+    Pos o = decode(in_range ? f : 0, p.Pimgo, p.Wpo, p.Ho, p.Wo);
+    if (in_range && o.valid) {
+      float sc[8], shf[8], mu[8], is[8], dzv[8];
+      load_affine(bn.scale, c * 8, sc);
+      load_affine(bn.shift, c * 8, shf);
+      load_affine(bn.mean, c * 8, mu);
+      load_affine(bn.invstd, c * 8, is);
+      load8<T>(view_addr<T>(p.dz, c, f, o.n, o.h, o.w), dzv);
+      float yv[4][8];
+      bool inb[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int h = 2 * o.h + (k >> 1), w = 2 * o.w + (k & 1);
+        inb[k] = h < p.H && w < p.W;
+        if (inb[k]) load8<T>(view_addr<T>(ym, c, o.n * p.Pimg + h * p.Wp + w, o.n, h, w), yv[k]);
+      }
+      int arg[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float best = -INFINITY;
+        arg[j] = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (!inb[k]) continue;
+          const float r = fmaxf(fmaf(yv[k][j], sc[j], shf[j]), 0.f);
+          if (r > best) best = r, arg[j] = k;   // strict '>' : first maximum wins (scan order h, w)
+        }
+      }
+      float cg[8], cgy[8];
+      if (PASS == 1) {
+        load_affine_d(bn.red_g, c * 8, p.inv_n, cg);
+        load_affine_d(bn.red_gy, c * 8, p.inv_n, cgy);
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (!inb[k]) continue;
+        float dyv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float v = fmaf(yv[k][j], sc[j], shf[j]);
+          const float g = (arg[j] == k && v > 0.f) ? dzv[j] : 0.f;
+          const float yh = (yv[k][j] - mu[j]) * is[j];
+          if (PASS == 0) {
+            rg[j] += g, rgy[j] = fmaf(g, yh, rgy[j]);
+          } else {
+            dyv[j] = sc[j] * (g - cg[j] - yh * cgy[j]);
+          }
+        }
+        if (PASS == 1) {
+          const int h = 2 * o.h + (k >> 1), w = 2 * o.w + (k & 1);
+          store8<T>(view_addr<T>(p.dy, c, o.n * p.Pimg + h * p.Wp + w, o.n, h, w), dyv);
+        }
+      }
+    }
+    if (PASS == 0) {
+      block_reduce8_atomic(rg, bn.red_g + c * 8, sh);
+      block_reduce8_atomic(rgy, bn.red_gy + c * 8, sh);
+    }
+    return;
+  }
+
+  const Pos q = decode(in_range ? f : 0, p.Pimg, p.Wp, p.H, p.W);
+  const bool valid = in_range && q.valid;
+  float aux[8], dacc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) dacc[j] = 0.f, aux[j] = 0.f;
+  if (valid && (p.mode == EW_ADD_RELU_ID || p.mode == EW_SIGMOID_MUL)) load8<T>(view_addr<T>(p.aux, c, f, q.n, q.h, q.w), aux);
+  for (int t = 0; t < p.ntasks; ++t) {
+    const int ch = t * p.nchunks + c;
+    float rg[8], rgy[8], dyv[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) rg[j] = rgy[j] = dyv[j] = 0.f;
+    if (valid) {
+      float y[8], sc[8], shf[8], mu[8], is[8], dzv[8], v[8];
+      load8<T>(ym.base + ((long long)ch * ym.plane + ym.g_lo + f) * G, y);
+      load_affine(bn.scale, ch * 8, sc);
+      load_affine(bn.shift, ch * 8, shf);
+      load_affine(bn.mean, ch * 8, mu);
+      load_affine(bn.invstd, ch * 8, is);
+      load8<T>(view_addr<T>(p.dz, ch, f, q.n, q.h, q.w), dzv);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = fmaf(y[j], sc[j], shf[j]);
+      float g[8];
+      if (p.mode == EW_RELU) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = v[j] > 0.f ? dzv[j] : 0.f;
+      } else if (p.mode == EW_ADD_RELU_ID) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = (v[j] + aux[j]) > 0.f ? dzv[j] : 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dacc[j] = g[j];
+      } else if (p.mode == EW_ADD_RELU_SC) {
+        // the other branch's normalised value completes the pre-activation
+        const BnArrays& bo = p.second ? p.bn : p.bn2;
+        const ActView& yo = p.second ? p.y : p.y2;
+        float y2[8], s2[8], h2[8];
+        load8<T>(yo.base + ((long long)ch * yo.plane + yo.g_lo + f) * G, y2);
+        load_affine(bo.scale, ch * 8, s2);
+        load_affine(bo.shift, ch * 8, h2);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = (v[j] + fmaf(y2[j], s2[j], h2[j])) > 0.f ? dzv[j] : 0.f;
+      } else {  // EW_SIGMOID_MUL
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float s = 1.f / (1.f + expf(-v[j]));
+          g[j] = dzv[j] * aux[j] * s * (1.f - s);
+          dacc[j] = fmaf(dzv[j], s, dacc[j]);
+        }
+      }
+      if (PASS == 0) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) rg[j] = g[j], rgy[j] = g[j] * (y[j] - mu[j]) * is[j];
+      } else {
+        float cg[8], cgy[8];
+        load_affine_d(bn.red_g, ch * 8, p.inv_n, cg);
+        load_affine_d(bn.red_gy, ch * 8, p.inv_n, cgy);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dyv[j] = sc[j] * (g[j] - cg[j] - (y[j] - mu[j]) * is[j] * cgy[j]);
+      }
+    }
+    if (PASS == 0) {
+      block_reduce8_atomic(rg, bn.red_g + ch * 8, sh);
+      block_reduce8_atomic(rgy, bn.red_gy + ch * 8, sh);
+    } else if (in_range) {
+      store8<T>(p.dy.base + ((long long)ch * p.dy.plane + p.dy.g_lo + f) * G, dyv);  // zero at pads
+    }
+  }
+  if (PASS == 1 && p.want_daux && in_range && !p.second) {
+    if (valid || p.daux.layout == LAY_P8) {
+      char* a = view_addr<T>(p.daux, c, f, q.n, q.h, q.w);
+      if (p.daux_accum && valid) {
+        float old[8];
+        load8<T>(a, old);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dacc[j] += old[j];
+      }
+      if (!p.daux_accum || valid) store8<T>(a, dacc);
+    }
+  }
+}
+
+cudaError_t launch_ew_bwd(const EwParams& p, int pass, int precision, cudaStream_t st) {
+  const long long per_chunk = (p.body + 255) / 256 * 256;
+  const unsigned grid = (unsigned)(per_chunk * p.nchunks / 256);
+  if (precision == 0) {
+    if (pass == 0)
+      ew_bwd_kernel<__nv_bfloat16, 0><<<grid, 256, 0, st>>>(p);
+    else
+      ew_bwd_kernel<__nv_bfloat16, 1><<<grid, 256, 0, st>>>(p);
+  } else {
+    if (pass == 0)
+      ew_bwd_kernel<float, 0><<<grid, 256, 0, st>>>(p);
+    else
+      ew_bwd_kernel<float, 1><<<grid, 256, 0, st>>>(p);
+  }
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// weight gradient on CUDA cores: dW[tap][k][cout] += sum_pos zin[pos+off][k] * dy[pos][cout]
+// grid (position slices, taps); block 256 = 16 x 16 thread grid, each thread (K/16) x (Cout/16) outputs.
+// ---------------------------------------------------------------------------------------------
+constexpr int kWgPos = 32;  // positions staged per iteration
+
+template <typename T, int KR, int CR>
+__global__ void __launch_bounds__(256) wgrad_kernel(const __grid_constant__ WgradParams p) {
+  extern __shared__ __align__(16) float wsm[];
+  const int K = p.nchunks * 8, Cout = p.Cout;
+  float* zs = wsm;                       // [kWgPos][K]
+  float* ds = wsm + kWgPos * K;          // [kWgPos][Cout]
+  const ConvTapDev tp = p.tap[blockIdx.y];
+  const ConvSrcDev src = p.src[tp.src];
+  const long long f0 = (long long)blockIdx.x * p.slice;
+  const long long f1 = min(f0 + (long long)p.slice, p.body);
+  const int tk = threadIdx.x >> 4, tc = threadIdx.x & 15;
+  constexpr int G = Gran<T>::bytes;
+  float acc[KR][CR];
+#pragma unroll
+  for (int i = 0; i < KR; ++i)
+#pragma unroll
+    for (int j = 0; j < CR; ++j) acc[i][j] = 0.f;
+  for (long long fb = f0; fb < f1; fb += kWgPos) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < kWgPos * p.nchunks; i += 256) {
+      const int c = i / kWgPos, pp = i - c * kWgPos;
+      float v[8];
+      if (fb + pp < f1)
+        load8<T>(src.base + (long long)c * src.plane_bytes + (fb + pp + tp.off) * G, v);
+      else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = 0.f;
+      }
+      float4* d = reinterpret_cast<float4*>(zs + pp * K + c * 8);
+      d[0] = make_float4(v[0], v[1], v[2], v[3]);
+      d[1] = make_float4(v[4], v[5], v[6], v[7]);
+    }
+    for (int i = threadIdx.x; i < kWgPos * (Cout / 8); i += 256) {
+      const int c = i / kWgPos, pp = i - c * kWgPos;
+      float v[8];
+      if (fb + pp < f1)
+        load8<T>(p.dy + (long long)c * p.dy_plane_bytes + (fb + pp) * G, v);
+      else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = 0.f;
+      }
+      float4* d = reinterpret_cast<float4*>(ds + pp * Cout + c * 8);
+      d[0] = make_float4(v[0], v[1], v[2], v[3]);
+      d[1] = make_float4(v[4], v[5], v[6], v[7]);
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (int pp = 0; pp < kWgPos; ++pp) {
+      float zv[KR], dv[CR];
+#pragma unroll
+      for (int i = 0; i < KR; ++i) zv[i] = zs[pp * K + tk + 16 * i];
+#pragma unroll
+      for (int j = 0; j < CR; ++j) dv[j] = ds[pp * Cout + tc + 16 * j];
+#pragma unroll
+      for (int i = 0; i < KR; ++i)
+#pragma unroll
+        for (int j = 0; j < CR; ++j) acc[i][j] = fmaf(zv[i], dv[j], acc[i][j]);
+    }
+  }
+  float* dw = p.dw + (size_t)blockIdx.y * K * Cout;
+#pragma unroll
+  for (int i = 0; i < KR; ++i)
+#pragma unroll
+    for (int j = 0; j < CR; ++j) atomicAdd(dw + (size_t)(tk + 16 * i) * Cout + tc + 16 * j, acc[i][j]);
+}
+
+template <typename T>
+static cudaError_t launch_wgrad_t(const WgradParams& p, cudaStream_t st) {
+  const int K = p.nchunks * 8;
+  dim3 grid((unsigned)((p.body + p.slice - 1) / p.slice), p.ntaps);
+  const size_t smem = (size_t)kWgPos * (K + p.Cout) * sizeof(float);
+  const int kr = K / 16, cr = p.Cout / 16;
+#define WG(KR_, CR_)                                                                       \
+  if (kr == KR_ && cr == CR_) {                                                            \
+    wgrad_kernel<T, KR_, CR_><<<grid, 256, smem, st>>>(p);                                 \
+    return cudaGetLastError();                                                             \
+  }
+  WG(1, 1) WG(1, 2) WG(1, 4) WG(1, 8) WG(2, 1) WG(2, 2) WG(2, 4) WG(2, 8)
+  WG(4, 1) WG(4, 2) WG(4, 4) WG(4, 8) WG(8, 1) WG(8, 2) WG(8, 4) WG(8, 8)
+#undef WG
+  return cudaErrorInvalidValue;
+}
+
+cudaError_t launch_wgrad(const WgradParams& p, int precision, cudaStream_t st) {
+  return precision == 0 ? launch_wgrad_t<__nv_bfloat16>(p, st) : launch_wgrad_t<float>(p, st);
+}
+
+// ---------------------------------------------------------------------------------------------
+// stem weight gradient: dW[tap][co] += sum_pos x[n, 3h-2+r, 3w-2+s] * dy[pos][co]
+// block 256 handles `slice` positions, 64 at a time staged in shared memory; 784 outputs over 256 threads.
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) stem_wgrad_kernel(const __grid_constant__ StemWgradParams p, int slice) {
+  __shared__ float xw[64][49];
+  __shared__ float dys[64][16];
+  const long long f0 = (long long)blockIdx.x * slice, f1 = min(f0 + (long long)slice, p.body);
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (long long fb = f0; fb < f1; fb += 64) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < 64 * 49; i += 256) {
+      const int pp = i / 49, t = i - pp * 49;
+      float v = 0.f;
+      if (fb + pp < f1) {
+        const Pos q = decode((int)(fb + pp), p.Pimg, p.Wp, p.H, p.W);
+        const int iy = 3 * q.h - 2 + t / 7, ix = 3 * q.w - 2 + t % 7;
+        if (q.valid && iy >= 0 && iy < p.Hin && ix >= 0 && ix < p.Win) v = p.x[((size_t)q.n * p.Hin + iy) * p.Win + ix];
+      }
+      xw[pp][t] = v;
+    }
+    for (int i = threadIdx.x; i < 64 * 2; i += 256) {
+      const int pp = i >> 1, c = i & 1;
+      float v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = 0.f;
+      if (fb + pp < f1) load8<T>(p.dy.base + ((long long)c * p.dy.plane + p.dy.g_lo + fb + pp) * Gran<T>::bytes, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) dys[pp][c * 8 + j] = v[j];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int o = threadIdx.x + 256 * r;
+      if (o < 784) {
+        const int t = o >> 4, co = o & 15;
+        float a = acc[r];
+        for (int pp = 0; pp < 64; ++pp) a = fmaf(xw[pp][t], dys[pp][co], a);
+        acc[r] = a;
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int o = threadIdx.x + 256 * r;
+    if (o < 784) atomicAdd(p.dw + o, acc[r]);
+  }
+}
+
+cudaError_t launch_stem_wgrad(const StemWgradParams& p, int precision, cudaStream_t st) {
+  const int slice = 2048;
+  const unsigned grid = (unsigned)((p.body + slice - 1) / slice);
+  if (precision == 0)
+    stem_wgrad_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(p, slice);
+  else
+    stem_wgrad_kernel<float><<<grid, 256, 0, st>>>(p, slice);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// head backward: d a4[n,c,h,w] = dz[n, c / group] / (H*W*group), dz = dlogp - softmax * sum(dlogp)
+// one block per sample, thread t: chunk t%16, positions t/16, t/16+8, ...
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(128) head_bwd_kernel(const __grid_constant__ HeadBwdParams p) {
+  __shared__ float dzc[16];
+  const int n = blockIdx.x;
+  if (threadIdx.x == 0) {
+    float s = 0.f;
+    for (int j = 0; j < p.classes; ++j) s += p.dlogp[(size_t)n * p.classes + j];
+    const int group = 128 / p.classes;
+    const float k = 1.f / (float)(p.H * p.W * group);
+    for (int j = 0; j < p.classes; ++j)
+      dzc[j] = (p.dlogp[(size_t)n * p.classes + j] - expf(p.logp[(size_t)n * p.classes + j]) * s) * k;
+  }
+  __syncthreads();
+  const int c = threadIdx.x & 15, pl = threadIdx.x >> 4;
+  const int group = 128 / p.classes;
+  float v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] = dzc[(c * 8 + j) / group];
+  float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int q = pl; q < p.Pimg; q += 8) {
+    const int h = q / p.Wp, w = q - h * p.Wp;
+    const bool valid = h < p.H && w < p.W;
+    store8<T>(p.da4.base + ((long long)c * p.da4.plane + p.da4.g_lo + (long long)n * p.Pimg + q) * Gran<T>::bytes,
+              valid ? v : z);
+  }
+}
+
+cudaError_t launch_head_bwd(const HeadBwdParams& p, int precision, cudaStream_t st) {
+  if (precision == 0)
+    head_bwd_kernel<__nv_bfloat16><<<p.nb, 128, 0, st>>>(p);
+  else
+    head_bwd_kernel<float><<<p.nb, 128, 0, st>>>(p);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// packed fp32 weight gradient -> reference parameter layout (inverse of pack_kernel's placement)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) unpack_kernel(const __grid_constant__ UnpackParams p) {
+  const int kk = p.ksize * p.ksize;
+  const int total = p.cout * p.cin * kk;
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= total) return;
+  const int co = i / (p.cin * kk);
+  const int r1 = i - co * (p.cin * kk);
+  const int ci = r1 / kk;
+  int tap = r1 - ci * kk, k = ci;
+  if (ci >= p.split) tap += 1, k -= p.split;
+  k += p.k_off;
+  p.dst[i] = p.src[((size_t)tap * p.K_tap + k) * p.Cout_p + p.cout_off + co];
+}
+
+cudaError_t launch_unpack(const UnpackParams& p, cudaStream_t st) {
+  const int total = p.cout * p.cin * p.ksize * p.ksize;
+  unpack_kernel<<<(total + 255) / 256, 256, 0, st>>>(p);
+  return cudaGetLastError();
+}
+
+}  // namespace mtldas

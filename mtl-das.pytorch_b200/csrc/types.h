@@ -83,6 +83,7 @@ struct StemParams {        // 7x7 / stride 3 / pad 2, Cin = 1 (modelA_MTL.py:74)
   ActView out;
   int Hin, Win, H, W, Wp, Pimg;
   long long body;
+  int raw;                 // 1: store conv + bias without the ReLU (training: BatchNorm follows as its own pass)
 };
 
 struct PoolParams {        // MaxPool2d(2,2,ceil_mode=True) (modelA_MTL.py:116)
@@ -110,6 +111,10 @@ struct PackSeg {           // one source layer scattered into a packed weight bl
   int cout, cin, ksize;
   int split;               // cin >= split go to tap+1 (dual-source 1x1), else INT_MAX
   int k_off, cout_off;     // placement inside the packed [K_tap x Cout_p] tap matrix
+  // dgrad packing (transpose = 1): packed K runs over the layer's OUTPUT channels (at k_off), packed N over its
+  // input channels [ci_lo, ci_lo+ci_n) (at cout_off); tap_map selects / reorders taps (-1 = tap not used)
+  int transpose, ci_lo, ci_n;
+  int tap_map[9];
 };
 struct PackParams {
   PackSeg seg;

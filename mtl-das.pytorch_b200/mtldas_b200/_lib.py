@@ -41,6 +41,17 @@ def _load():
         "mtldas_plan_read_tensor": (ci, [vp, c.c_char_p, ci, vp, vp]),
         "mtldas_conv2d_nchw": (ci, [vp, vp, vp, vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, ci, ci, ci, ci]),
         "mtldas_conv2d_nchw_static": (ci, [vp, vp, vp, vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, ci, ci, ci, ci, vp]),
+        "mtldas_train_create": (vp, [ci, ci, ci]),
+        "mtldas_train_destroy": (None, [vp]),
+        "mtldas_train_num_state_entries": (ci, [vp]),
+        "mtldas_train_num_params": (sz, [vp]),
+        "mtldas_train_workspace_bytes": (sz, [vp]),
+        "mtldas_train_bind_workspace": (ci, [vp, vp, sz, vp]),
+        "mtldas_train_forward": (ci, [vp, c.POINTER(vp), ci, vp, ci, vp, vp, vp]),
+        "mtldas_train_backward": (ci, [vp, c.POINTER(vp), ci, vp, vp, vp, vp]),
+        "mtldas_train_last_launch_count": (ci, [vp]),
+        "mtldas_train_read_tensor": (ci, [vp, c.c_char_p, ci, vp, vp]),
+        "mtldas_train_describe": (sz, [vp, c.c_char_p, sz]),
         "mtldas_umma_selftest": (cf, [ci, ci, ci]),
         "mtldas_umma_rate": (ci, [ci, ci, ci, c.POINTER(cf)]),
     }

@@ -130,6 +130,91 @@ class EvalPlan:
         return out
 
 
+class TrainPlan:
+    """Train-mode forward (batch-statistics BatchNorm) + backward through mtldas_train_* (utils.py:344-373)."""
+
+    def __init__(self, kind="MTL", batch=32, precision="bf16", device=None, need_device=True):
+        self.kind, self.precision, self.batch = kind, precision, int(batch)
+        self._h = lib.mtldas_train_create(KINDS[kind], self.batch, PRECISIONS[precision])
+        if not self._h:
+            raise MtldasError("train_create: " + lib.mtldas_last_error().decode())
+        self.n_state = lib.mtldas_train_num_state_entries(self._h)
+        self.n_params = lib.mtldas_train_num_params(self._h)
+        self.workspace_bytes = lib.mtldas_train_workspace_bytes(self._h)
+        self.classes = {"MTL": (16, 2), "single_distance": (16,), "single_event": (2,)}[kind]
+        self.device, self._ws, self._state, self._arr = None, None, None, None
+        if need_device:
+            self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+            _require_b200(self.device)
+            with torch.cuda.device(self.device):
+                self._ws = torch.empty(self.workspace_bytes + 256, dtype=torch.uint8, device=self.device)
+                ptr = (self._ws.data_ptr() + 255) & ~255
+                check(lib.mtldas_train_bind_workspace(self._h, ctypes.c_void_p(ptr), self.workspace_bytes,
+                                                      _stream_ptr(self.device)), "train_bind_workspace")
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            lib.mtldas_train_destroy(h)
+            self._h = None
+
+    def describe(self):
+        n = lib.mtldas_train_describe(self._h, None, 0)
+        buf = ctypes.create_string_buffer(n)
+        lib.mtldas_train_describe(self._h, buf, n)
+        return json.loads(buf.value.decode())
+
+    def _state_array(self, state_tensors):
+        for t in state_tensors:
+            if t.device != self.device or not t.is_contiguous():
+                raise MtldasError("state tensors must be contiguous and on the plan's device")
+        self._state = list(state_tensors)
+        self._arr = (ctypes.c_void_p * self.n_state)(*[t.data_ptr() for t in self._state])
+
+    def forward(self, state_tensors, x):
+        """state_tensors: the module's state_dict values in order (parameters fp32, running stats fp32, counters int64).
+        Running statistics are updated in place."""
+        if not x.is_cuda:
+            raise MtldasError("input must be a CUDA tensor; there is no CPU fallback")
+        x = x.contiguous().float()
+        n = x.shape[0]
+        if n > self.batch:
+            raise MtldasError(f"batch {n} larger than the plan's {self.batch}")
+        self._state_array(state_tensors)
+        self._x = x
+        outs = [torch.empty((n, c), dtype=torch.float32, device=x.device) for c in self.classes]
+        with torch.cuda.device(self.device):
+            check(lib.mtldas_train_forward(self._h, self._arr, self.n_state, ctypes.c_void_p(x.data_ptr()), n,
+                                           ctypes.c_void_p(outs[0].data_ptr()),
+                                           ctypes.c_void_p(outs[1].data_ptr()) if len(outs) > 1 else None,
+                                           _stream_ptr(self.device)), "train_forward")
+        return tuple(outs)
+
+    def backward(self, douts, flat=None):
+        """douts: d loss / d log-probs per task. Returns the flat fp32 gradient (named_parameters order)."""
+        douts = [d.contiguous().float() for d in douts]
+        if flat is None:
+            flat = torch.empty(self.n_params, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(lib.mtldas_train_backward(self._h, self._arr, self.n_state, ctypes.c_void_p(douts[0].data_ptr()),
+                                            ctypes.c_void_p(douts[1].data_ptr()) if len(douts) > 1 else None,
+                                            ctypes.c_void_p(flat.data_ptr()), _stream_ptr(self.device)), "train_backward")
+        return flat
+
+    @property
+    def last_launch_count(self):
+        return lib.mtldas_train_last_launch_count(self._h)
+
+    def read_tensor(self, name, nb):
+        d = self.describe()
+        t = next(t for t in d["tensors"] if t["name"] == name)
+        out = torch.empty((nb, t["C"], t["H"], t["W"]), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(lib.mtldas_train_read_tensor(self._h, name.encode(), nb, ctypes.c_void_p(out.data_ptr()),
+                                               _stream_ptr(self.device)), "train_read_tensor")
+        return out
+
+
 def conv2d_nchw(x, weight, bias=None, aux=None, x2=None, stride=1, epilogue=0, precision="bf16",
                 aux_phase_split=False):
     """One fused convolution through mtldas_conv2d_nchw (unit-parity entry point)."""

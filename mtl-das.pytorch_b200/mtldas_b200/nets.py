@@ -18,7 +18,7 @@ import torch
 import torch.nn as nn
 
 from ._lib import MtldasError
-from .engine import EvalPlan
+from .engine import EvalPlan, TrainPlan
 
 _WIDTHS = (16, 16, 32, 64, 128)          # modelA_MTL.py:61-66
 _CLASSES = {"distance": 16, "event": 2}  # modelA_MTL.py:68-69
@@ -95,8 +95,44 @@ class _DasNet(nn.Module):
             raise MtldasError("mtldas_b200 modules run on a B200 through the CUDA extension only; "
                               "got a non-CUDA input and there is no CPU fallback")
         if self.training:
-            raise MtldasError("training-mode forward/backward is not available in this build yet")
+            return _TrainStep.apply(self, x, *[p for _, p in self.named_parameters()])
         return self._eval_plan(x.device).forward(x)
+
+    def _train_plan(self, device, n):
+        key = (str(device), self.precision)
+        plan = self._tplans.get(key) if hasattr(self, "_tplans") else None
+        if not hasattr(self, "_tplans"):
+            self._tplans = {}
+        if plan is None or plan.batch < n:
+            plan = TrainPlan(self._kind(), max(n, 8), self.precision, device)
+            self._tplans[key] = plan
+        return plan
+
+
+class _TrainStep(torch.autograd.Function):
+    """model(x) in train mode + loss.backward() (utils.py:359,373) through mtldas_train_forward / _backward.
+    One forward may be outstanding per module: backward differentiates the most recent forward."""
+
+    @staticmethod
+    def forward(ctx, module, x, *params):
+        plan = module._train_plan(x.device, x.shape[0])
+        state = [v.detach() for v in module.state_dict(keep_vars=True).values()]
+        outs = plan.forward(state, x)
+        ctx.plan, ctx.shapes = plan, [p.shape for p in params]
+        ctx.mark_non_differentiable()
+        return outs
+
+    @staticmethod
+    def backward(ctx, *douts):
+        flat = ctx.plan.backward(douts)
+        grads, off = [], 0
+        for shp in ctx.shapes:
+            n = 1
+            for s in shp:
+                n *= s
+            grads.append(flat[off:off + n].view(shp))
+            off += n
+        return (None, None, *grads)
 
 
 class MTL_Net(_DasNet):
