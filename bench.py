@@ -44,6 +44,7 @@ def parse():
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--cpu-sample", type=int, default=256, help="patches per CPU-baseline step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--train-batch", type=int, default=256, help="training patches per GPU per step")
     return ap.parse_args()
 
 
@@ -67,6 +68,23 @@ def cpu_samples_per_s(sample, steps, warmup):
     return sample * steps / dt, dt / steps * 1e3, cores
 
 
+def cpu_train_samples_per_s(batch, steps, warmup):
+    """Reference training step on the host cores: zero_grad, forward, NLL+NLL, backward (utils.py:359-373)."""
+    import torch
+    from oracle import mtl_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = O.synth_state_dict("MTL", seed=0)
+    x, yd, ye = O.synth_patches(batch, seed=1234)
+    for _ in range(warmup):
+        O.loss_and_grads(sd, x, yd, ye, "MTL")
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        O.loss_and_grads(sd, x, yd, ye, "MTL")
+    dt = time.perf_counter() - t0
+    return batch * steps / dt, dt / steps * 1e3, cores
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -83,6 +101,9 @@ def run_reference(args):
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    tval, tms, _ = cpu_train_samples_per_s(32, max(2, min(args.steps, 5)), 1)
+    line["train"] = {"value": tval, "unit": UNIT, "ms_per_step": tms, "batch": 32,
+                     "what": "reference CPU training step fwd+bwd (BASELINE.json configs[0]), oracle port"}
     print(json.dumps(line), flush=True)
 
 
@@ -98,7 +119,7 @@ class ClockSampler:
         self.rows, self.proc = [], None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -154,6 +175,59 @@ def conv_algorithmic_elems_per_sample(desc):
                 e += L["cin"] * hi * wi + L["cout"] * ho * wo
         per_op.append(e)
     return per_op
+
+
+def measure_train(args, dev, world, rank, barrier):
+    """BASELINE.json configs[2]: MTL training, per-GPU batch 256, data parallel with ONE NCCL all-reduce of the flat
+    fp32 gradient per step.  A step = weight packing + forward (batch-stat BN) + backward + all-reduce + Adam step,
+    through the drop-in module / DataParallelTrainer."""
+    import torch
+    import torch.distributed as dist
+    from mtldas_b200 import MTL_Net, synth as O
+    from mtldas_b200.ddp import DataParallelTrainer
+    nb = args.train_batch
+    m = MTL_Net()
+    m.precision = args.precision
+    m.load_state_dict(O.synth_state_dict("MTL", seed=0), strict=True)
+    m = m.to(dev).train()
+    opt = torch.optim.Adam(m.parameters(), lr=1e-3 / 1.5, weight_decay=1e-5)       # utils.py:133-134,247
+    trainer = DataParallelTrainer(m, opt)
+    base, yd, ye = O.synth_patches(64, seed=4321 + rank)
+    reps = (nb + 63) // 64
+    xh = base.repeat(reps, 1, 1, 1)[:nb].contiguous().pin_memory()
+    ydd, yed = yd.repeat(reps)[:nb].to(dev), ye.repeat(reps)[:nb].to(dev)
+    x = xh.to(dev)
+    for _ in range(3):
+        trainer.step(x, [ydd, yed])
+    barrier()
+    steps = max(3, min(args.steps, 20))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        loss = trainer.step(x, [ydd, yed])
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    # end to end: H2D of the batch from pinned memory + D2H of the loss every step
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        xd = xh.to(dev, non_blocking=True)
+        loss = trainer.step(xd, [ydd, yed])
+        lv = float(loss)
+    barrier()
+    e2e = torch.tensor([time.perf_counter() - t0], device=dev)
+    if world > 1:
+        dist.all_reduce(e2e, op=dist.ReduceOp.MAX)
+    plan = m._train_plan(dev, nb)
+    return {"value": world * nb * steps / (float(ms.item()) * 1e-3), "unit": UNIT, "ms_per_step": float(ms.item()) / steps,
+            "steps": steps, "batch_per_gpu": nb, "scaling": "weak",
+            "step": "pack weights + forward (batch-stat BN) + backward + all-reduce + Adam",
+            "allreduce_bytes_per_step": plan.n_params * 4 if world > 1 else 0,
+            "e2e": {"value": world * nb * steps / float(e2e.item()), "unit": UNIT,
+                    "h2d_bytes_per_step": nb * PATCH_BYTES, "d2h_bytes_per_step": 4},
+            "gpu_launches_per_step": plan.last_launch_count, "last_loss": lv}
 
 
 def run_ours(args):
@@ -247,6 +321,8 @@ def run_ours(args):
                 "per_op_ms": {(op.get("name") or op["op"]) + f"#{i}": round(m, 4)
                               for i, (m, op) in enumerate(zip(per_op_ms, desc["program"]))}}
 
+    train = measure_train(args, dev, world, rank, barrier)
+
     if rank == 0:
         value = world * B * args.steps / (ms_total * 1e-3)
         line = {
@@ -266,6 +342,7 @@ def run_ours(args):
             "cuda_graph": os.environ.get("MTLDAS_NO_GRAPH", "0") != "1",
             "clocks": clocks,
             "roofline": roof,
+            "train": train,
         }
         if world == 1 and not args.no_cpu_baseline:
             steps = 16
