@@ -14,6 +14,7 @@
 #include <algorithm>
 #include <climits>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <sstream>
 
@@ -32,6 +33,53 @@ namespace mtldas {
   } while (0)
 
 static inline size_t round_up_sz(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// MTLDAS_TRAIN_PROFILE=1: CUDA-event pair around every op, table of device milliseconds per op kind on stderr
+struct OpTimer {
+  bool on;
+  cudaStream_t st;
+  std::vector<cudaEvent_t> ev;
+  std::vector<int> kind;
+  explicit OpTimer(cudaStream_t s) : st(s) {
+    const char* e = getenv("MTLDAS_TRAIN_PROFILE");
+    on = e && e[0] == '1';
+  }
+  void begin(int k) {
+    if (!on) return;
+    cudaEvent_t a;
+    cudaEventCreate(&a);
+    cudaEventRecord(a, st);
+    ev.push_back(a);
+    kind.push_back(k);
+  }
+  void end() {
+    if (!on) return;
+    cudaEvent_t a;
+    cudaEventCreate(&a);
+    cudaEventRecord(a, st);
+    ev.push_back(a);
+  }
+  void report(const char* what) {
+    if (!on) return;
+    cudaStreamSynchronize(st);
+    static const char* names[] = {"stem", "conv", "stats", "finalize", "ew_fwd", "head", "head_bwd", "ew_bwd",
+                                  "bn_grad", "wgrad+unpack", "dgrad", "stem_wgrad"};
+    float tot[12] = {0};
+    int cnt[12] = {0};
+    for (size_t i = 0; i < kind.size(); ++i) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, ev[2 * i], ev[2 * i + 1]);
+      tot[kind[i]] += ms, cnt[kind[i]]++;
+    }
+    float all = 0.f;
+    for (float t : tot) all += t;
+    fprintf(stderr, "[trainprof] %s total %.3f ms:", what, all);
+    for (int k = 0; k < 12; ++k)
+      if (cnt[k]) fprintf(stderr, " %s x%d %.3f;", names[k], cnt[k], tot[k]);
+    fprintf(stderr, "\n");
+    for (auto e : ev) cudaEventDestroy(e);
+  }
+};
 
 static int clone_tensor(Plan& p, const std::string& name, int src, int layout) {
   const TensorInfo t = p.tensors[src];
@@ -409,7 +457,9 @@ int train_forward(TrainPlan& tp, const void* const* state, const float* x, int n
   tp.nb = nb, tp.x = x, tp.launches = 0;
   float* logp0 = reinterpret_cast<float*>(p.ws + tp.logp_off);
   float* logp1 = logp0 + (size_t)p.mb * 16;
+  OpTimer timer(st);
   for (auto& op : tp.fwd) {
+    timer.begin(op.kind);
     if (op.kind == TOP_STEM) {
       const TensorInfo& t = p.tensors[tp.y_stem];
       StemParams q{};
@@ -463,8 +513,10 @@ int train_forward(TrainPlan& tp, const void* const* state, const float* x, int n
       }
       CK(cudaMemcpyAsync(dst, q.out, (size_t)nb * h.classes * sizeof(float), cudaMemcpyDeviceToDevice, st));
     }
+    timer.end();
     ++tp.launches;
   }
+  timer.report("forward");
   tp.have_forward = true;
   return 0;
 }
@@ -481,7 +533,9 @@ int train_backward(TrainPlan& tp, const void* const* state, const float* dout0, 
   CK(cudaMemsetAsync(grads, 0, tp.n_params * sizeof(float), st));
   float* logp0 = reinterpret_cast<float*>(p.ws + tp.logp_off);
   float* logp1 = logp0 + (size_t)p.mb * 16;
+  OpTimer timer(st);
   for (auto& op : tp.bwd) {
+    timer.begin(op.kind);
     if (op.kind == TOP_HEADBWD) {
       const HeadOpHost& h = p.heads[op.a];
       const TensorInfo& t = p.tensors[h.in_tensor];
@@ -556,8 +610,10 @@ int train_backward(TrainPlan& tp, const void* const* state, const float* dout0, 
       u.cout = 16, u.cin = 1, u.ksize = 7, u.split = INT_MAX, u.k_off = 0, u.cout_off = 0, u.Cout_p = 16, u.K_tap = 1;
       CK(launch_unpack(u, st));
     }
+    timer.end();
     ++tp.launches;
   }
+  timer.report("backward");
   (void)state;
   return 0;
 }
