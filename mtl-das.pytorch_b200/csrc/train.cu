@@ -582,7 +582,7 @@ int train_backward(TrainPlan& tp, const void* const* state, const float* dout0, 
       q.dy = p.ws + td.offset + ((size_t)f.g[w.group].out_chunk0 * td.plane + td.g_lo) * p.gran;
       q.dy_plane_bytes = td.plane * p.gran;
       q.dw = reinterpret_cast<float*>(p.ws + w.dw_off);
-      q.ntaps = f.ntaps, q.nchunks = f.nchunks, q.Cout = f.Cout, q.body = cp.body;
+      q.ntaps = f.ntaps, q.nchunks = f.nchunks, q.Cout = f.Cout, q.body = cp.body, q.nsrc = f.nsrc;
       long long want = std::max<long long>(1, 592 / f.ntaps);
       q.slice = (int)std::max<long long>(256, (cp.body + want - 1) / want);
       q.slice = (q.slice + 31) / 32 * 32;

@@ -8,7 +8,9 @@
 //   backward: dgamma = sum(g*y_hat), dbeta = sum(g), dy = gamma*invstd*(g - mean(g) - y_hat*mean(g*y_hat));
 //   ReLU' = [out > 0]; sigmoid' = s(1-s); mask multiply: d mask = dz*feat, d feat = dz*mask;
 //   MaxPool2d(2,2,ceil): gradient to the first maximal element of the window (scan order h, w).
+#include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 
 #include "gran.cuh"
 #include "ptx.cuh"
@@ -314,6 +316,13 @@ __global__ void __launch_bounds__(256) ew_bwd_kernel(const __grid_constant__ EwP
     if (PASS == 0) {
       block_reduce8_atomic(rg, bn.red_g + c * 8, sh);
       block_reduce8_atomic(rgy, bn.red_gy + c * 8, sh);
+    } else if (f < 16) {
+      // the tensor-core weight gradient reduces 16 positions per MMA: keep [body, round_up(body,16)) zero
+      const long long full = (p.body / p.Pimgo) * p.Pimg;
+      if (full + f < (full + 15) / 16 * 16) {
+        float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        store8<T>(p.dy.base + ((long long)c * p.dy.plane + p.dy.g_lo + full + f) * G, z);
+      }
     }
     return;
   }
@@ -380,8 +389,9 @@ __global__ void __launch_bounds__(256) ew_bwd_kernel(const __grid_constant__ EwP
     if (PASS == 0) {
       block_reduce8_atomic(rg, bn.red_g + ch * 8, sh);
       block_reduce8_atomic(rgy, bn.red_gy + ch * 8, sh);
-    } else if (in_range) {
-      store8<T>(p.dy.base + ((long long)ch * p.dy.plane + p.dy.g_lo + f) * G, dyv);  // zero at pads
+    } else if (in_range || f < (p.body + 15) / 16 * 16) {
+      // zero at pads, and zero up to the next multiple of 16 positions (tensor-core wgrad granularity)
+      store8<T>(p.dy.base + ((long long)ch * p.dy.plane + p.dy.g_lo + f) * G, dyv);
     }
   }
   if (PASS == 1 && p.want_daux && in_range && !p.second) {
@@ -504,8 +514,156 @@ static cudaError_t launch_wgrad_t(const WgradParams& p, cudaStream_t st) {
   return cudaErrorInvalidValue;
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// weight gradient on tcgen05 (bf16 path):  D_t[co][ci] = sum_pos dy[pos][co] * zin[pos + off_t][ci]
+// Both operands are read from shared memory in the MN-major interleaved layout, which is exactly the P8 slab
+// [chunk][position][8 channels]: the MMA's K dimension is the POSITION axis (16 positions per instruction),
+// M = output channels (128 rows; rows >= Cout are zero), N = input channels of one tap, and a tap is again a
+// start-address shift of the B descriptor.  The accumulators of all taps of a tap group stay in TMEM for the whole
+// position slice of the CTA (grid.x = slices, grid.y = tap groups) and are added to the packed fp32 gradient
+// [tap][ci][co] with coalesced red.global.add (32 consecutive co per warp instruction).
+// ---------------------------------------------------------------------------------------------
+constexpr int kWgStage = 128;   // positions per pipeline stage
+constexpr int kWgHeader = 256;
+
+__global__ void __launch_bounds__(128) wgrad_umma_kernel(const __grid_constant__ WgradParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);  // [0,1] full, [2,3] empty, [4] acc
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 64);
+  const int Cin = p.nchunks * 8, Cout = p.Cout;
+  const int tap0 = blockIdx.y * p.taps_per_cta;
+  const int ntap = min(p.taps_per_cta, p.ntaps - tap0);
+  const uint32_t a_chunk = kWgStage * 16u;                          // dy slab: [16 chunk slots][128][16 B]
+  const uint32_t a_stage = 16u * a_chunk;
+  const int SPb = kWgStage + p.halo_lo + p.halo_hi;
+  const uint32_t b_chunk = (uint32_t)SPb * 16u;                     // zin slab: [nsrc*nchunks][SPb][16 B]
+  const uint32_t b_stage = ((uint32_t)(p.nsrc * p.nchunks) * b_chunk + 127u) & ~127u;
+  uint8_t* a_slab = smem + kWgHeader;
+  uint8_t* b_slab = a_slab + 2 * a_stage;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long f0 = (long long)blockIdx.x * p.slice;
+  const long long f1 = min(f0 + (long long)p.slice, (p.body + 15) / 16 * 16);
+  const int nstage = (int)((f1 - f0 + kWgStage - 1) / kWgStage);
+  uint32_t cols = 32;
+  while ((int)cols < ntap * Cin) cols <<= 1;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 5; ++i) ptx::mbar_init(bars + i, 1);
+    ptx::fence_mbar_init();
+  }
+  // rows >= Cout of the M = 128 operand: zero once (never overwritten by the bulk copies)
+  for (int i = threadIdx.x; i < (int)(2 * a_stage / 16); i += 128) reinterpret_cast<uint4*>(a_slab)[i] = make_uint4(0, 0, 0, 0);
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  if (warp == 1) ptx::tmem_alloc(tmem_slot, cols);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (ptx::elect_one()) {
+      for (int s = 0; s < nstage; ++s) {
+        const int b = s & 1;
+        if (s >= 2) ptx::mbar_wait(bars + 2 + b, ((s >> 1) - 1) & 1);
+        const long long fb = f0 + (long long)s * kWgStage;
+        const uint32_t bytes = (uint32_t)(Cout / 8) * a_chunk + (uint32_t)(p.nsrc * p.nchunks) * b_chunk;
+        ptx::mbar_arrive_expect_tx(bars + b, bytes);
+        for (int c = 0; c < Cout / 8; ++c)
+          ptx::bulk_g2s(a_slab + b * a_stage + c * a_chunk, p.dy + (long long)c * p.dy_plane_bytes + fb * 16, a_chunk, bars + b);
+        for (int sr = 0; sr < p.nsrc; ++sr)
+          for (int c = 0; c < p.nchunks; ++c)
+            ptx::bulk_g2s(b_slab + b * b_stage + (size_t)(sr * p.nchunks + c) * b_chunk,
+                          p.src[sr].base + (long long)c * p.src[sr].plane_bytes + (fb - p.halo_lo) * 16, b_chunk, bars + b);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (ptx::elect_one()) {
+      const uint32_t idesc = ptx::umma_idesc_bf16(128, Cin, 1, 1);
+      // MN-major interleaved: LBO = distance between 8-position groups (128 B), SBO = distance between 8-channel chunks
+      const uint64_t a_hi = ptx::umma_desc(0, 128u, a_chunk);
+      const uint64_t b_hi = ptx::umma_desc(0, 128u, b_chunk);
+      const uint32_t a16 = ptx::smem_u32(a_slab) >> 4, b16 = ptx::smem_u32(b_slab) >> 4;
+      uint32_t acc = 0u;
+      for (int s = 0; s < nstage; ++s) {
+        const int b = s & 1;
+        ptx::mbar_wait(bars + b, (s >> 1) & 1);
+        ptx::tc_fence_after();
+        const long long fb = f0 + (long long)s * kWgStage;
+        const int ksteps = (int)min((long long)(kWgStage / 16), (f1 - fb + 15) / 16);
+        for (int j = 0; j < ksteps; ++j) {
+          const uint32_t a_lo = a16 + (uint32_t)b * (a_stage >> 4) + (uint32_t)j * 16u;
+          for (int t = 0; t < ntap; ++t) {
+            const ConvTapDev tp = p.tap[tap0 + t];
+            const uint32_t b_lo = b16 + (uint32_t)b * (b_stage >> 4) + (uint32_t)(tp.src * p.nchunks) * (b_chunk >> 4) +
+                                  (uint32_t)(p.halo_lo + tp.off + j * 16);
+            ptx::umma_bf16(tmem_base + (uint32_t)(t * Cin), a_hi | a_lo, b_hi | b_lo, idesc, acc);
+          }
+          acc = 1u;
+        }
+        ptx::umma_commit(bars + 2 + b);
+      }
+      ptx::umma_commit(bars + 4);
+    }
+    __syncwarp();
+  }
+
+  // ---- epilogue: lane = output channel (row of D); columns = (tap, ci) ------------------------------
+  ptx::mbar_wait(bars + 4, 0);
+  ptx::tc_fence_after();
+  const int co = warp * 32 + lane;
+  const int K = Cin;
+  for (int t = 0; t < ntap; ++t) {
+    for (int c0 = 0; c0 < Cin; c0 += 16) {
+      uint32_t r[16];
+      ptx::tmem_ld16_issue(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * Cin + c0), r);
+      ptx::tmem_wait16(r);
+      if (co < Cout && nstage > 0) {
+        float* dst = p.dw + ((size_t)(tap0 + t) * K + c0) * Cout + co;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) atomicAdd(dst + (size_t)j * Cout, __uint_as_float(r[j]));
+      }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem_base, cols);
+}
+
+static cudaError_t launch_wgrad_umma(WgradParams p, cudaStream_t st) {
+  const int Cin = p.nchunks * 8;
+  const int tg_max = std::max(1, 512 / Cin);
+  const int ngroups = (p.ntaps + tg_max - 1) / tg_max;
+  p.taps_per_cta = (p.ntaps + ngroups - 1) / ngroups;
+  int lo = 0, hi = 0;
+  for (int t = 0; t < p.ntaps; ++t) lo = std::max(lo, -p.tap[t].off), hi = std::max(hi, p.tap[t].off);
+  p.halo_lo = lo, p.halo_hi = hi;
+  const long long body16 = (p.body + 15) / 16 * 16;
+  long long want = std::max<long long>(1, 444 / ngroups);              // about three CTAs per SM
+  long long slice = std::max<long long>(1024, (body16 + want - 1) / want);
+  p.slice = (int)((slice + kWgStage - 1) / kWgStage * kWgStage);
+  const int SPb = kWgStage + lo + hi;
+  const size_t b_stage = ((size_t)(p.nsrc * p.nchunks) * SPb * 16 + 127) & ~(size_t)127;
+  const size_t smem = kWgHeader + 2 * (size_t)16 * kWgStage * 16 + 2 * b_stage;
+  static size_t configured = 0;
+  if (smem > configured) {
+    cudaError_t e = cudaFuncSetAttribute(wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    configured = smem;
+  }
+  dim3 grid((unsigned)((body16 + p.slice - 1) / p.slice), ngroups);
+  wgrad_umma_kernel<<<grid, 128, smem, st>>>(p);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_wgrad(const WgradParams& p, int precision, cudaStream_t st) {
-  return precision == 0 ? launch_wgrad_t<__nv_bfloat16>(p, st) : launch_wgrad_t<float>(p, st);
+  if (precision == 0) {
+    const char* e = getenv("MTLDAS_WGRAD_CUDA_CORES");
+    if (!(e && e[0] == '1')) return launch_wgrad_umma(p, st);
+    return launch_wgrad_t<__nv_bfloat16>(p, st);
+  }
+  return launch_wgrad_t<float>(p, st);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -96,6 +96,8 @@ struct WgradParams {     // dW[tap][k][cout] += sum_pos zin[pos + off_tap][k] * 
   int ntaps, nchunks, Cout;  // K = 8*nchunks
   long long body;
   int slice;                 // positions per CTA
+  int nsrc;                  // sources referenced by the taps
+  int taps_per_cta, halo_lo, halo_hi;  // tensor-core kernel only (filled by the launcher)
 };
 
 struct HeadBwdParams {   // d(log_softmax(group mean(GAP(a4)))) -> d a4
