@@ -199,11 +199,10 @@ cudaError_t launch_head(const HeadParams& p, int precision, cudaStream_t stream,
 // weight packing (+ eval BatchNorm fold: w' = w*g/sqrt(rv+eps), b' = beta + (b - rm)*g/sqrt(rv+eps))
 // thread = one element of the source weight [cout, cin, k, k].
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) pack_kernel(const __grid_constant__ PackParams p) {
+__device__ __forceinline__ void pack_element(const PackParams& p, int i) {
   const PackSeg& s = p.seg;
   const int kk = s.ksize * s.ksize;
   const int total = s.cout * s.cin * kk;
-  const int i = blockIdx.x * 256 + threadIdx.x;
   if (i >= total) return;
   const int co = i / (s.cin * kk);
   const int r1 = i - co * (s.cin * kk);
@@ -237,6 +236,28 @@ __global__ void __launch_bounds__(256) pack_kernel(const __grid_constant__ PackP
     size_t e = (((size_t)tap * (p.K_tap / 8) + (k >> 3)) * p.Cout_p + cop) * 8 + (k & 7);
     reinterpret_cast<__nv_bfloat16*>(p.dst)[e] = __float2bfloat16(v);
   }
+}
+
+__global__ void __launch_bounds__(256) pack_kernel(const __grid_constant__ PackParams p) {
+  pack_element(p, blockIdx.x * 256 + threadIdx.x);
+}
+
+__global__ void __launch_bounds__(256) pack_batch_kernel(const __grid_constant__ PackBatch b) {
+  const PackParams& p = b.p[blockIdx.y];
+  const int total = p.seg.cout * p.seg.cin * p.seg.ksize * p.seg.ksize;
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) pack_element(p, i);
+}
+
+cudaError_t launch_pack_batch(const PackParams* packs, int n, cudaStream_t stream) {
+  static PackBatch b;  // host staging (32 KB kernel parameter block)
+  for (int i0 = 0; i0 < n; i0 += kPackBatch) {
+    const int m = n - i0 < kPackBatch ? n - i0 : kPackBatch;
+    for (int i = 0; i < m; ++i) b.p[i] = packs[i0 + i];
+    pack_batch_kernel<<<dim3(48, m), 256, 0, stream>>>(b);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 cudaError_t launch_pack(const PackParams& p, cudaStream_t stream) {

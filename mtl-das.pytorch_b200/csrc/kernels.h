@@ -16,6 +16,7 @@ cudaError_t launch_stem(const StemParams& p, int precision, cudaStream_t stream,
 cudaError_t launch_pool(const PoolParams& p, int precision, cudaStream_t stream, bool pdl = false);
 cudaError_t launch_head(const HeadParams& p, int precision, cudaStream_t stream, bool pdl = false);
 cudaError_t launch_pack(const PackParams& p, cudaStream_t stream);
+cudaError_t launch_pack_batch(const PackParams* packs, int n, cudaStream_t stream);
 
 // layout conversion (tests, debugging, and the autograd boundary): fp32 NCHW <-> P8 / P8S2 views
 cudaError_t launch_nchw_to_view(const float* nchw, ActView v, int nb, int C, int H, int W, int precision,

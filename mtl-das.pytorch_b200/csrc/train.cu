@@ -347,6 +347,7 @@ TrainPlan* build_train_plan(int kind, int batch, int precision) {
   tp.stem_dw_off = take(49 * 16 * sizeof(float));
   tp.zero_bwd_end = o;
   for (auto& b : tp.bns) b.f_off = take((size_t)b.C * 4 * sizeof(float));
+  tp.pack_off = o;
   for (size_t i = 0; i < p.convs.size(); ++i) {
     if (i < n_inf_convs) continue;  // inference packs are not used by the training plan
     ConvOpHost& c = p.convs[i];
@@ -355,8 +356,9 @@ TrainPlan* build_train_plan(int kind, int batch, int precision) {
       c.g[gi].bias_off = (size_t)-1;
     }
   }
-  tp.zero_bias_off = take(256 * sizeof(float));
   p.stem_w_off = take(49 * 16 * 4);
+  tp.pack_end = o;
+  tp.zero_bias_off = take(256 * sizeof(float));
   p.stem_b_off = tp.zero_bias_off;
   tp.logp_off = take((size_t)batch * 18 * sizeof(float));
   for (size_t i = n_inf_convs; i < p.convs.size(); ++i)
@@ -402,11 +404,9 @@ static EwParams ew_params(const TrainPlan& tp, const TrainPlan::EwHost& e, int n
 
 static int pack_train(TrainPlan& tp, const void* const* state, cudaStream_t st) {
   Plan& p = *tp.p;
-  for (size_t i = tp.n_inf_convs; i < p.convs.size(); ++i) {
-    const ConvOpHost& c = p.convs[i];
-    for (int gi = 0; gi < c.ngroups; ++gi)
-      CK(cudaMemsetAsync(p.ws + c.g[gi].w_off, 0, (size_t)c.ntaps * c.nchunks * 8 * c.Cout * (p.precision == 0 ? 2 : 4), st));
-  }
+  // one memset over all packed weight images (merged / channel-padded blocks keep zeros), one batched pack launch
+  CK(cudaMemsetAsync(p.ws + tp.pack_off, 0, tp.pack_end - tp.pack_off, st));
+  std::vector<PackParams> packs;
   for (size_t ci = 0; ci < (size_t)tp.n_inf_convs; ++ci) {  // forward packs: same placement as inference, no fold
     const ConvOpHost& c = p.convs[tp.fconv_of[ci]];
     for (int gi = 0; gi < c.ngroups; ++gi)
@@ -415,7 +415,7 @@ static int pack_train(TrainPlan& tp, const void* const* state, cudaStream_t st) 
         q.seg = make_seg(p, sh, state);
         q.dst = p.ws + c.g[gi].w_off, q.bias_dst = nullptr;
         q.Cout_p = c.Cout, q.K_tap = c.nchunks * 8, q.fp32 = p.precision == 0 ? 0 : 1, q.fold = 0;
-        CK(launch_pack(q, st));
+        packs.push_back(q);
       }
   }
   for (auto& dp : tp.dgrads) {
@@ -427,7 +427,7 @@ static int pack_train(TrainPlan& tp, const void* const* state, cudaStream_t st) 
       for (int t = 0; t < 9; ++t) q.seg.tap_map[t] = dp.tap_map[t];
       q.dst = p.ws + c.g[0].w_off, q.bias_dst = nullptr;
       q.Cout_p = c.Cout, q.K_tap = c.nchunks * 8, q.fp32 = p.precision == 0 ? 0 : 1, q.fold = 0;
-      CK(launch_pack(q, st));
+      packs.push_back(q);
     }
   }
   {
@@ -435,13 +435,14 @@ static int pack_train(TrainPlan& tp, const void* const* state, cudaStream_t st) 
     q.seg = make_seg(p, PackSegHost{p.stem_layer, INT_MAX, 0, 0}, state);
     q.dst = p.ws + p.stem_w_off, q.bias_dst = nullptr;
     q.Cout_p = 16, q.K_tap = 1, q.fp32 = 1, q.fold = 0;
-    CK(launch_pack(q, st));
+    packs.push_back(q);
   }
+  CK(launch_pack_batch(packs.data(), (int)packs.size(), st));
   return 0;
 }
 
-int train_forward(TrainPlan& tp, const void* const* state, const float* x, int nb, float* out0, float* out1,
-                  cudaStream_t st) {
+static int train_forward_eager(TrainPlan& tp, const void* const* state, const float* x, int nb, float* out0,
+                               float* out1, cudaStream_t st) {
   Plan& p = *tp.p;
   if (!p.ws) {
     set_error("train_forward: no workspace bound");
@@ -521,8 +522,8 @@ int train_forward(TrainPlan& tp, const void* const* state, const float* x, int n
   return 0;
 }
 
-int train_backward(TrainPlan& tp, const void* const* state, const float* dout0, const float* dout1, float* grads,
-                   cudaStream_t st) {
+static int train_backward_eager(TrainPlan& tp, const void* const* state, const float* dout0, const float* dout1,
+                                float* grads, cudaStream_t st) {
   Plan& p = *tp.p;
   if (!tp.have_forward) {
     set_error("train_backward: no forward pass to differentiate");
@@ -616,6 +617,98 @@ int train_backward(TrainPlan& tp, const void* const* state, const float* dout0, 
   timer.report("backward");
   (void)state;
   return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// CUDA-graph replay: a training step is ~125 forward + ~235 backward launches; when the same buffers come back
+// (steady-state training loop) the captured graph is replayed.  First use eager, second use captured.
+// ---------------------------------------------------------------------------------------------------------
+template <typename F>
+static int run_with_graph(TrainPlan& tp, std::vector<TrainPlan::GraphEntry>& cache, const std::vector<const void*>& key,
+                          int nb, cudaStream_t st, F&& eager) {
+  const char* ng = getenv("MTLDAS_NO_GRAPH");
+  const char* prof = getenv("MTLDAS_TRAIN_PROFILE");
+  if ((ng && ng[0] == '1') || (prof && prof[0] == '1')) return eager(st);
+  TrainPlan::GraphEntry* e = nullptr;
+  for (auto& g : cache)
+    if (g.nb == nb && g.key == key) e = &g;
+  if (!e) {
+    if (cache.size() >= 4) {
+      if (cache.front().exec) cudaGraphExecDestroy(cache.front().exec);
+      cache.erase(cache.begin());
+    }
+    cache.push_back(TrainPlan::GraphEntry{key, nb, nullptr, 0, 0});
+    e = &cache.back();
+  }
+  e->uses++;
+  if (e->exec) {
+    CK(cudaGraphLaunch(e->exec, st));
+    tp.launches = e->launches;
+    return 0;
+  }
+  if (e->uses < 2) return eager(st);
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cs) != cudaSuccess) cudaGetLastError();
+  if (cs != cudaStreamCaptureStatusNone) return eager(st);
+  if (!tp.cap_stream) CK(cudaStreamCreateWithFlags(&tp.cap_stream, cudaStreamNonBlocking));
+  CK(cudaStreamBeginCapture(tp.cap_stream, cudaStreamCaptureModeThreadLocal));
+  int rc = eager(tp.cap_stream);
+  cudaGraph_t graph = nullptr;
+  cudaError_t ce = cudaStreamEndCapture(tp.cap_stream, &graph);
+  if (rc || ce != cudaSuccess) {
+    if (graph) cudaGraphDestroy(graph);
+    cudaGetLastError();
+    if (!rc) set_error("train graph capture failed: %s", cudaGetErrorString(ce));
+    return rc ? rc : -2;
+  }
+  e->launches = tp.launches;
+  ce = cudaGraphInstantiate(&e->exec, graph, 0);
+  cudaGraphDestroy(graph);
+  if (ce != cudaSuccess) {
+    e->exec = nullptr;
+    set_error("train graph instantiate failed: %s", cudaGetErrorString(ce));
+    return -2;
+  }
+  CK(cudaGraphLaunch(e->exec, st));
+  return 0;
+}
+
+int train_forward(TrainPlan& tp, const void* const* state, const float* x, int nb, float* out0, float* out1,
+                  cudaStream_t st) {
+  Plan& p = *tp.p;
+  if (!p.ws) {
+    set_error("train_forward: no workspace bound");
+    return -3;
+  }
+  if (nb < 1 || nb > p.mb) {
+    set_error("train_forward: batch %d outside [1, %d] (BatchNorm statistics need the whole batch in one pass)", nb, p.mb);
+    return -1;
+  }
+  std::vector<const void*> key{x, out0, out1};
+  for (size_t i = 0; i < p.state_keys.size(); ++i) key.push_back(state[i]);
+  int rc = run_with_graph(tp, tp.fwd_graphs, key, nb, st,
+                          [&](cudaStream_t s) { return train_forward_eager(tp, state, x, nb, out0, out1, s); });
+  if (!rc) tp.nb = nb, tp.x = x, tp.have_forward = true;
+  return rc;
+}
+
+int train_backward(TrainPlan& tp, const void* const* state, const float* dout0, const float* dout1, float* grads,
+                   cudaStream_t st) {
+  if (!tp.have_forward) {
+    set_error("train_backward: no forward pass to differentiate");
+    return -3;
+  }
+  std::vector<const void*> key{dout0, dout1, grads, tp.x};
+  return run_with_graph(tp, tp.bwd_graphs, key, tp.nb, st,
+                        [&](cudaStream_t s) { return train_backward_eager(tp, state, dout0, dout1, grads, s); });
+}
+
+TrainPlan::~TrainPlan() {
+  for (auto* c : {&fwd_graphs, &bwd_graphs})
+    for (auto& g : *c)
+      if (g.exec) cudaGraphExecDestroy(g.exec);
+  if (cap_stream) cudaStreamDestroy(cap_stream);
+  delete p;
 }
 
 }  // namespace mtldas

@@ -62,13 +62,21 @@ struct TrainPlan {
   std::set<long long> written;
   int y_stem = -1, bn_stem = -1, ew_stem = -1, dy_stem = -1, n_inf_convs = 0;
   size_t zero_fwd_off = 0, zero_fwd_end = 0, zero_bwd_off = 0, zero_bwd_end = 0;
-  size_t stem_dw_off = 0, zero_bias_off = 0, logp_off = 0;
+  size_t stem_dw_off = 0, zero_bias_off = 0, logp_off = 0, pack_off = 0, pack_end = 0;
+  struct GraphEntry {
+    std::vector<const void*> key;
+    int nb;
+    cudaGraphExec_t exec;
+    int uses, launches;
+  };
+  std::vector<GraphEntry> fwd_graphs, bwd_graphs;
+  cudaStream_t cap_stream = nullptr;
   // state of the last forward
   int nb = 0, launches = 0;
   const float* x = nullptr;
   bool have_forward = false;
 
-  ~TrainPlan() { delete p; }
+  ~TrainPlan();
 };
 
 TrainPlan* build_train_plan(int kind, int batch, int precision);

@@ -126,4 +126,9 @@ struct PackParams {
   float eps;
 };
 
+constexpr int kPackBatch = 128;
+struct PackBatch {          // many independent packs in one launch (blockIdx.y selects the entry)
+  PackParams p[kPackBatch];
+};
+
 }  // namespace mtldas
