@@ -70,8 +70,20 @@ int mtldas_plan_bind_workspace(mtldas_plan* plan, void* dev_workspace, size_t by
     set_error("bind_workspace: %s", cudaGetErrorString(e));
     return MTLDAS_ERR_CUDA;
   }
-  plan->p->ws = (char*)dev_workspace;
-  plan->p->packed = false;
+  Plan& pp = *plan->p;
+  if (!pp.copy_stream) {  // created once here so that the forward entry points never create anything
+    bool ok = cudaStreamCreateWithFlags(&pp.copy_stream, cudaStreamNonBlocking) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&pp.ev_start, cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 0; i < 2 && ok; ++i)
+      ok = cudaEventCreateWithFlags(&pp.ev_h2d[i], cudaEventDisableTiming) == cudaSuccess &&
+           cudaEventCreateWithFlags(&pp.ev_comp[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) {
+      set_error("bind_workspace: could not create the copy stream / events");
+      return MTLDAS_ERR_CUDA;
+    }
+  }
+  pp.ws = (char*)dev_workspace;
+  pp.packed = false;
   return 0;
 }
 
@@ -122,33 +134,42 @@ int mtldas_plan_forward_eval_host(mtldas_plan* plan, const float* host_x, int n,
   }
   cudaStream_t st = (cudaStream_t)stream;
   const int c0 = p.heads[0].classes, c1 = p.heads.size() > 1 ? p.heads[1].classes : 0;
-  float* xs = reinterpret_cast<float*>(p.ws + p.x_stage_off);
-  float* o0 = reinterpret_cast<float*>(p.ws + p.out_stage_off);
-  float* o1 = o0 + (size_t)p.mb * 16;
-  int launches = 0;
-  for (int s = 0; s < n; s += p.mb) {
+  const size_t xslot = (size_t)p.mb * kPatchH * kPatchW;
+  float* xs[2] = {reinterpret_cast<float*>(p.ws + p.x_stage_off), reinterpret_cast<float*>(p.ws + p.x_stage_off) + xslot};
+  float* o0[2] = {reinterpret_cast<float*>(p.ws + p.out_stage_off),
+                  reinterpret_cast<float*>(p.ws + p.out_stage_off) + (size_t)p.mb * 18};
+  float* o1[2] = {o0[0] + (size_t)p.mb * 16, o0[1] + (size_t)p.mb * 16};
+#define CKH(call)                                                        \
+  do {                                                                   \
+    cudaError_t e_ = (call);                                             \
+    if (e_ != cudaSuccess) {                                             \
+      set_error("forward_eval_host: %s: %s", #call, cudaGetErrorString(e_)); \
+      return MTLDAS_ERR_CUDA;                                            \
+    }                                                                    \
+  } while (0)
+  // Two staging slots: the copy stream brings pass i+1 in while the caller's stream computes pass i.
+  CKH(cudaEventRecord(p.ev_start, st));
+  CKH(cudaStreamWaitEvent(p.copy_stream, p.ev_start, 0));
+  int launches = 0, i = 0;
+  for (int s = 0; s < n; s += p.mb, ++i) {
     const int nb = n - s < p.mb ? n - s : p.mb;
-    cudaError_t e = cudaMemcpyAsync(xs, host_x + (size_t)s * kPatchH * kPatchW, (size_t)nb * kPatchH * kPatchW * 4,
-                                    cudaMemcpyHostToDevice, st);
-    if (e == cudaSuccess) {
-      int rc = plan_forward_eval(p, xs, nb, o0, c1 ? o1 : nullptr, st);
-      if (rc) return rc;
-      launches += p.last_launches;
-      e = cudaMemcpyAsync(host_out0 + (size_t)s * c0, o0, (size_t)nb * c0 * 4, cudaMemcpyDeviceToHost, st);
-    }
-    if (e == cudaSuccess && c1 && host_out1)
-      e = cudaMemcpyAsync(host_out1 + (size_t)s * c1, o1, (size_t)nb * c1 * 4, cudaMemcpyDeviceToHost, st);
-    if (e != cudaSuccess) {
-      set_error("forward_eval_host: %s", cudaGetErrorString(e));
-      return MTLDAS_ERR_CUDA;
-    }
+    const int slot = i & 1;
+    if (i >= 2) CKH(cudaStreamWaitEvent(p.copy_stream, p.ev_comp[slot], 0));  // slot free again
+    CKH(cudaMemcpyAsync(xs[slot], host_x + (size_t)s * kPatchH * kPatchW, (size_t)nb * kPatchH * kPatchW * 4,
+                        cudaMemcpyHostToDevice, p.copy_stream));
+    CKH(cudaEventRecord(p.ev_h2d[slot], p.copy_stream));
+    CKH(cudaStreamWaitEvent(st, p.ev_h2d[slot], 0));
+    int rc = plan_forward_eval(p, xs[slot], nb, o0[slot], c1 ? o1[slot] : nullptr, st);
+    if (rc) return rc;
+    launches += p.last_launches;
+    CKH(cudaEventRecord(p.ev_comp[slot], st));
+    CKH(cudaMemcpyAsync(host_out0 + (size_t)s * c0, o0[slot], (size_t)nb * c0 * 4, cudaMemcpyDeviceToHost, st));
+    if (c1 && host_out1)
+      CKH(cudaMemcpyAsync(host_out1 + (size_t)s * c1, o1[slot], (size_t)nb * c1 * 4, cudaMemcpyDeviceToHost, st));
   }
   p.last_launches = launches;
-  cudaError_t e = cudaStreamSynchronize(st);
-  if (e != cudaSuccess) {
-    set_error("forward_eval_host: %s", cudaGetErrorString(e));
-    return MTLDAS_ERR_CUDA;
-  }
+  CKH(cudaStreamSynchronize(st));
+#undef CKH
   return 0;
 }
 

@@ -354,8 +354,8 @@ Plan* build_plan(int kind, int mb, int precision) {
     }
   p.stem_w_off = take(49 * 16 * 4);
   p.stem_b_off = take(16 * 4);
-  p.x_stage_off = take((size_t)mb * kPatchH * kPatchW * 4);
-  p.out_stage_off = take((size_t)mb * 18 * 4);
+  p.x_stage_off = take((size_t)2 * mb * kPatchH * kPatchW * 4);  // two slots: H2D of pass i+1 overlaps pass i
+  p.out_stage_off = take((size_t)2 * mb * 18 * 4);
   p.ws_bytes = off;
   return pp;
 }
@@ -571,6 +571,9 @@ Plan::~Plan() {
   for (auto& g : graphs)
     if (g.exec) cudaGraphExecDestroy(g.exec);
   if (cap_stream) cudaStreamDestroy(cap_stream);
+  if (copy_stream) cudaStreamDestroy(copy_stream);
+  for (auto e : {ev_start, ev_h2d[0], ev_h2d[1], ev_comp[0], ev_comp[1]})
+    if (e) cudaEventDestroy(e);
 }
 
 // The layer program is ~36 launches per micro-batch pass (576 for a 4096 batch): replaying it as one CUDA graph

@@ -99,6 +99,9 @@ struct Plan {
   int use_graphs = 1;
   int use_pdl = 1;
   cudaStream_t cap_stream = nullptr;
+  // host entry point: private copy stream and events so that the H2D of pass i+1 overlaps the compute of pass i
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_start = nullptr, ev_h2d[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr};
   ~Plan();
 
   int find_tensor(const std::string& n) const;

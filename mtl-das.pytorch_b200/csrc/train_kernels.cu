@@ -155,14 +155,19 @@ cudaError_t launch_bn_grad(const BnGradParams& p, cudaStream_t st) {
 // thread = (position, chunk-of-a-task); EW_SIGMOID_MUL loops over the tasks that share the feature map;
 // EW_RELU_POOL: thread = (pooled position, chunk).
 // ---------------------------------------------------------------------------------------------
+#ifndef MTLDAS_EW_PPT
+#define MTLDAS_EW_PPT 1
+#endif
+constexpr int kEwPpt = MTLDAS_EW_PPT;  // positions per thread (per-channel BatchNorm constants are loaded once per thread)
+
 template <typename T>
 __global__ void __launch_bounds__(256) ew_fwd_kernel(const __grid_constant__ EwParams p) {
-  const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
-  if (idx >= p.body * p.nchunks) return;
-  const int c = (int)(idx / p.body);
-  const int f = (int)(idx - (long long)c * p.body);
   constexpr int G = Gran<T>::bytes;
   if (p.mode == EW_RELU_POOL) {
+    const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (idx >= p.body * p.nchunks) return;
+    const int c = (int)(idx / p.body);
+    const int f = (int)(idx - (long long)c * p.body);
     const Pos o = decode(f, p.Pimgo, p.Wpo, p.Ho, p.Wo);
     float m[8];
 #pragma unroll
@@ -189,47 +194,63 @@ __global__ void __launch_bounds__(256) ew_fwd_kernel(const __grid_constant__ EwP
     store8<T>(view_addr<T>(p.out, c, f, o.n, o.h, o.w), m);
     return;
   }
-  const Pos q = decode(f, p.Pimg, p.Wp, p.H, p.W);
-  if (!q.valid && p.out.layout != LAY_P8) return;
-  float aux[8];
-  if (q.valid && (p.mode == EW_ADD_RELU_ID || p.mode == EW_SIGMOID_MUL)) load8<T>(view_addr<T>(p.aux, c, f, q.n, q.h, q.w), aux);
+  // thread = chunk c (of a task) x kEwPpt positions 256 apart; a block covers 1024 consecutive positions of one chunk
+  const long long per_chunk = (p.body + 256 * kEwPpt - 1) / (256 * kEwPpt) * (256 * kEwPpt);
+  const long long base = (long long)blockIdx.x * (256 * kEwPpt) + threadIdx.x;
+  const int c = (int)(base / per_chunk);
+  const int f0 = (int)(base - (long long)c * per_chunk);
   for (int t = 0; t < p.ntasks; ++t) {
     const int ch = t * p.nchunks + c;
-    float z[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) z[j] = 0.f;
-    if (q.valid) {
-      float v[8], sc[8], sh[8];
-      load8<T>(p.y.base + ((long long)ch * p.y.plane + p.y.g_lo + f) * G, v);
-      load_affine(p.bn.scale, ch * 8, sc);
-      load_affine(p.bn.shift, ch * 8, sh);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = fmaf(v[j], sc[j], sh[j]);
-      if (p.mode == EW_RELU) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) z[j] = fmaxf(v[j], 0.f);
-      } else if (p.mode == EW_ADD_RELU_ID) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) z[j] = fmaxf(v[j] + aux[j], 0.f);
-      } else if (p.mode == EW_ADD_RELU_SC) {
-        float v2[8];
-        load8<T>(p.y2.base + ((long long)ch * p.y2.plane + p.y2.g_lo + f) * G, v2);
-        load_affine(p.bn2.scale, ch * 8, sc);
-        load_affine(p.bn2.shift, ch * 8, sh);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) z[j] = fmaxf(v[j] + fmaf(v2[j], sc[j], sh[j]), 0.f);
-      } else {  // EW_SIGMOID_MUL
-#pragma unroll
-        for (int j = 0; j < 8; ++j) z[j] = aux[j] / (1.f + expf(-v[j]));
-      }
+    float sc[8], sh[8], s2[8], h2[8];
+    load_affine(p.bn.scale, ch * 8, sc);
+    load_affine(p.bn.shift, ch * 8, sh);
+    if (p.mode == EW_ADD_RELU_SC) {
+      load_affine(p.bn2.scale, ch * 8, s2);
+      load_affine(p.bn2.shift, ch * 8, h2);
     }
-    store8<T>(view_addr<T>(p.out, ch, f, q.n, q.h, q.w), z);
+#pragma unroll
+    for (int i = 0; i < kEwPpt; ++i) {
+      const int f = f0 + i * 256;
+      if (f >= p.body) continue;
+      const Pos q = decode(f, p.Pimg, p.Wp, p.H, p.W);
+      if (!q.valid && p.out.layout != LAY_P8) continue;
+      float z[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) z[j] = 0.f;
+      if (q.valid) {
+        float v[8];
+        load8<T>(p.y.base + ((long long)ch * p.y.plane + p.y.g_lo + f) * G, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = fmaf(v[j], sc[j], sh[j]);
+        if (p.mode == EW_RELU) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) z[j] = fmaxf(v[j], 0.f);
+        } else if (p.mode == EW_ADD_RELU_SC) {
+          float v2[8];
+          load8<T>(p.y2.base + ((long long)ch * p.y2.plane + p.y2.g_lo + f) * G, v2);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) z[j] = fmaxf(v[j] + fmaf(v2[j], s2[j], h2[j]), 0.f);
+        } else {
+          float aux[8];
+          load8<T>(view_addr<T>(p.aux, c, f, q.n, q.h, q.w), aux);
+          if (p.mode == EW_ADD_RELU_ID) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) z[j] = fmaxf(v[j] + aux[j], 0.f);
+          } else {  // EW_SIGMOID_MUL
+#pragma unroll
+            for (int j = 0; j < 8; ++j) z[j] = aux[j] / (1.f + expf(-v[j]));
+          }
+        }
+      }
+      store8<T>(view_addr<T>(p.out, ch, f, q.n, q.h, q.w), z);
+    }
   }
 }
 
 cudaError_t launch_ew_fwd(const EwParams& p, int precision, cudaStream_t st) {
   const long long total = p.body * p.nchunks;
-  const unsigned grid = (unsigned)((total + 255) / 256);
+  const unsigned grid = p.mode == EW_RELU_POOL ? (unsigned)((total + 255) / 256)
+                                               : (unsigned)((p.body + 256 * kEwPpt - 1) / (256 * kEwPpt) * p.nchunks);
   if (precision == 0)
     ew_fwd_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(p);
   else
@@ -244,9 +265,11 @@ cudaError_t launch_ew_fwd(const EwParams& p, int precision, cudaStream_t st) {
 template <typename T, int PASS>
 __global__ void __launch_bounds__(256) ew_bwd_kernel(const __grid_constant__ EwParams p) {
   __shared__ float sh[8][8];
-  // a block never straddles two chunks: the launcher pads body to a multiple of 256 per chunk (see launch)
-  const long long per_chunk = (p.body + 255) / 256 * 256;
-  const long long idx2 = (long long)blockIdx.x * 256 + threadIdx.x;
+  // a block never straddles two chunks: pool mode covers 256 pooled positions per block, the other modes 1024
+  // positions (kEwPpt per thread); the launcher sizes the grid accordingly
+  const int span = p.mode == EW_RELU_POOL ? 256 : 256 * kEwPpt;
+  const long long per_chunk = (p.body + span - 1) / span * span;
+  const long long idx2 = (long long)blockIdx.x * span + threadIdx.x;
   const int c = (int)(idx2 / per_chunk);
   const int f = (int)(idx2 - (long long)c * per_chunk);
   const bool in_range = f < p.body;
@@ -327,90 +350,111 @@ __global__ void __launch_bounds__(256) ew_bwd_kernel(const __grid_constant__ EwP
     return;
   }
 
-  const Pos q = decode(in_range ? f : 0, p.Pimg, p.Wp, p.H, p.W);
-  const bool valid = in_range && q.valid;
-  float aux[8], dacc[8];
+  // non-pool modes: thread = chunk c x kEwPpt positions (f, f+256, ...) of a 1024-position block
+  float dacc[kEwPpt][8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) dacc[j] = 0.f, aux[j] = 0.f;
-  if (valid && (p.mode == EW_ADD_RELU_ID || p.mode == EW_SIGMOID_MUL)) load8<T>(view_addr<T>(p.aux, c, f, q.n, q.h, q.w), aux);
+  for (int i = 0; i < kEwPpt; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dacc[i][j] = 0.f;
+  const int body16 = (int)((p.body + 15) / 16 * 16);
   for (int t = 0; t < p.ntasks; ++t) {
     const int ch = t * p.nchunks + c;
-    float rg[8], rgy[8], dyv[8];
+    float sc[8], shf[8], mu[8], is[8], s2[8], h2[8], cg[8], cgy[8], rg[8], rgy[8];
+    load_affine(bn.scale, ch * 8, sc);
+    load_affine(bn.shift, ch * 8, shf);
+    load_affine(bn.mean, ch * 8, mu);
+    load_affine(bn.invstd, ch * 8, is);
+    if (p.mode == EW_ADD_RELU_SC) {
+      const BnArrays& bo = p.second ? p.bn : p.bn2;
+      load_affine(bo.scale, ch * 8, s2);
+      load_affine(bo.shift, ch * 8, h2);
+    }
+    if (PASS == 1) {
+      load_affine_d(bn.red_g, ch * 8, p.inv_n, cg);
+      load_affine_d(bn.red_gy, ch * 8, p.inv_n, cgy);
+    }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) rg[j] = rgy[j] = dyv[j] = 0.f;
-    if (valid) {
-      float y[8], sc[8], shf[8], mu[8], is[8], dzv[8], v[8];
-      load8<T>(ym.base + ((long long)ch * ym.plane + ym.g_lo + f) * G, y);
-      load_affine(bn.scale, ch * 8, sc);
-      load_affine(bn.shift, ch * 8, shf);
-      load_affine(bn.mean, ch * 8, mu);
-      load_affine(bn.invstd, ch * 8, is);
-      load8<T>(view_addr<T>(p.dz, ch, f, q.n, q.h, q.w), dzv);
+    for (int j = 0; j < 8; ++j) rg[j] = rgy[j] = 0.f;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = fmaf(y[j], sc[j], shf[j]);
-      float g[8];
-      if (p.mode == EW_RELU) {
+    for (int i = 0; i < kEwPpt; ++i) {
+      const int fi = f + i * 256;
+      const bool in_r = fi < p.body;
+      const Pos q = decode(in_r ? fi : 0, p.Pimg, p.Wp, p.H, p.W);
+      const bool valid = in_r && q.valid;
+      float dyv[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) g[j] = v[j] > 0.f ? dzv[j] : 0.f;
-      } else if (p.mode == EW_ADD_RELU_ID) {
+      for (int j = 0; j < 8; ++j) dyv[j] = 0.f;
+      if (valid) {
+        float y[8], dzv[8], g[8];
+        load8<T>(ym.base + ((long long)ch * ym.plane + ym.g_lo + fi) * G, y);
+        load8<T>(view_addr<T>(p.dz, ch, fi, q.n, q.h, q.w), dzv);
+        if (p.mode == EW_RELU) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) g[j] = (v[j] + aux[j]) > 0.f ? dzv[j] : 0.f;
+          for (int j = 0; j < 8; ++j) g[j] = fmaf(y[j], sc[j], shf[j]) > 0.f ? dzv[j] : 0.f;
+        } else if (p.mode == EW_ADD_RELU_SC) {
+          const ActView& yo = p.second ? p.y : p.y2;
+          float y2[8];
+          load8<T>(yo.base + ((long long)ch * yo.plane + yo.g_lo + fi) * G, y2);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) dacc[j] = g[j];
-      } else if (p.mode == EW_ADD_RELU_SC) {
-        // the other branch's normalised value completes the pre-activation
-        const BnArrays& bo = p.second ? p.bn : p.bn2;
-        const ActView& yo = p.second ? p.y : p.y2;
-        float y2[8], s2[8], h2[8];
-        load8<T>(yo.base + ((long long)ch * yo.plane + yo.g_lo + f) * G, y2);
-        load_affine(bo.scale, ch * 8, s2);
-        load_affine(bo.shift, ch * 8, h2);
+          for (int j = 0; j < 8; ++j) g[j] = (fmaf(y[j], sc[j], shf[j]) + fmaf(y2[j], s2[j], h2[j])) > 0.f ? dzv[j] : 0.f;
+        } else {
+          float aux[8];
+          load8<T>(view_addr<T>(p.aux, c, fi, q.n, q.h, q.w), aux);
+          if (p.mode == EW_ADD_RELU_ID) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) g[j] = (v[j] + fmaf(y2[j], s2[j], h2[j])) > 0.f ? dzv[j] : 0.f;
-      } else {  // EW_SIGMOID_MUL
+            for (int j = 0; j < 8; ++j) {
+              g[j] = (fmaf(y[j], sc[j], shf[j]) + aux[j]) > 0.f ? dzv[j] : 0.f;
+              dacc[i][j] = g[j];
+            }
+          } else {  // EW_SIGMOID_MUL
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float s = 1.f / (1.f + expf(-v[j]));
-          g[j] = dzv[j] * aux[j] * s * (1.f - s);
-          dacc[j] = fmaf(dzv[j], s, dacc[j]);
+            for (int j = 0; j < 8; ++j) {
+              const float sg = 1.f / (1.f + expf(-fmaf(y[j], sc[j], shf[j])));
+              g[j] = dzv[j] * aux[j] * sg * (1.f - sg);
+              dacc[i][j] = fmaf(dzv[j], sg, dacc[i][j]);
+            }
+          }
+        }
+        if (PASS == 0) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) rg[j] += g[j], rgy[j] = fmaf(g[j], (y[j] - mu[j]) * is[j], rgy[j]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) dyv[j] = sc[j] * (g[j] - cg[j] - (y[j] - mu[j]) * is[j] * cgy[j]);
         }
       }
-      if (PASS == 0) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) rg[j] = g[j], rgy[j] = g[j] * (y[j] - mu[j]) * is[j];
-      } else {
-        float cg[8], cgy[8];
-        load_affine_d(bn.red_g, ch * 8, p.inv_n, cg);
-        load_affine_d(bn.red_gy, ch * 8, p.inv_n, cgy);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) dyv[j] = sc[j] * (g[j] - cg[j] - (y[j] - mu[j]) * is[j] * cgy[j]);
-      }
+      // zero at pads, and zero up to the next multiple of 16 positions (tensor-core wgrad granularity)
+      if (PASS == 1 && fi < body16) store8<T>(p.dy.base + ((long long)ch * p.dy.plane + p.dy.g_lo + fi) * G, dyv);
     }
     if (PASS == 0) {
       block_reduce8_atomic(rg, bn.red_g + ch * 8, sh);
       block_reduce8_atomic(rgy, bn.red_gy + ch * 8, sh);
-    } else if (in_range || f < (p.body + 15) / 16 * 16) {
-      // zero at pads, and zero up to the next multiple of 16 positions (tensor-core wgrad granularity)
-      store8<T>(p.dy.base + ((long long)ch * p.dy.plane + p.dy.g_lo + f) * G, dyv);
     }
   }
-  if (PASS == 1 && p.want_daux && in_range && !p.second) {
-    if (valid || p.daux.layout == LAY_P8) {
-      char* a = view_addr<T>(p.daux, c, f, q.n, q.h, q.w);
-      if (p.daux_accum && valid) {
+  if (PASS == 1 && p.want_daux && !p.second) {
+#pragma unroll
+    for (int i = 0; i < kEwPpt; ++i) {
+      const int fi = f + i * 256;
+      if (fi >= p.body) continue;
+      const Pos q = decode(fi, p.Pimg, p.Wp, p.H, p.W);
+      if (!(q.valid || p.daux.layout == LAY_P8)) continue;
+      char* a = view_addr<T>(p.daux, c, fi, q.n, q.h, q.w);
+      if (p.daux_accum) {
+        if (!q.valid) continue;
         float old[8];
         load8<T>(a, old);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) dacc[j] += old[j];
+        for (int j = 0; j < 8; ++j) dacc[i][j] += old[j];
       }
-      if (!p.daux_accum || valid) store8<T>(a, dacc);
+      store8<T>(a, dacc[i]);
     }
   }
 }
 
 cudaError_t launch_ew_bwd(const EwParams& p, int pass, int precision, cudaStream_t st) {
-  const long long per_chunk = (p.body + 255) / 256 * 256;
-  const unsigned grid = (unsigned)(per_chunk * p.nchunks / 256);
+  const int span = p.mode == EW_RELU_POOL ? 256 : 256 * kEwPpt;
+  const long long per_chunk = (p.body + span - 1) / span * span;
+  const unsigned grid = (unsigned)(per_chunk * p.nchunks / span);
   if (precision == 0) {
     if (pass == 0)
       ew_bwd_kernel<__nv_bfloat16, 0><<<grid, 256, 0, st>>>(p);
