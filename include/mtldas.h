@@ -166,6 +166,15 @@ MTLDAS_API int mtldas_train_last_launch_count(const mtldas_train* t);
 MTLDAS_API int mtldas_train_read_tensor(mtldas_train* t, const char* name, int nb, float* dev_out_nchw, void* stream);
 MTLDAS_API size_t mtldas_train_describe(const mtldas_train* t, char* buf, size_t cap);
 
+/* streaming inference over a large DAS array --------------------------------------------------------
+ * No counterpart in the reference (its README only motivates it): cuts the [100 x 250] patches the
+ * network expects (utils.py:128) out of dev_array [n_channels, n_time] fp32 row-major: window wi covers fibre
+ * channels first_channel + wi*window_stride .. +100, time block tb covers samples tb*250 .. +250
+ * (n_time / 250 full blocks); dev_patches receives [n_windows * (n_time/250), 1, 100, 250], window-major.
+ * Shard windows across GPUs with no collective (mtldas_b200.ddp.shard_windows). */
+MTLDAS_API int mtldas_window_gather(const float* dev_array, long long n_channels, long long n_time, int first_channel,
+                                    int window_stride, int n_windows, float* dev_patches, void* stream);
+
 /* tcgen05 descriptor self-test: runs one 128xNx16 UMMA on known operands under the descriptor
  * conventions the library uses and returns the max abs error (or <0 on error). */
 MTLDAS_API float mtldas_umma_selftest(int n_cols, int row_shift, int swap_lbo_sbo);

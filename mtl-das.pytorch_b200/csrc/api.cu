@@ -46,6 +46,8 @@ mtldas_plan* mtldas_plan_create(int model_kind, int micro_batch, int precision) 
   h->p->use_graphs = (ng && ng[0] == '1') ? 0 : 1;
   const char* np = getenv("MTLDAS_NO_PDL");
   h->p->use_pdl = (np && np[0] == '1') ? 0 : 1;
+  const char* npz = getenv("MTLDAS_NO_PERSIST");
+  h->p->use_persist = (npz && npz[0] == '1') ? 0 : 1;
   return h;
 }
 void mtldas_plan_destroy(mtldas_plan* plan) {
@@ -195,6 +197,22 @@ int mtldas_conv2d_nchw(const float* dev_x, const float* dev_x2, const float* dev
   const char* sw = getenv("MTLDAS_UMMA_SWAP_DESC");
   return single_conv(dev_x, dev_x2, dev_weight, dev_bias, dev_aux, dev_out, n, cin, cin2, h, w, cout, ksize, stride,
                      epilogue, precision, aux_phase_split, (sw && sw[0] == '1') ? 1 : 0);
+}
+
+int mtldas_window_gather(const float* dev_array, long long n_channels, long long n_time, int first_channel,
+                         int window_stride, int n_windows, float* dev_patches, void* stream) {
+  if (!dev_array || !dev_patches || n_windows < 0 || window_stride < 1 || first_channel < 0 || n_time < kPatchW ||
+      (long long)first_channel + (long long)(n_windows > 0 ? n_windows - 1 : 0) * window_stride + kPatchH > n_channels) {
+    set_error("window_gather: windows do not fit the array");
+    return MTLDAS_ERR_ARG;
+  }
+  cudaError_t e = launch_window_gather(dev_array, n_time, first_channel, window_stride, n_windows,
+                                       (int)(n_time / kPatchW), dev_patches, (cudaStream_t)stream);
+  if (e != cudaSuccess) {
+    set_error("window_gather: %s", cudaGetErrorString(e));
+    return MTLDAS_ERR_CUDA;
+  }
+  return 0;
 }
 
 float mtldas_umma_selftest(int n_cols, int row_shift, int swap_lbo_sbo) {

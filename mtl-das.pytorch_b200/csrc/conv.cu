@@ -15,7 +15,9 @@
 // Reference ops replaced: nn.Conv2d (+BatchNorm2d eval fold) + ReLU / residual add / Sigmoid * feature,
 // /root/reference/model/modelA_MTL.py:12-32 (ResBlock), :42-50 (att_generator), :101-113 (output layers),
 // :144,151,157,163 (mask multiply), :149,155,161 (torch.cat -> two sources).
+#include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cuda_bf16.h>
 
 #include "gran.cuh"
@@ -213,6 +215,10 @@ __global__ void __launch_bounds__(128, 6) conv_umma_kernel(const __grid_constant
       const uint32_t a_kstep = 2u * chunk16, b_kstep = 2u * (uint32_t)p.Cout;
       const uint32_t tap16 = (uint32_t)p.tap_bytes >> 4, stage16 = stage_bytes >> 4;
       const int MT = p.MT, KC2 = p.nchunks >> 1, Cout = p.Cout, ntaps = p.ntaps;
+      uint32_t tap_off[kMaxTaps];  // per-tap slab offsets in registers (no parameter-block loads in the issue loop)
+#pragma unroll
+      for (int t = 0; t < kMaxTaps; ++t)
+        tap_off[t] = t < ntaps ? (uint32_t)(p.tap[t].src * p.nchunks) * chunk16 + (uint32_t)(p.halo_lo + p.tap[t].off) : 0u;
       ptx::mbar_wait(bars + kBarSlab, 0);
       ptx::tc_fence_after();
       DBG(2)
@@ -224,15 +230,16 @@ __global__ void __launch_bounds__(128, 6) conv_umma_kernel(const __grid_constant
           const uint32_t d_tmem = tmem_base + (uint32_t)(mt * Cout);
           uint32_t acc = 0u;
           uint32_t b_lo = wring16;
-          for (int t = 0; t < ntaps; ++t) {
-            const ConvTapDev tp = p.tap[t];
-            uint32_t a_lo = slab16 + (uint32_t)(tp.src * p.nchunks) * chunk16 +
-                            (uint32_t)(p.halo_lo + tp.off + mt * kTileM);
-            for (int k = 0; k < KC2; ++k) {
-              ptx::umma_bf16(d_tmem, a_hi | a_lo, b_hi | b_lo, idesc, acc);
-              acc = 1u;
-              a_lo += a_kstep;
-              b_lo += b_kstep;
+#pragma unroll
+          for (int t = 0; t < kMaxTaps; ++t) {
+            if (t < ntaps) {
+              uint32_t a_lo = slab16 + tap_off[t] + (uint32_t)(mt * kTileM);
+              for (int k = 0; k < KC2; ++k) {
+                ptx::umma_bf16(d_tmem, a_hi | a_lo, b_hi | b_lo, idesc, acc);
+                acc = 1u;
+                a_lo += a_kstep;
+                b_lo += b_kstep;
+              }
             }
           }
           ptx::umma_commit(bars + kBarAcc + mt);
@@ -331,6 +338,211 @@ __global__ void __launch_bounds__(128, 6) conv_umma_kernel(const __grid_constant
 }
 
 // ---------------------------------------------------------------------------------------------
+// persistent, pipelined variant for layers whose packed weights stay resident in shared memory.
+// One CTA loops over tiles (tile = blockIdx.x + k*gridDim.x).  Warp 0: producer (weights once, then a ring of
+// input slabs); warp 1: MMA issuer into one of two TMEM accumulator sets; warps 2..9: epilogue (two warps per
+// TMEM lane quarter, accumulator tiles split between them).  The tensor pipe, the bulk-copy engine and the
+// epilogue warps of different tiles overlap inside the CTA instead of relying on CTA-level concurrency.
+// ---------------------------------------------------------------------------------------------
+constexpr int kPersistThreads = 320;
+constexpr int kPBarW = 0, kPBarSlabFull = 1, kPBarSlabEmpty = 4, kPBarAccFull = 7, kPBarAccEmpty = 9;  // 8-byte slots
+
+__device__ __forceinline__ int fast_div(int f, unsigned long long magic) {
+  return (int)(((unsigned long long)(unsigned)f * magic) >> 40);
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(const __grid_constant__ ConvParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const ConvGroupDev& g = p.g[blockIdx.y];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 192);
+  float* bias_s = reinterpret_cast<float*>(smem + 256);
+  uint8_t* wsm = smem + kSmemHeader;
+  const uint32_t w_bytes = (uint32_t)(p.ntaps * p.tap_bytes);
+  const uint32_t chunk_bytes = (uint32_t)p.SP * 16u;
+  const uint32_t slab_bytes = (uint32_t)(p.nsrc * p.nchunks) * chunk_bytes;
+  const uint32_t slab_stride = (slab_bytes + 127u) & ~127u;
+  uint8_t* slabs = wsm + ((w_bytes + 127u) & ~127u);
+  const int S = p.persist_stages;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tile_pos = p.MT * kTileM;
+  const int ntiles = (int)((p.body + tile_pos - 1) / tile_pos);
+  const uint32_t acc_cols = (uint32_t)(p.MT * p.Cout);
+  const int nsets = p.acc_sets;                       // 1 or 2 TMEM accumulator sets
+  const int nepi = (int)(blockDim.x >> 5) - 2;        // 4 or 8 epilogue warps
+  uint32_t cols = 32;
+  while (cols < (uint32_t)nsets * acc_cols) cols <<= 1;
+
+  ptx::pdl_launch_dependents();
+  if (threadIdx.x == 0) {
+    ptx::mbar_init(bars + kPBarW, 1);
+    for (int i = 0; i < 3; ++i) {
+      ptx::mbar_init(bars + kPBarSlabFull + i, 1);
+      ptx::mbar_init(bars + kPBarSlabEmpty + i, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(bars + kPBarAccFull + i, 1);
+      ptx::mbar_init(bars + kPBarAccEmpty + i, (uint32_t)nepi);  // one arrival per epilogue warp
+    }
+    ptx::fence_mbar_init();
+  }
+  if (warp == 1) ptx::tmem_alloc(tmem_slot, cols);
+  for (int i = threadIdx.x; i < p.Cout; i += blockDim.x) bias_s[i] = g.bias[i];
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (ptx::elect_one()) {
+      ptx::mbar_arrive_expect_tx(bars + kPBarW, w_bytes);
+      ptx::bulk_g2s(wsm, g.w, w_bytes, bars + kPBarW);
+      ptx::pdl_grid_wait();
+      int it = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const int s = it % S;
+        if (it >= S) ptx::mbar_wait(bars + kPBarSlabEmpty + s, ((it / S) - 1) & 1);
+        ptx::mbar_arrive_expect_tx(bars + kPBarSlabFull + s, slab_bytes);
+        uint8_t* slab = slabs + (size_t)s * slab_stride;
+        const long long start = (long long)tile * tile_pos - p.halo_lo;
+        for (int sr = 0; sr < p.nsrc; ++sr) {
+          const char* src = g.src[sr].base + start * 16;
+          for (int c = 0; c < p.nchunks; ++c)
+            ptx::bulk_g2s(slab + (size_t)(sr * p.nchunks + c) * chunk_bytes, src + (long long)c * g.src[sr].plane_bytes,
+                          chunk_bytes, bars + kPBarSlabFull + s);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (ptx::elect_one()) {
+      const uint32_t idesc = ptx::umma_idesc_bf16(kTileM, p.Cout, 0, 0);
+      const uint32_t b_kstride = (uint32_t)p.Cout * 16u;
+      const uint64_t a_hi = ptx::umma_desc(0, chunk_bytes, 128u);
+      const uint64_t b_hi = ptx::umma_desc(0, b_kstride, 128u);
+      const uint32_t w16 = ptx::smem_u32(wsm) >> 4, slabs16 = ptx::smem_u32(slabs) >> 4;
+      const uint32_t chunk16 = chunk_bytes >> 4, a_kstep = 2u * chunk16, b_kstep = 2u * (uint32_t)p.Cout;
+      const int MT = p.MT, KC2 = p.nchunks >> 1, Cout = p.Cout, ntaps = p.ntaps;
+      // per-tap slab offsets in registers (the tap table lives in the kernel parameter block; reading it inside
+      // the issue loop would put a constant-bank load in front of every MMA)
+      uint32_t tap_off[kMaxTaps];
+#pragma unroll
+      for (int t = 0; t < kMaxTaps; ++t)
+        tap_off[t] = t < ntaps ? (uint32_t)(p.tap[t].src * p.nchunks) * chunk16 + (uint32_t)(p.halo_lo + p.tap[t].off) : 0u;
+      ptx::mbar_wait(bars + kPBarW, 0);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const int s = it % S, a = nsets == 2 ? (it & 1) : 0;
+        const bool dbg_on = p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && it < 12;
+        if (dbg_on) p.dbg[it * 8 + 0] = clock64();
+        ptx::mbar_wait(bars + kPBarSlabFull + s, (it / S) & 1);
+        if (dbg_on) p.dbg[it * 8 + 1] = clock64();
+        if (it >= nsets) ptx::mbar_wait(bars + kPBarAccEmpty + a, ((it / nsets) - 1) & 1);
+        if (dbg_on) p.dbg[it * 8 + 2] = clock64();
+        ptx::tc_fence_after();
+        const uint32_t slab16 = slabs16 + (uint32_t)s * (slab_stride >> 4);
+        // consecutive MMAs go to DIFFERENT accumulator tiles (mt innermost): back-to-back accumulation into the same
+        // TMEM tile serialises on the accumulate latency, interleaving the MT tiles keeps the tensor pipe busy
+        const uint32_t d_base = tmem_base + (uint32_t)a * acc_cols;
+        uint32_t acc = 0u, b_lo = w16;
+#pragma unroll
+        for (int t = 0; t < kMaxTaps; ++t) {
+          if (t < ntaps) {
+            uint32_t a_lo = slab16 + tap_off[t];
+            for (int k = 0; k < KC2; ++k) {
+              for (int mt = 0; mt < MT; ++mt)
+                ptx::umma_bf16(d_base + (uint32_t)(mt * Cout), a_hi | (a_lo + (uint32_t)(mt * kTileM)), b_hi | b_lo, idesc, acc);
+              acc = 1u;
+              a_lo += a_kstep;
+              b_lo += b_kstep;
+            }
+          }
+        }
+        ptx::umma_commit(bars + kPBarSlabEmpty + s);
+        ptx::umma_commit(bars + kPBarAccFull + a);
+        if (dbg_on) p.dbg[it * 8 + 3] = clock64();
+      }
+    }
+    __syncwarp();
+  } else {
+    // ---- epilogue warps: TMEM lane quarter = warp % 4; the two warps of a quarter take alternate accumulator tiles
+    const int quarter = warp & 3, half = (warp - 2) >> 2, mt_step = nepi >> 2;
+    const ActView outv = g.out, auxv = g.aux;
+    const long long out_plane_bytes = outv.plane * 16, aux_plane_bytes = auxv.plane * 16;
+    const int aux_nchunks = g.aux_nchunks;
+    const int Cout = p.Cout, MT = p.MT, H = p.H, W = p.W, Wp = p.Wp, Pimg = p.Pimg, body = (int)p.body;
+    const unsigned long long m_pimg = p.magic_pimg, m_wp = p.magic_wp;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      const int a = nsets == 2 ? (it & 1) : 0;
+      const bool dbg_on = p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && it < 12 && warp == 2 && lane == 0;
+      if (dbg_on) p.dbg[it * 8 + 4] = clock64();
+      ptx::mbar_wait(bars + kPBarAccFull + a, (it / nsets) & 1);
+      if (dbg_on) p.dbg[it * 8 + 5] = clock64();
+      ptx::tc_fence_after();
+      for (int mt = half; mt < MT; mt += mt_step) {
+        const int f = tile * tile_pos + mt * kTileM + quarter * 32 + lane;
+        const bool in_body = f < body;
+        int n = 0, h = 0, w = 0;
+        if (in_body) {
+          n = fast_div(f, m_pimg);
+          const int rem = f - n * Pimg;
+          h = fast_div(rem, m_wp);
+          w = rem - h * Wp;
+        }
+        const bool valid = in_body && (h < H) && (w < W);
+        const bool do_store = in_body && (valid || outv.layout == LAY_P8);
+        char* out_addr0 = view_addr<__nv_bfloat16>(outv, 0, f, n, h, w);
+        const char* aux_addr0 = view_addr<__nv_bfloat16>(auxv, 0, f, n, h, w);
+        const uint32_t trow = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)a * acc_cols + (uint32_t)(mt * Cout);
+        if (Cout >= 32) {
+          for (int c0 = 0; c0 < Cout; c0 += 32) {
+            uint32_t r[32];
+            ptx::tmem_ld32_issue(trow + (uint32_t)c0, r);
+            ptx::tmem_wait32(r);
+            if (do_store) {
+#pragma unroll
+              for (int hlf = 0; hlf < 2; ++hlf) {
+                float v[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[hlf * 16 + j]);
+                epilogue_cols<__nv_bfloat16, EPI>(bias_s, c0 + hlf * 16, valid, v, aux_addr0, aux_plane_bytes,
+                                                  aux_nchunks, out_addr0, out_plane_bytes);
+              }
+            }
+          }
+        } else {
+          uint32_t r[16];
+          ptx::tmem_ld16_issue(trow, r);
+          ptx::tmem_wait16(r);
+          if (do_store) {
+            float v[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+            epilogue_cols<__nv_bfloat16, EPI>(bias_s, 0, valid, v, aux_addr0, aux_plane_bytes, aux_nchunks, out_addr0,
+                                              out_plane_bytes);
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (dbg_on) p.dbg[it * 8 + 6] = clock64();
+      if (lane == 0) ptx::mbar_arrive(bars + kPBarAccEmpty + a);  // this warp is done reading accumulator set a
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem_base, cols);
+}
+
+size_t conv_persist_smem_bytes(const ConvParams& p) {
+  size_t w = ((size_t)p.ntaps * p.tap_bytes + 127) & ~(size_t)127;
+  size_t slab = ((size_t)p.nsrc * p.nchunks * p.SP * 16 + 127) & ~(size_t)127;
+  return kSmemHeader + w + (size_t)p.persist_stages * slab;
+}
+
+// ---------------------------------------------------------------------------------------------
 // FP32 path
 // ---------------------------------------------------------------------------------------------
 constexpr int kFp32CoutBlock = 32;
@@ -398,7 +610,48 @@ static cudaError_t launch_ex(K kernel, dim3 grid, dim3 block, size_t smem, cudaS
 }
 
 cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream, bool pdl) {
-  if (precision == 0) {
+  if (precision == 0 && p.persist_stages > 0) {
+    const size_t smem = conv_persist_smem_bytes(p);
+    static size_t configured_p = 0;
+    if (smem > configured_p) {
+      cudaError_t e = cudaSuccess;
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_ADD_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_SIGMOID_MUL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_ACCUM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+      configured_p = smem;
+    }
+    const int tile = p.MT * kTileM;
+    const int ntiles = (int)((p.body + tile - 1) / tile);
+    static int env_threads = -1, env_ctas = -1;
+    if (env_threads < 0) {
+      const char* a = getenv("MTLDAS_PERSIST_THREADS");
+      const char* b = getenv("MTLDAS_PERSIST_CTAS");
+      env_threads = a ? atoi(a) : 320;
+      env_ctas = b ? atoi(b) : 2;
+    }
+    const int threads = env_threads == 320 ? 320 : 192;
+    int per_sm = (int)std::min<size_t>((size_t)env_ctas, (220 * 1024) / smem);
+    per_sm = std::min(per_sm, 65536 / (96 * threads));
+    per_sm = std::max(per_sm, 1);
+    ConvParams q = p;
+    q.acc_sets = (per_sm * 2 * p.MT * p.Cout <= 512) ? 2 : 1;
+    uint32_t cols = 32;
+    while (cols < (uint32_t)(q.acc_sets * p.MT * p.Cout)) cols <<= 1;
+    per_sm = std::max(1, std::min(per_sm, (int)(512 / cols)));
+    int ctas = std::min(ntiles, 148 * per_sm / std::max(1, p.ngroups));
+    ctas = std::max(ctas, 1);
+    dim3 grid(ctas, p.ngroups, 1);
+    switch (p.epi) {
+      case EPI_NONE: return launch_ex(conv_umma_persist_kernel<EPI_NONE>, grid, dim3(threads), smem, stream, pdl, q);
+      case EPI_RELU: return launch_ex(conv_umma_persist_kernel<EPI_RELU>, grid, dim3(threads), smem, stream, pdl, q);
+      case EPI_ADD_RELU: return launch_ex(conv_umma_persist_kernel<EPI_ADD_RELU>, grid, dim3(threads), smem, stream, pdl, q);
+      case EPI_ACCUM: return launch_ex(conv_umma_persist_kernel<EPI_ACCUM>, grid, dim3(threads), smem, stream, pdl, q);
+      default: return launch_ex(conv_umma_persist_kernel<EPI_SIGMOID_MUL>, grid, dim3(threads), smem, stream, pdl, q);
+    }
+  } else if (precision == 0) {
     size_t smem = conv_umma_smem_bytes(p);
     static size_t configured = 0;
     if (smem > configured) {

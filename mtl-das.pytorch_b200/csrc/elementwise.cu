@@ -267,6 +267,34 @@ cudaError_t launch_pack(const PackParams& p, cudaStream_t stream) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// streaming inference: cut [100 x 250] patches out of a large DAS array [n_channels, n_time] (fp32, row major).
+// patch (wi, tb) = array[start0 + wi*stride : +100, tb*250 : +250]; output order: window-major, then time block.
+// thread = one float4 of a patch row (250 floats = 62 float4 + 2 floats handled by the last lanes).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) window_gather_kernel(const float* __restrict__ arr, long long n_time,
+                                                            int start0, int stride, int n_windows, int n_tblocks,
+                                                            float* __restrict__ out) {
+  const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+  const long long total = (long long)n_windows * n_tblocks * 100 * 250;
+  if (idx >= total) return;
+  const int col = (int)(idx % 250);
+  const int row = (int)((idx / 250) % 100);
+  const long long pidx = idx / 25000;
+  const int tb = (int)(pidx % n_tblocks);
+  const int wi = (int)(pidx / n_tblocks);
+  out[idx] = arr[(long long)(start0 + wi * stride + row) * n_time + (long long)tb * 250 + col];
+}
+
+cudaError_t launch_window_gather(const float* arr, long long n_time, int start0, int stride, int n_windows,
+                                 int n_tblocks, float* out, cudaStream_t stream) {
+  const long long total = (long long)n_windows * n_tblocks * 25000;
+  if (total == 0) return cudaSuccess;
+  window_gather_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(arr, n_time, start0, stride, n_windows,
+                                                                             n_tblocks, out);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
 // fp32 NCHW <-> view
 // ---------------------------------------------------------------------------------------------
 template <typename T, bool ToView>

@@ -372,6 +372,20 @@ ConvParams Plan::conv_params(const ConvOpHost& op, int nb) const {
   q.MT = op.MT, q.SP = op.MT * kTileM + op.halo_lo + op.halo_hi;
   q.tps = op.tps, q.NS = op.NS, q.nstages = op.nstages, q.tap_bytes = op.tap_bytes, q.tmem_cols = op.tmem_cols;
   q.epi = op.epi, q.swap_desc = swap_desc, q.ngroups = op.ngroups;
+  q.magic_pimg = (1ull << 40) / (unsigned long long)q.Pimg + 1, q.magic_wp = (1ull << 40) / (unsigned long long)q.Wp + 1;
+  q.persist_stages = 0;
+  if (op.nstages == 1 && use_persist) {
+    const size_t slab = (size_t)op.nsrc * op.nchunks * q.SP * 16, wb = (size_t)op.ntaps * op.tap_bytes;
+    static int env_stages = -1;
+    if (env_stages < 0) {
+      const char* e = getenv("MTLDAS_PERSIST_STAGES");
+      env_stages = e ? atoi(e) : 3;
+    }
+    if (wb + (size_t)env_stages * slab <= 100 * 1024)
+      q.persist_stages = env_stages;
+    else if (wb + 2 * slab <= 200 * 1024)
+      q.persist_stages = 2;
+  }
   for (int t = 0; t < op.ntaps; ++t) q.tap[t] = op.tap[t];
   for (int gi = 0; gi < op.ngroups; ++gi) {
     const ConvGroupHost& g = op.g[gi];
@@ -737,6 +751,17 @@ int single_conv(const float* x, const float* x2, const float* weight, const floa
       for (int i = 0; i < ntile; ++i) {
         t0 = std::min(t0, h[(size_t)i * 16]);
         t1 = std::max(t1, h[(size_t)i * 16]);
+      }
+      if (cp.persist_stages > 0) {
+        fprintf(stderr, "[convdbg] persistent kernel, stages %d, tiles %d; CTA 0 per iteration (SM clocks relative to it 0):\n",
+                cp.persist_stages, ntile);
+        for (int it = 0; it < 12; ++it) {
+          const long long* r = &h[(size_t)it * 8];
+          if (!r[0]) break;
+          fprintf(stderr, "[convdbg]  it %2d mma: start %lld slab-ready +%lld acc-free +%lld issued +%lld | epi(w2): wait-start %lld acc-ready +%lld done +%lld\n",
+                  it, r[0] - h[0], r[1] - r[0], r[2] - r[1], r[3] - r[2], r[4] - h[0], r[5] - r[4], r[6] - r[5]);
+        }
+        break;
       }
       fprintf(stderr, "[convdbg] tiles=%d MT=%d NS=%d tps=%d smem=%zu last CTA start +%lld ns\n", ntile, cp.MT, cp.NS,
               cp.tps, conv_umma_smem_bytes(cp), t1 - t0);

@@ -98,6 +98,7 @@ struct Plan {
   unsigned long long graph_clock = 0;
   int use_graphs = 1;
   int use_pdl = 1;
+  int use_persist = 1;
   cudaStream_t cap_stream = nullptr;
   // host entry point: private copy stream and events so that the H2D of pass i+1 overlaps the compute of pass i
   cudaStream_t copy_stream = nullptr;

@@ -630,6 +630,12 @@ __global__ void __launch_bounds__(128) wgrad_umma_kernel(const __grid_constant__
       const uint64_t b_hi = ptx::umma_desc(0, 128u, b_chunk);
       const uint32_t a16 = ptx::smem_u32(a_slab) >> 4, b16 = ptx::smem_u32(b_slab) >> 4;
       uint32_t acc = 0u;
+      uint32_t tap_off[kMaxTaps];  // per-tap B-operand offsets in registers (no parameter loads in the issue loop)
+#pragma unroll
+      for (int t = 0; t < kMaxTaps; ++t)
+        tap_off[t] = t < ntap ? (uint32_t)(p.tap[tap0 + t].src * p.nchunks) * (b_chunk >> 4) +
+                                    (uint32_t)(p.halo_lo + p.tap[tap0 + t].off)
+                              : 0u;
       for (int s = 0; s < nstage; ++s) {
         const int b = s & 1;
         ptx::mbar_wait(bars + b, (s >> 1) & 1);
@@ -638,12 +644,10 @@ __global__ void __launch_bounds__(128) wgrad_umma_kernel(const __grid_constant__
         const int ksteps = (int)min((long long)(kWgStage / 16), (f1 - fb + 15) / 16);
         for (int j = 0; j < ksteps; ++j) {
           const uint32_t a_lo = a16 + (uint32_t)b * (a_stage >> 4) + (uint32_t)j * 16u;
-          for (int t = 0; t < ntap; ++t) {
-            const ConvTapDev tp = p.tap[tap0 + t];
-            const uint32_t b_lo = b16 + (uint32_t)b * (b_stage >> 4) + (uint32_t)(tp.src * p.nchunks) * (b_chunk >> 4) +
-                                  (uint32_t)(p.halo_lo + tp.off + j * 16);
-            ptx::umma_bf16(tmem_base + (uint32_t)(t * Cin), a_hi | a_lo, b_hi | b_lo, idesc, acc);
-          }
+          const uint32_t b_j = b16 + (uint32_t)b * (b_stage >> 4) + (uint32_t)(j * 16);
+#pragma unroll
+          for (int t = 0; t < kMaxTaps; ++t)
+            if (t < ntap) ptx::umma_bf16(tmem_base + (uint32_t)(t * Cin), a_hi | a_lo, b_hi | (b_j + tap_off[t]), idesc, acc);
           acc = 1u;
         }
         ptx::umma_commit(bars + 2 + b);
