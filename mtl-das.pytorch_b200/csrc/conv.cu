@@ -135,7 +135,7 @@ __device__ __forceinline__ void epilogue_cols(const float* bias_s, int c0, bool 
 }
 
 template <int EPI>
-__global__ void __launch_bounds__(128, 6) conv_umma_kernel(const __grid_constant__ ConvParams p) {
+__global__ void __launch_bounds__(128, 3) conv_umma_kernel(const __grid_constant__ ConvParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   const ConvGroupDev& g = p.g[blockIdx.y];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
@@ -245,7 +245,11 @@ __global__ void __launch_bounds__(128, 6) conv_umma_kernel(const __grid_constant
           ptx::umma_commit(bars + kBarAcc + mt);
         }
       } else {
-        uint32_t acc = 0u;
+        // streamed weights.  With p.ksplit the even / odd 16-channel K steps accumulate into two TMEM sets that the
+        // epilogue adds: consecutive MMAs then never target the same accumulator tile twice within 2*MT issues
+        // (back-to-back accumulation into one tile serialises on the accumulate latency).
+        uint32_t acc0 = 0u, acc1 = 0u;
+        const uint32_t set1 = p.ksplit ? (uint32_t)(MT * Cout) : 0u;
         for (int st = 0; st < p.nstages; ++st) {
           const int slot = st % p.NS;
           ptx::mbar_wait(bars + kBarWFull + slot, (st / p.NS) & 1);
@@ -257,10 +261,12 @@ __global__ void __launch_bounds__(128, 6) conv_umma_kernel(const __grid_constant
             uint32_t a_lo = slab16 + (uint32_t)(tp.src * p.nchunks) * chunk16 + (uint32_t)(p.halo_lo + tp.off);
             uint32_t b_lo = wring16 + (uint32_t)slot * stage16 + (uint32_t)ti * tap16;
             for (int k = 0; k < KC2; ++k) {
+              const bool odd = p.ksplit && (k & 1);
+              const uint32_t d0 = tmem_base + (odd ? set1 : 0u);
+              const uint32_t acc = odd ? acc1 : acc0;
               for (int mt = 0; mt < MT; ++mt)
-                ptx::umma_bf16(tmem_base + (uint32_t)(mt * Cout), a_hi | (a_lo + (uint32_t)(mt * kTileM)), b_hi | b_lo,
-                               idesc, acc);
-              acc = 1u;
+                ptx::umma_bf16(d0 + (uint32_t)(mt * Cout), a_hi | (a_lo + (uint32_t)(mt * kTileM)), b_hi | b_lo, idesc, acc);
+              if (odd) acc1 = 1u; else acc0 = 1u;
               a_lo += a_kstep;
               b_lo += b_kstep;
             }
@@ -303,6 +309,13 @@ __global__ void __launch_bounds__(128, 6) conv_umma_kernel(const __grid_constant
           uint32_t r[32];
           ptx::tmem_ld32_issue(trow + (uint32_t)c0, r);
           ptx::tmem_wait32(r);
+          if (p.ksplit && !resident) {  // second K-split accumulator set
+            uint32_t r2[32];
+            ptx::tmem_ld32_issue(trow + (uint32_t)(MT * Cout + c0), r2);
+            ptx::tmem_wait32(r2);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
+          }
           if (mt == 0 && c0 == 0 && threadIdx.x == 64) DBG(7)
           if (do_store) {
 #pragma unroll

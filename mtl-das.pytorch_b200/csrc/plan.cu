@@ -146,8 +146,11 @@ void choose_tiling(ConvOpHost& op) {
     op.NS = std::max(1, std::min(std::min(ns, op.ntaps), kMaxRing));
   }
   op.nstages = (op.ntaps + op.tps - 1) / op.tps;
+  // K-split accumulation (two TMEM sets) is implemented in the kernel but measured slower on B200 for these
+  // layers (TMEM-limited CTA concurrency, doubled epilogue loads): left off.
+  op.ksplit = 0;
   int cols = 32;
-  while (cols < MT * op.Cout) cols <<= 1;
+  while (cols < (op.ksplit ? 2 : 1) * MT * op.Cout) cols <<= 1;
   op.tmem_cols = cols;
 }
 
@@ -371,7 +374,7 @@ ConvParams Plan::conv_params(const ConvOpHost& op, int nb) const {
   q.halo_lo = op.halo_lo, q.halo_hi = op.halo_hi;
   q.MT = op.MT, q.SP = op.MT * kTileM + op.halo_lo + op.halo_hi;
   q.tps = op.tps, q.NS = op.NS, q.nstages = op.nstages, q.tap_bytes = op.tap_bytes, q.tmem_cols = op.tmem_cols;
-  q.epi = op.epi, q.swap_desc = swap_desc, q.ngroups = op.ngroups;
+  q.epi = op.epi, q.swap_desc = swap_desc, q.ngroups = op.ngroups, q.ksplit = op.ksplit;
   q.magic_pimg = (1ull << 40) / (unsigned long long)q.Pimg + 1, q.magic_wp = (1ull << 40) / (unsigned long long)q.Wp + 1;
   q.persist_stages = 0;
   if (op.nstages == 1 && use_persist) {

@@ -53,7 +53,7 @@ struct ConvOpHost {
   int Hv = 0, Wv = 0;         // valid extents when they differ from the plane geometry (0 = H, W)
   ConvTapDev tap[kMaxTaps];
   ConvGroupHost g[kMaxGroups];
-  int MT, tps, NS, nstages, tap_bytes, tmem_cols;
+  int MT, tps, NS, nstages, tap_bytes, tmem_cols, ksplit;
 };
 struct PoolOpHost {
   std::string name;

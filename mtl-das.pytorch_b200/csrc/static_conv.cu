@@ -198,7 +198,8 @@ extern "C" int mtldas_conv2d_nchw_static(const float* dev_x, const float* dev_x2
   q.halo_lo = op.halo_lo, q.halo_hi = op.halo_hi;
   q.MT = op.MT, q.SP = op.MT * kTileM + op.halo_lo + op.halo_hi;
   q.tps = op.tps, q.NS = op.NS, q.nstages = op.nstages, q.tap_bytes = op.tap_bytes, q.tmem_cols = op.tmem_cols;
-  q.epi = epilogue, q.swap_desc = 0, q.ngroups = 1, q.dbg = nullptr;
+  q.epi = epilogue, q.swap_desc = 0, q.ngroups = 1, q.dbg = nullptr, q.ksplit = op.ksplit;
+  q.magic_pimg = (1ull << 40) / (unsigned long long)q.Pimg + 1, q.magic_wp = (1ull << 40) / (unsigned long long)q.Wp + 1;
   for (int t = 0; t < op.ntaps; ++t) q.tap[t] = op.tap[t];
   ConvGroupDev& d = q.g[0];
   if (stride == 2 && ksize == 3) {

@@ -72,6 +72,7 @@ struct ConvParams {
   int swap_desc;           // debug: swap the LBO/SBO roles in the UMMA descriptors
   int ngroups;
   unsigned long long magic_pimg, magic_wp;  // floor(2^40/d)+1: exact f/d for f < 2^22 by multiply-shift
+  int ksplit;              // ring kernel: even/odd K steps accumulate into two TMEM sets (summed in the epilogue)
   int acc_sets;            // persistent kernel: TMEM accumulator sets (1 or 2), chosen by the launcher
   int persist_stages;      // > 0: resident weights, persistent pipelined kernel with this many slab stages
   long long* dbg;          // optional [grid.x][8] timeline (globaltimer ns) for diagnostics, else null
