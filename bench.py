@@ -40,7 +40,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=4096, help="patches per GPU per step")
-    ap.add_argument("--micro-batch", type=int, default=int(os.environ.get("MTLDAS_MICRO_BATCH", "512")))
+    ap.add_argument("--micro-batch", type=int, default=int(os.environ.get("MTLDAS_MICRO_BATCH", "4096")))
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--cpu-sample", type=int, default=256, help="patches per CPU-baseline step")
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -33,7 +33,7 @@ int mtldas_device_ok(void) {
 }
 
 mtldas_plan* mtldas_plan_create(int model_kind, int micro_batch, int precision) {
-  if (model_kind < 0 || model_kind > 2 || micro_batch < 1 || micro_batch > 1024 || precision < 0 || precision > 1) {
+  if (model_kind < 0 || model_kind > 2 || micro_batch < 1 || micro_batch > 4096 || precision < 0 || precision > 1) {
     set_error("plan_create: bad arguments (kind %d, micro_batch %d, precision %d)", model_kind, micro_batch,
               precision);
     return nullptr;
@@ -136,11 +136,12 @@ int mtldas_plan_forward_eval_host(mtldas_plan* plan, const float* host_x, int n,
   }
   cudaStream_t st = (cudaStream_t)stream;
   const int c0 = p.heads[0].classes, c1 = p.heads.size() > 1 ? p.heads[1].classes : 0;
-  const size_t xslot = (size_t)p.mb * kPatchH * kPatchW;
+  const int chunk = p.host_chunk;
+  const size_t xslot = (size_t)chunk * kPatchH * kPatchW;
   float* xs[2] = {reinterpret_cast<float*>(p.ws + p.x_stage_off), reinterpret_cast<float*>(p.ws + p.x_stage_off) + xslot};
   float* o0[2] = {reinterpret_cast<float*>(p.ws + p.out_stage_off),
-                  reinterpret_cast<float*>(p.ws + p.out_stage_off) + (size_t)p.mb * 18};
-  float* o1[2] = {o0[0] + (size_t)p.mb * 16, o0[1] + (size_t)p.mb * 16};
+                  reinterpret_cast<float*>(p.ws + p.out_stage_off) + (size_t)chunk * 18};
+  float* o1[2] = {o0[0] + (size_t)chunk * 16, o0[1] + (size_t)chunk * 16};
 #define CKH(call)                                                        \
   do {                                                                   \
     cudaError_t e_ = (call);                                             \
@@ -153,8 +154,8 @@ int mtldas_plan_forward_eval_host(mtldas_plan* plan, const float* host_x, int n,
   CKH(cudaEventRecord(p.ev_start, st));
   CKH(cudaStreamWaitEvent(p.copy_stream, p.ev_start, 0));
   int launches = 0, i = 0;
-  for (int s = 0; s < n; s += p.mb, ++i) {
-    const int nb = n - s < p.mb ? n - s : p.mb;
+  for (int s = 0; s < n; s += chunk, ++i) {
+    const int nb = n - s < chunk ? n - s : chunk;
     const int slot = i & 1;
     if (i >= 2) CKH(cudaStreamWaitEvent(p.copy_stream, p.ev_comp[slot], 0));  // slot free again
     CKH(cudaMemcpyAsync(xs[slot], host_x + (size_t)s * kPatchH * kPatchW, (size_t)nb * kPatchH * kPatchW * 4,

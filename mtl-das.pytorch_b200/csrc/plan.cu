@@ -133,6 +133,9 @@ void choose_tiling(ConvOpHost& op) {
     slab = (size_t)op.nsrc * op.nchunks * SP * 16;
     if (MT == 1) break;
     if (MT * op.Cout <= 256 && slab <= 80 * 1024) break;
+    // compute-heavy layers (>= 128 output channels): four independent accumulator tiles keep the tensor pipe busy
+    // (two serialise on the accumulate latency); needs the slab plus a two-slot weight ring in shared memory
+    if (MT * op.Cout <= 512 && op.Cout >= 128 && op.nchunks >= 16 && slab + 2 * (size_t)op.tap_bytes <= 216 * 1024) break;
   }
   op.MT = MT;
   if (slab + total_w <= 96 * 1024) {
@@ -357,8 +360,10 @@ Plan* build_plan(int kind, int mb, int precision) {
     }
   p.stem_w_off = take(49 * 16 * 4);
   p.stem_b_off = take(16 * 4);
-  p.x_stage_off = take((size_t)2 * mb * kPatchH * kPatchW * 4);  // two slots: H2D of pass i+1 overlaps pass i
-  p.out_stage_off = take((size_t)2 * mb * 18 * 4);
+  // host entry point: chunks of at most 1024 patches through two staging slots (H2D of chunk i+1 overlaps chunk i)
+  p.host_chunk = std::min(mb, 1024);
+  p.x_stage_off = take((size_t)2 * p.host_chunk * kPatchH * kPatchW * 4);
+  p.out_stage_off = take((size_t)2 * p.host_chunk * 18 * 4);
   p.ws_bytes = off;
   return pp;
 }

@@ -80,6 +80,7 @@ struct Plan {
   int stem_layer, stem_out;
   size_t stem_w_off, stem_b_off;
   size_t x_stage_off, out_stage_off;
+  int host_chunk = 0;
   size_t ws_bytes;
   char* ws = nullptr;
   bool packed = false;

@@ -72,17 +72,22 @@ class _DasNet(nn.Module):
         self._plans = {}
         self._packed_sig = {}
         self.precision = os.environ.get("MTLDAS_PRECISION", "bf16")
-        self.micro_batch = int(os.environ.get("MTLDAS_MICRO_BATCH", "512"))
+        self.micro_batch = int(os.environ.get("MTLDAS_MICRO_BATCH", "4096"))
 
     # ---- engine plumbing -------------------------------------------------------------------
     def _kind(self):
         return "MTL" if len(self.tasks) == 2 else "single_" + self.tasks[0]
 
-    def _eval_plan(self, device):
-        key = (str(device), self.precision, self.micro_batch)
-        if key not in self._plans:
-            self._plans[key] = EvalPlan(self._kind(), self.micro_batch, self.precision, device)
-        plan = self._plans[key]
+    def _eval_plan(self, device, n=1):
+        # one pass over as many patches as possible is fastest on B200 (launch / tail overheads dominate the
+        # L2-residency gain of small micro-batches); the workspace grows with the largest batch seen, up to the cap
+        key = (str(device), self.precision)
+        want = max(8, min(int(n), self.micro_batch))
+        plan = self._plans.get(key)
+        if plan is None or plan.micro_batch < want:
+            plan = EvalPlan(self._kind(), want, self.precision, device)
+            self._plans[key] = plan
+            self._packed_sig.pop(key, None)
         sd = {k: v for k, v in self.state_dict(keep_vars=True).items()}
         sig = tuple((v.data_ptr(), v._version) for v in sd.values())
         if self._packed_sig.get(key) != sig:
@@ -96,7 +101,7 @@ class _DasNet(nn.Module):
                               "got a non-CUDA input and there is no CPU fallback")
         if self.training:
             return _TrainStep.apply(self, x, *[p for _, p in self.named_parameters()])
-        return self._eval_plan(x.device).forward(x)
+        return self._eval_plan(x.device, x.shape[0]).forward(x)
 
     def _train_plan(self, device, n):
         key = (str(device), self.precision)

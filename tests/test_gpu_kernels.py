@@ -137,7 +137,7 @@ def test_dropin_module_and_host_path():
     for o, r in zip((out1, out2), ref):
         assert float((o.cpu().double() - r).abs().max() / r.abs().max()) < 1e-4
     # host-buffer entry point == device entry point
-    plan = m._eval_plan(x.cuda().device)
+    plan = m._eval_plan(x.cuda().device, n)
     h1, h2 = plan.forward_host(x.pin_memory())
     assert torch.allclose(h1, out1.cpu(), atol=1e-6) and torch.allclose(h2, out2.cpu(), atol=1e-6)
     # a parameter update invalidates the packed weights
