@@ -379,8 +379,10 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
   uint8_t* slabs = wsm + ((w_bytes + 127u) & ~127u);
   const int S = p.persist_stages;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tile_pos = p.MT * kTileM;
+  const int tile_rows = p.MT * kTileM;                                   // rows computed per tile
+  const int tile_pos = p.pool_k > 0 ? 2 * p.Wp * p.pool_k : tile_rows;   // rows a tile advances by
   const int ntiles = (int)((p.body + tile_pos - 1) / tile_pos);
+  uint8_t* staging = slabs + (size_t)p.persist_stages * slab_stride;     // fused max-pool: [chunk][tile_rows][16 B]
   const uint32_t acc_cols = (uint32_t)(p.MT * p.Cout);
   const int nsets = p.acc_sets;                       // 1 or 2 TMEM accumulator sets
   const int nepi = (int)(blockDim.x >> 5) - 2;        // 4 or 8 epilogue warps
@@ -509,7 +511,20 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
         char* out_addr0 = view_addr<__nv_bfloat16>(outv, 0, f, n, h, w);
         const char* aux_addr0 = view_addr<__nv_bfloat16>(auxv, 0, f, n, h, w);
         const uint32_t trow = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)a * acc_cols + (uint32_t)(mt * Cout);
-        if (Cout >= 32) {
+        if (EPI == EPI_RELU && p.pool_k > 0) {
+          // fused max-pool: relu(acc + bias) of this row goes to the shared-memory staging tile (zero at pads)
+          const int row = mt * kTileM + quarter * 32 + lane;
+          for (int c0 = 0; c0 < Cout; c0 += 16) {
+            uint32_t r[16];
+            ptx::tmem_ld16_issue(trow + (uint32_t)c0, r);
+            ptx::tmem_wait16(r);
+            float v[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = valid ? fmaxf(__uint_as_float(r[j]) + bias_s[c0 + j], 0.f) : 0.f;
+            store8<__nv_bfloat16>(reinterpret_cast<char*>(staging) + ((size_t)(c0 >> 3) * tile_rows + row) * 16, v);
+            store8<__nv_bfloat16>(reinterpret_cast<char*>(staging) + ((size_t)((c0 >> 3) + 1) * tile_rows + row) * 16, v + 8);
+          }
+        } else if (Cout >= 32) {
           for (int c0 = 0; c0 < Cout; c0 += 32) {
             uint32_t r[32];
             ptx::tmem_ld32_issue(trow + (uint32_t)c0, r);
@@ -542,6 +557,35 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
       __syncwarp();
       if (dbg_on) p.dbg[it * 8 + 6] = clock64();
       if (lane == 0) ptx::mbar_arrive(bars + kPBarAccEmpty + a);  // this warp is done reading accumulator set a
+      if (EPI == EPI_RELU && p.pool_k > 0) {
+        // ---- fused MaxPool2d(2,2,ceil): the tile is pool_k image-row pairs; every pooled granule is the max of four
+        // staged granules (pads were staged as zero, and post-ReLU values are >= 0, so clipped windows are correct)
+        const int nthr = nepi * 32, e = (warp - 2) * 32 + lane;
+        asm volatile("bar.sync 1, %0;" ::"r"(nthr) : "memory");
+        const int Wph = Wp >> 1, nch = Cout >> 3, per_chunk = p.pool_k * Wph;
+        const int hp_half = (H + 1) >> 1;                      // row pairs per image (Hp is even)
+        const ActView pv = g.pool_out;
+        for (int o = e; o < per_chunk * nch; o += nthr) {
+          const int c = o / per_chunk, q = o - c * per_chunk;
+          const int rp = q / Wph, cp = q - rp * Wph;
+          const int r0 = 2 * rp * Wp + 2 * cp;                 // row in the staging tile
+          if ((long long)tile * tile_pos + r0 >= p.body) continue;
+          const uint4* sp = reinterpret_cast<const uint4*>(staging + ((size_t)c * tile_rows + r0) * 16);
+          uint4 m = sp[0];
+          const uint4 b1 = sp[1], b2 = sp[Wp], b3 = sp[Wp + 1];
+          __nv_bfloat162* mm = reinterpret_cast<__nv_bfloat162*>(&m);
+          const __nv_bfloat162* x1 = reinterpret_cast<const __nv_bfloat162*>(&b1);
+          const __nv_bfloat162* x2 = reinterpret_cast<const __nv_bfloat162*>(&b2);
+          const __nv_bfloat162* x3 = reinterpret_cast<const __nv_bfloat162*>(&b3);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) mm[j] = __hmax2(__hmax2(mm[j], x1[j]), __hmax2(x2[j], x3[j]));
+          const int R = tile * p.pool_k + rp;                  // global row-pair index
+          const int n = R / hp_half, ho = R - n * hp_half;
+          const long long pos = (long long)c * pv.plane + pv.g_lo + (long long)n * p.pool_Pimgo + ho * p.pool_Wpo + cp;
+          *reinterpret_cast<uint4*>(pv.base + pos * 16) = m;
+        }
+        asm volatile("bar.sync 1, %0;" ::"r"(nthr) : "memory");  // staging is reused by the next tile
+      }
     }
   }
   ptx::tc_fence_before();
@@ -552,7 +596,8 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
 size_t conv_persist_smem_bytes(const ConvParams& p) {
   size_t w = ((size_t)p.ntaps * p.tap_bytes + 127) & ~(size_t)127;
   size_t slab = ((size_t)p.nsrc * p.nchunks * p.SP * 16 + 127) & ~(size_t)127;
-  return kSmemHeader + w + (size_t)p.persist_stages * slab;
+  size_t staging = p.pool_k > 0 ? (size_t)(p.Cout / 8) * p.MT * kTileM * 16 : 0;
+  return kSmemHeader + w + (size_t)p.persist_stages * slab + staging;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -636,7 +681,7 @@ cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream,
       if (e != cudaSuccess) return e;
       configured_p = smem;
     }
-    const int tile = p.MT * kTileM;
+    const int tile = p.pool_k > 0 ? 2 * p.Wp * p.pool_k : p.MT * kTileM;
     const int ntiles = (int)((p.body + tile - 1) / tile);
     static int env_threads = -1, env_ctas = -1;
     if (env_threads < 0) {

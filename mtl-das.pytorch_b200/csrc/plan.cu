@@ -123,6 +123,21 @@ ActView Plan::view(int tensor, int chunk0) const {
 // ---------------------------------------------------------------------------------------------
 // conv op construction
 // ---------------------------------------------------------------------------------------------
+// shared-memory stages of the persistent kernel for this op (0 = not eligible); `extra` = bytes of other buffers
+int persist_stages_for(const ConvOpHost& op, size_t extra) {
+  if (op.nstages != 1) return 0;
+  const size_t SP = (size_t)op.MT * kTileM + op.halo_lo + op.halo_hi;
+  const size_t slab = (size_t)op.nsrc * op.nchunks * SP * 16, wb = (size_t)op.ntaps * op.tap_bytes;
+  static int env_stages = -1;
+  if (env_stages < 0) {
+    const char* e = getenv("MTLDAS_PERSIST_STAGES");
+    env_stages = e ? atoi(e) : 3;
+  }
+  if (wb + (size_t)env_stages * slab + extra <= 108 * 1024) return env_stages;
+  if (wb + 2 * slab + extra <= 200 * 1024) return 2;
+  return 0;
+}
+
 void choose_tiling(ConvOpHost& op) {
   op.tap_bytes = op.nchunks * 8 * op.Cout * 2;
   const int total_w = op.ntaps * op.tap_bytes;
@@ -338,9 +353,20 @@ Plan* build_plan(int kind, int mb, int precision) {
       op3.g[t].out_tensor = o, op3.g[t].out_chunk0 = (oc / 8) * t;
       op3.g[t].segs.push_back(b.seg("output_layer" + std::to_string(l + 1) + "." + std::to_string(t) + ".0"));
     }
+    choose_tiling(op3);
+    // bf16 inference: ReLU + 2x2 max-pool are fused into the conv epilogue (shared-memory staging tile) when the layer
+    // qualifies for the persistent kernel; the full-resolution tensor `o` is then never written
+    const char* nofuse = getenv("MTLDAS_NO_POOL_FUSE");
+    const size_t staging = (size_t)(oc / 8) * op3.MT * kTileM * 16;
+    const bool fuse = precision == 0 && !(nofuse && nofuse[0] == '1') && persist_stages_for(op3, staging) > 0 &&
+                      (op3.MT * kTileM) / (2 * (W[l] + 1)) >= 1;
+    if (fuse)
+      for (int t = 0; t < T; ++t) op3.g[t].pool_tensor = pooled;
     b.finish(op3);
-    p.pools.push_back(PoolOpHost{"pool" + std::to_string(l + 1), o, pooled});
-    p.program.push_back(Op{2, (int)p.pools.size() - 1});
+    if (!fuse) {
+      p.pools.push_back(PoolOpHost{"pool" + std::to_string(l + 1), o, pooled});
+      p.program.push_back(Op{2, (int)p.pools.size() - 1});
+    }
     a_prev = pooled;
   }
 
@@ -381,18 +407,14 @@ ConvParams Plan::conv_params(const ConvOpHost& op, int nb) const {
   q.tps = op.tps, q.NS = op.NS, q.nstages = op.nstages, q.tap_bytes = op.tap_bytes, q.tmem_cols = op.tmem_cols;
   q.epi = op.epi, q.swap_desc = swap_desc, q.ngroups = op.ngroups, q.ksplit = op.ksplit;
   q.magic_pimg = (1ull << 40) / (unsigned long long)q.Pimg + 1, q.magic_wp = (1ull << 40) / (unsigned long long)q.Wp + 1;
-  q.persist_stages = 0;
-  if (op.nstages == 1 && use_persist) {
-    const size_t slab = (size_t)op.nsrc * op.nchunks * q.SP * 16, wb = (size_t)op.ntaps * op.tap_bytes;
-    static int env_stages = -1;
-    if (env_stages < 0) {
-      const char* e = getenv("MTLDAS_PERSIST_STAGES");
-      env_stages = e ? atoi(e) : 3;
-    }
-    if (wb + (size_t)env_stages * slab <= 100 * 1024)
-      q.persist_stages = env_stages;
-    else if (wb + 2 * slab <= 200 * 1024)
-      q.persist_stages = 2;
+  q.pool_k = 0;
+  const bool pool = op.g[0].pool_tensor >= 0;
+  const size_t staging = pool ? (size_t)(op.Cout / 8) * op.MT * kTileM * 16 : 0;
+  q.persist_stages = (use_persist || pool) ? persist_stages_for(op, staging) : 0;
+  if (pool) {
+    const TensorInfo& tp = tensors[op.g[0].pool_tensor];
+    q.pool_k = (op.MT * kTileM) / (2 * q.Wp);
+    q.pool_Wpo = tp.Wp, q.pool_Pimgo = tp.Pimg;
   }
   for (int t = 0; t < op.ntaps; ++t) q.tap[t] = op.tap[t];
   for (int gi = 0; gi < op.ngroups; ++gi) {
@@ -414,6 +436,7 @@ ConvParams Plan::conv_params(const ConvOpHost& op, int nb) const {
     }
     if (g.aux_tensor >= 0) d.aux = view(g.aux_tensor, g.aux_chunk0);
     d.aux_nchunks = g.aux_nchunks;
+    if (g.pool_tensor >= 0) d.pool_out = view(g.pool_tensor, g.out_chunk0);
   }
   return q;
 }
@@ -841,6 +864,7 @@ std::string Plan::describe() const {
           o << "[\"" << tensors[g.aux_tensor].name << "\"," << g.aux_chunk0 << "," << g.aux_nchunks << "]";
         else
           o << "null";
+        if (g.pool_tensor >= 0) o << ",\"pool\":\"" << tensors[g.pool_tensor].name << "\"";
         o << ",\"w_off\":" << g.w_off << ",\"bias_off\":" << g.bias_off << ",\"segs\":[";
         for (size_t si = 0; si < g.segs.size(); ++si) {
           const PackSegHost& s = g.segs[si];

@@ -42,6 +42,7 @@ struct PackSegHost {
 struct ConvGroupHost {
   SrcRef src[kMaxSrc];
   int out_tensor, out_chunk0;
+  int pool_tensor = -1;       // >= 0: fused ReLU + max-pool epilogue writes this pooled tensor (out_tensor unused)
   int out_phase = -1;         // >= 0: write one phase plane of a P8S2 tensor (stride-2 dgrad)
   int aux_tensor, aux_chunk0, aux_nchunks;
   size_t w_off, bias_off;     // into the workspace
@@ -116,6 +117,7 @@ Plan* build_plan(int kind, int mb, int precision);
 int add_tensor(Plan& p, const std::string& name, int C, int H, int W, int layout);
 PackSeg make_seg(const Plan& p, const PackSegHost& h, const void* const* state);
 void choose_tiling(ConvOpHost& op);
+int persist_stages_for(const ConvOpHost& op, size_t extra);
 int plan_pack_eval(Plan& p, const void* const* state, cudaStream_t stream);
 int plan_forward_eval(Plan& p, const float* x, int n, float* out0, float* out1, cudaStream_t stream);
 

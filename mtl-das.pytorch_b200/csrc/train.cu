@@ -177,7 +177,7 @@ TrainPlan* build_train_plan(int kind, int batch, int precision) {
         tp.bns[bn].segs.push_back(TrainPlan::BnSeg{s.layer, inf.g[g].out_chunk0 * 8 + s.cout_off, p.layers[s.layer].cout});
     ConvOpHost f = inf;  // same sources / taps / tiling; raw output, no bias, no fused activation
     f.name = "fwd:" + inf.name, f.epi = EPI_NONE;
-    for (int g = 0; g < f.ngroups; ++g) f.g[g].out_tensor = y, f.g[g].aux_tensor = -1;
+    for (int g = 0; g < f.ngroups; ++g) f.g[g].out_tensor = y, f.g[g].aux_tensor = -1, f.g[g].pool_tensor = -1;
     p.convs.push_back(f);
     tp.fconv_of[ci] = (int)p.convs.size() - 1;
     tp.fwd.push_back({TOP_CONV, tp.fconv_of[ci], 0});
@@ -189,7 +189,10 @@ TrainPlan* build_train_plan(int kind, int batch, int precision) {
     e.ntasks = 1, e.nchunks = p.tensors[out_t].nchunks;
     if (inf.epi == EPI_RELU) {
       e.mode = EW_RELU;
-      if (oi + 1 < inf_prog.size() && inf_prog[oi + 1].kind == 2 && p.pools[inf_prog[oi + 1].index].in_tensor == out_t) {
+      if (inf.g[0].pool_tensor >= 0) {  // inference fuses the pool into this conv's epilogue
+        e.mode = EW_RELU_POOL;
+        e.out = inf.g[0].pool_tensor;
+      } else if (oi + 1 < inf_prog.size() && inf_prog[oi + 1].kind == 2 && p.pools[inf_prog[oi + 1].index].in_tensor == out_t) {
         e.mode = EW_RELU_POOL;
         e.out = p.pools[inf_prog[oi + 1].index].out_tensor;
       }

@@ -53,6 +53,7 @@ struct ConvGroupDev {
   ActView aux;
   int aux_nchunks;         // aux chunk = (output chunk) % aux_nchunks (tasks sharing one feature map)
   int pad_;
+  ActView pool_out;        // fused ReLU + 2x2 ceil max-pool: pooled tensor (persistent kernel, pool_k > 0)
 };
 struct ConvParams {
   int H, W, Wp, Pimg;      // output geometry
@@ -72,6 +73,8 @@ struct ConvParams {
   int swap_desc;           // debug: swap the LBO/SBO roles in the UMMA descriptors
   int ngroups;
   unsigned long long magic_pimg, magic_wp;  // floor(2^40/d)+1: exact f/d for f < 2^22 by multiply-shift
+  int pool_k;              // > 0: fused max-pool, the CTA tile is pool_k image-row pairs (2*Wp*pool_k positions)
+  int pool_Wpo, pool_Pimgo; // pooled geometry
   int ksplit;              // ring kernel: even/odd K steps accumulate into two TMEM sets (summed in the epilogue)
   int acc_sets;            // persistent kernel: TMEM accumulator sets (1 or 2), chosen by the launcher
   int persist_stages;      // > 0: resident weights, persistent pipelined kernel with this many slab stages

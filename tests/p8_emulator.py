@@ -125,6 +125,17 @@ class Emu:
             elif op["epi"] == 1:
                 y = torch.relu(y)
             on, oc0 = g["out"]
+            if "pool" in g:      # fused ReLU + MaxPool2d(2,2,ceil): only the pooled tensor is written
+                full = torch.zeros(self.nb, op["Cout"], H, W, dtype=torch.float64)
+                full[n[valid], :, h[valid], w[valid]] = y[valid]
+                pooled = torch.nn.functional.max_pool2d(full, 2, 2, ceil_mode=True)
+                pi = self.t[g["pool"]]["info"]
+                fo, no, ho, wo, vo = self.coords(pi["H"], pi["W"])
+                for c in range(op["Cout"] // 8):
+                    vals = torch.zeros(len(fo), 8, dtype=torch.float64)
+                    vals[vo] = pooled[no[vo], c * 8:(c + 1) * 8, ho[vo], wo[vo]]
+                    self.scatter(g["pool"], oc0 + c, fo, no, ho, wo, vo, vals)
+                continue
             for c in range(op["Cout"] // 8):
                 self.scatter(on, oc0 + c, f, n, h, w, valid, y[:, c * 8:(c + 1) * 8])
 
