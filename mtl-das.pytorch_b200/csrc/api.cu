@@ -46,6 +46,10 @@ mtldas_plan* mtldas_plan_create(int model_kind, int micro_batch, int precision) 
   h->p->use_graphs = (ng && ng[0] == '1') ? 0 : 1;
   const char* np = getenv("MTLDAS_NO_PDL");
   h->p->use_pdl = (np && np[0] == '1') ? 0 : 1;
+  // tensor-core stem (stem_umma.cu) is correct but measured slower than the FFMA2 stem on B200 (0.85 vs 0.58 ms per
+  // 4096 patches: its stage/build/drain phases serialise per tile); opt in with MTLDAS_UMMA_STEM=1
+  const char* nus = getenv("MTLDAS_UMMA_STEM");
+  h->p->use_umma_stem = (nus && nus[0] == '1') ? 1 : 0;
   const char* npz = getenv("MTLDAS_NO_PERSIST");
   h->p->use_persist = (npz && npz[0] == '1') ? 0 : 1;
   return h;

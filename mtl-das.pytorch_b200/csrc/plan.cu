@@ -386,6 +386,7 @@ Plan* build_plan(int kind, int mb, int precision) {
     }
   p.stem_w_off = take(49 * 16 * 4);
   p.stem_b_off = take(16 * 4);
+  p.stem_wu_off = take(2048);
   // host entry point: chunks of at most 1024 patches through two staging slots (H2D of chunk i+1 overlaps chunk i)
   p.host_chunk = std::min(mb, 1024);
   p.x_stage_off = take((size_t)2 * p.host_chunk * kPatchH * kPatchW * 4);
@@ -495,6 +496,11 @@ int plan_pack_eval(Plan& p, const void* const* state, cudaStream_t stream) {
     q.bias_dst = reinterpret_cast<float*>(p.ws + p.stem_b_off);
     q.Cout_p = 16, q.K_tap = 1, q.fp32 = 1, q.fold = 1, q.eps = 1e-5f;
     CK(launch_pack(q, stream));
+    if (p.precision == 0) {  // bf16 tensor-core stem: taps are the K dimension (49 -> 64)
+      CK(cudaMemsetAsync(p.ws + p.stem_wu_off, 0, 2048, stream));
+      q.seg.k_from_tap = 1, q.dst = p.ws + p.stem_wu_off, q.K_tap = 64, q.fp32 = 0;
+      CK(launch_pack(q, stream));
+    }
   }
   p.packed = true;
   return 0;
@@ -526,6 +532,7 @@ static int run_pass(Plan& p, const float* x, int nb, float* out0, float* out1, c
       q.out = p.view(p.stem_out, 0);
       q.Hin = kPatchH, q.Win = kPatchW, q.H = t.H, q.W = t.W, q.Wp = t.Wp, q.Pimg = t.Pimg;
       q.body = (long long)nb * t.Pimg;
+      q.w_umma = (p.precision == 0 && p.use_umma_stem) ? p.ws + p.stem_wu_off : nullptr;
       CK(launch_stem(q, p.precision, stream, pdl));
     } else if (op.kind == 1) {
       ConvParams q = p.conv_params(p.convs[op.index], nb);

@@ -79,7 +79,8 @@ struct Plan {
   std::vector<HeadOpHost> heads;
   std::vector<Op> program;
   int stem_layer, stem_out;
-  size_t stem_w_off, stem_b_off;
+  size_t stem_w_off, stem_b_off, stem_wu_off = 0;
+  int use_umma_stem = 0;
   size_t x_stage_off, out_stage_off;
   int host_chunk = 0;
   size_t ws_bytes;

@@ -91,6 +91,7 @@ struct StemParams {        // 7x7 / stride 3 / pad 2, Cin = 1 (modelA_MTL.py:74)
   int Hin, Win, H, W, Wp, Pimg;
   long long body;
   int raw;                 // 1: store conv + bias without the ReLU (training: BatchNorm follows as its own pass)
+  const char* w_umma;      // bf16 UMMA image [8 K-chunks][16 cout][8] (K = 49 taps padded to 64) or null
 };
 
 struct PoolParams {        // MaxPool2d(2,2,ceil_mode=True) (modelA_MTL.py:116)
@@ -122,6 +123,7 @@ struct PackSeg {           // one source layer scattered into a packed weight bl
   // input channels [ci_lo, ci_lo+ci_n) (at cout_off); tap_map selects / reorders taps (-1 = tap not used)
   int transpose, ci_lo, ci_n;
   int tap_map[9];
+  int k_from_tap;          // stem: the filter taps ARE the K dimension (k = r*ksize+s, single packed tap)
 };
 struct PackParams {
   PackSeg seg;
