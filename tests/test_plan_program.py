@@ -65,3 +65,22 @@ def test_modules_keep_reference_contract():
     m.eval()
     with pytest.raises(MtldasError):
         m(torch.zeros(1, 1, 100, 250))
+
+
+def test_model_c_boundary_class_and_launcher():
+    """Model C keeps its constructor / state_dict contract (566 keys) and refuses to run (kernels are
+    the next row); the launcher binds an (absent here or present) reference utils.py to the drop-in modules."""
+    from model.modelC_multiClassifier import Multi_Classifier
+    from mtldas_b200 import MtldasError
+    m = Multi_Classifier(init_weights=False)
+    sd = m.state_dict()
+    assert len(sd) == 566 and sum(p.numel() for p in m.parameters()) == 21850560
+    assert tuple(sd["Conv2d_1a_3x3.conv.weight"].shape) == (32, 1, 3, 3) and tuple(sd["fc.weight"].shape) == (32, 2048)
+    assert not any(k.startswith("AuxLogits") for k in sd)
+    with pytest.raises(MtldasError):
+        m(torch.zeros(1, 1, 100, 250))
+    from mtldas_b200 import run_reference
+    run_reference.prepare()
+    import sys
+    from mtldas_b200 import nets
+    assert sys.modules["model.modelA_MTL"].MTL_Net is nets.MTL_Net
