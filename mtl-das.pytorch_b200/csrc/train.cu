@@ -339,7 +339,7 @@ TrainPlan* build_train_plan(int kind, int batch, int precision) {
   };
   for (auto& t : p.tensors) t.offset = take(t.bytes);
   tp.zero_fwd_off = o;  // [zero_fwd_off, zero_fwd_end): BN sums, cleared at every forward
-  for (auto& b : tp.bns) b.sum_off = take((size_t)b.C * 2 * sizeof(double));
+  for (auto& b : tp.bns) b.sum_off = take((size_t)b.C * 2 * sizeof(double) + 16);  // + completion counter
   tp.zero_fwd_end = o;
   tp.zero_bwd_off = o;  // cleared at every backward: BN reductions and packed weight-gradient buffers
   for (auto& b : tp.bns) b.red_off = take((size_t)b.C * 2 * sizeof(double));
@@ -463,6 +463,7 @@ static int train_forward_eager(TrainPlan& tp, const void* const* state, const fl
   float* logp1 = logp0 + (size_t)p.mb * 16;
   OpTimer timer(st);
   for (auto& op : tp.fwd) {
+    if (op.kind == TOP_FINAL) continue;  // folded into the statistics kernel
     timer.begin(op.kind);
     if (op.kind == TOP_STEM) {
       const TensorInfo& t = p.tensors[tp.y_stem];
@@ -482,22 +483,22 @@ static int train_forward_eager(TrainPlan& tp, const void* const* state, const fl
       q.y = p.view(b.tensor, 0), q.nchunks = b.C / 8, q.body = (long long)nb * p.tensors[b.tensor].Pimg;
       BnArrays a = bn_arrays(tp, op.a);
       q.sum = a.sum, q.sumsq = a.sumsq;
-      CK(launch_stats(q, p.precision, st));
-    } else if (op.kind == TOP_FINAL) {
-      const TrainPlan::BnHost& b = tp.bns[op.a];
-      FinalizeParams q{};
-      q.bn = bn_arrays(tp, op.a), q.C = b.C, q.n = (double)nb * b.H * b.W, q.eps = 1e-5f, q.momentum = 0.1f;
-      q.nseg = (int)b.segs.size();
-      for (int s = 0; s < q.nseg; ++s) {
+      q.done = reinterpret_cast<unsigned int*>(p.ws + b.sum_off + (size_t)b.C * 2 * sizeof(double));
+      FinalizeParams& fq = q.fin;  // performed by the last stats block
+      fq.bn = a, fq.C = b.C, fq.n = (double)nb * b.H * b.W, fq.eps = 1e-5f, fq.momentum = 0.1f;
+      fq.nseg = (int)b.segs.size();
+      for (int s = 0; s < fq.nseg; ++s) {
         const LayerSpec& L = p.layers[b.segs[s].layer];
-        FinalizeSeg& fs = q.seg[s];
+        FinalizeSeg& fs = fq.seg[s];
         fs.gamma = (const float*)state[L.i_gamma], fs.beta = (const float*)state[L.i_beta];
         fs.running_mean = (float*)state[L.i_rm], fs.running_var = (float*)state[L.i_rv];
         fs.num_batches_tracked = (long long*)state[L.i_nbt];
         fs.conv_bias = L.i_b >= 0 ? (const float*)state[L.i_b] : nullptr;
         fs.ch_off = b.segs[s].ch_off, fs.count = b.segs[s].count;
       }
-      CK(launch_finalize(q, st));
+      CK(launch_stats(q, p.precision, st));
+    } else if (op.kind == TOP_FINAL) {
+      continue;  // folded into the statistics kernel
     } else if (op.kind == TOP_EW) {
       EwParams q = ew_params(tp, tp.ews[op.a], nb);
       CK(launch_ew_fwd(q, p.precision, st));
@@ -538,7 +539,9 @@ static int train_backward_eager(TrainPlan& tp, const void* const* state, const f
   float* logp0 = reinterpret_cast<float*>(p.ws + tp.logp_off);
   float* logp1 = logp0 + (size_t)p.mb * 16;
   OpTimer timer(st);
+  std::vector<UnpackParams> unpacks;  // packed weight gradients -> parameter layout, one batched launch at the end
   for (auto& op : tp.bwd) {
+    if (op.kind == TOP_BNGRAD) continue;  // written by the elementwise backward's second pass
     timer.begin(op.kind);
     if (op.kind == TOP_HEADBWD) {
       const HeadOpHost& h = p.heads[op.a];
@@ -559,14 +562,25 @@ static int train_backward_eager(TrainPlan& tp, const void* const* state, const f
       q.dz = p.view(e.dz, 0), q.dy = p.view(e.dy, 0);
       q.want_daux = e.daux >= 0, q.daux_accum = e.daux_accum;
       if (e.daux >= 0) q.daux = p.view(e.daux, 0);
+      auto set_gsegs = [&](int bi) {
+        const TrainPlan::BnHost& b = tp.bns[bi];
+        q.ngseg = (int)b.segs.size();
+        for (int s = 0; s < q.ngseg; ++s) {
+          const TrainPlan::ParamOff& po = tp.param_off[b.segs[s].layer];
+          q.gseg[s] = BnGradSeg{grads + po.gamma, grads + po.beta, b.segs[s].ch_off, b.segs[s].count};
+        }
+      };
+      set_gsegs(e.bn);
       CK(launch_ew_bwd(q, 0, p.precision, st));
       CK(launch_ew_bwd(q, 1, p.precision, st));
       if (e.mode == EW_ADD_RELU_SC) {  // the shortcut branch shares g; its own BatchNorm gives its own dy
         q.second = 1, q.dy = p.view(e.dy2, 0), q.want_daux = 0;
+        set_gsegs(e.bn2);
         CK(launch_ew_bwd(q, 0, p.precision, st));
         CK(launch_ew_bwd(q, 1, p.precision, st));
       }
     } else if (op.kind == TOP_BNGRAD) {
+      continue;  // written by the elementwise backward's second pass
       const TrainPlan::BnHost& b = tp.bns[op.a];
       BnGradParams q{};
       q.bn = bn_arrays(tp, op.a), q.nseg = (int)b.segs.size();
@@ -597,7 +611,7 @@ static int train_backward_eager(TrainPlan& tp, const void* const* state, const f
         u.src = q.dw, u.dst = grads + tp.param_off[sh.layer].w;
         u.cout = L.cout, u.cin = L.cin, u.ksize = L.ksize, u.split = sh.split, u.k_off = sh.k_off, u.cout_off = sh.cout_off;
         u.Cout_p = f.Cout, u.K_tap = f.nchunks * 8;
-        CK(launch_unpack(u, st));
+        unpacks.push_back(u);
       }
     } else if (op.kind == TOP_DGRAD) {
       ConvParams q = p.conv_params(p.convs[tp.dgrads[op.a].conv], nb);
@@ -612,11 +626,13 @@ static int train_backward_eager(TrainPlan& tp, const void* const* state, const f
       UnpackParams u{};
       u.src = q.dw, u.dst = grads + tp.param_off[p.stem_layer].w;
       u.cout = 16, u.cin = 1, u.ksize = 7, u.split = INT_MAX, u.k_off = 0, u.cout_off = 0, u.Cout_p = 16, u.K_tap = 1;
-      CK(launch_unpack(u, st));
+      unpacks.push_back(u);
     }
     timer.end();
     ++tp.launches;
   }
+  CK(launch_unpack_batch(unpacks.data(), (int)unpacks.size(), st));
+  ++tp.launches;
   timer.report("backward");
   (void)state;
   return 0;

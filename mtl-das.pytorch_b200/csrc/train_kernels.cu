@@ -67,6 +67,32 @@ __device__ __forceinline__ void block_reduce8_atomic(float* v, double* dst, floa
 
 }  // namespace
 
+__device__ __forceinline__ void finalize_channel(const FinalizeParams& p, int c) {
+  if (c >= p.C) return;
+  const double mean = __ldcg(p.bn.sum + c) / p.n;  // L2 reads: the sums were produced by other blocks' atomics
+  double var = __ldcg(p.bn.sumsq + c) / p.n - mean * mean;
+  if (var < 0.0) var = 0.0;
+  const double invstd = rsqrt(var + (double)p.eps);
+  float scale = 0.f, shift = 0.f, fm = 0.f, fi = 0.f;
+  for (int s = 0; s < p.nseg; ++s) {
+    const FinalizeSeg& g = p.seg[s];
+    if (c >= g.ch_off && c < g.ch_off + g.count) {
+      const int i = c - g.ch_off;
+      fm = (float)mean, fi = (float)invstd;
+      scale = (float)((double)g.gamma[i] * invstd);
+      shift = (float)((double)g.beta[i] - mean * (double)g.gamma[i] * invstd);
+      const double bias = g.conv_bias ? (double)g.conv_bias[i] : 0.0;
+      const double unbiased = p.n > 1.0 ? var * p.n / (p.n - 1.0) : var;
+      g.running_mean[i] = (float)((1.0 - p.momentum) * (double)g.running_mean[i] + p.momentum * (mean + bias));
+      g.running_var[i] = (float)((1.0 - p.momentum) * (double)g.running_var[i] + p.momentum * unbiased);
+      if (i == 0) *g.num_batches_tracked += 1;
+    }
+  }
+  p.bn.scale[c] = scale, p.bn.shift[c] = shift, p.bn.mean[c] = fm, p.bn.invstd[c] = fi;
+}
+
+__global__ void finalize_kernel(const __grid_constant__ FinalizeParams p) { finalize_channel(p, threadIdx.x); }
+
 // ---------------------------------------------------------------------------------------------
 // batch statistics: per-channel sum and sum of squares (pads and guards are zero -> planes are summed whole)
 // grid (ceil(body/1024), nchunks), block 256
@@ -91,6 +117,15 @@ __global__ void __launch_bounds__(256) stats_kernel(const __grid_constant__ Stat
   }
   block_reduce8_atomic(s, p.sum + c * 8, sh);
   block_reduce8_atomic(q, p.sumsq + c * 8, sh);
+  // last block to finish turns the sums into scale / shift / running statistics (no separate finalize launch)
+  __shared__ unsigned int last;
+  __threadfence();
+  if (threadIdx.x == 0) last = atomicAdd(p.done, 1u) == gridDim.x * gridDim.y - 1 ? 1u : 0u;
+  __syncthreads();
+  if (last) {
+    __threadfence();
+    finalize_channel(p.fin, threadIdx.x);
+  }
 }
 
 cudaError_t launch_stats(const StatsParams& p, int precision, cudaStream_t st) {
@@ -105,31 +140,6 @@ cudaError_t launch_stats(const StatsParams& p, int precision, cudaStream_t st) {
 // ---------------------------------------------------------------------------------------------
 // finalize: mean / invstd / scale / shift, running statistics (one block, one thread per channel)
 // ---------------------------------------------------------------------------------------------
-__global__ void finalize_kernel(const __grid_constant__ FinalizeParams p) {
-  const int c = threadIdx.x;
-  if (c >= p.C) return;
-  const double mean = p.bn.sum[c] / p.n;
-  double var = p.bn.sumsq[c] / p.n - mean * mean;
-  if (var < 0.0) var = 0.0;
-  const double invstd = rsqrt(var + (double)p.eps);
-  float scale = 0.f, shift = 0.f, fm = 0.f, fi = 0.f;
-  for (int s = 0; s < p.nseg; ++s) {
-    const FinalizeSeg& g = p.seg[s];
-    if (c >= g.ch_off && c < g.ch_off + g.count) {
-      const int i = c - g.ch_off;
-      fm = (float)mean, fi = (float)invstd;
-      scale = (float)((double)g.gamma[i] * invstd);
-      shift = (float)((double)g.beta[i] - mean * (double)g.gamma[i] * invstd);
-      const double bias = g.conv_bias ? (double)g.conv_bias[i] : 0.0;
-      const double unbiased = p.n > 1.0 ? var * p.n / (p.n - 1.0) : var;
-      g.running_mean[i] = (float)((1.0 - p.momentum) * (double)g.running_mean[i] + p.momentum * (mean + bias));
-      g.running_var[i] = (float)((1.0 - p.momentum) * (double)g.running_var[i] + p.momentum * unbiased);
-      if (i == 0) *g.num_batches_tracked += 1;
-    }
-  }
-  p.bn.scale[c] = scale, p.bn.shift[c] = shift, p.bn.mean[c] = fm, p.bn.invstd[c] = fi;
-}
-
 cudaError_t launch_finalize(const FinalizeParams& p, cudaStream_t st) {
   finalize_kernel<<<1, 256, 0, st>>>(p);
   return cudaGetLastError();
@@ -262,6 +272,22 @@ cudaError_t launch_ew_fwd(const EwParams& p, int precision, cudaStream_t st) {
 // fused elementwise backward.  PASS 0: reductions sum(g), sum(g*y_hat); PASS 1: dy (and d aux).
 // g = dz * activation'(.) is recomputed in both passes from dz and the saved raw tensors.
 // ---------------------------------------------------------------------------------------------
+// d gamma / d beta of chunk c (all tasks) from the completed reductions: written once, by the thread at f == 0
+__device__ __forceinline__ void write_bn_grads(const EwParams& p, const BnArrays& bn, int c) {
+  const int ntask = p.mode == EW_RELU_POOL ? 1 : p.ntasks;
+  for (int t = 0; t < ntask; ++t)
+    for (int j = 0; j < 8; ++j) {
+      const int ch = (t * p.nchunks + c) * 8 + j;
+      for (int s = 0; s < p.ngseg; ++s) {
+        const BnGradSeg& g = p.gseg[s];
+        if (ch >= g.ch_off && ch < g.ch_off + g.count) {
+          g.dgamma[ch - g.ch_off] = (float)bn.red_gy[ch];
+          g.dbeta[ch - g.ch_off] = (float)bn.red_g[ch];
+        }
+      }
+    }
+}
+
 template <typename T, int PASS>
 __global__ void __launch_bounds__(256) ew_bwd_kernel(const __grid_constant__ EwParams p) {
   __shared__ float sh[8][8];
@@ -336,6 +362,7 @@ __global__ void __launch_bounds__(256) ew_bwd_kernel(const __grid_constant__ EwP
         }
       }
     }
+    if (PASS == 1 && f == 0) write_bn_grads(p, bn, c);
     if (PASS == 0) {
       block_reduce8_atomic(rg, bn.red_g + c * 8, sh);
       block_reduce8_atomic(rgy, bn.red_gy + c * 8, sh);
@@ -431,6 +458,7 @@ __global__ void __launch_bounds__(256) ew_bwd_kernel(const __grid_constant__ EwP
       block_reduce8_atomic(rgy, bn.red_gy + ch * 8, sh);
     }
   }
+  if (PASS == 1 && f == 0) write_bn_grads(p, bn, c);
   if (PASS == 1 && p.want_daux && !p.second) {
 #pragma unroll
     for (int i = 0; i < kEwPpt; ++i) {
@@ -828,6 +856,33 @@ __global__ void __launch_bounds__(256) unpack_kernel(const __grid_constant__ Unp
   if (ci >= p.split) tap += 1, k -= p.split;
   k += p.k_off;
   p.dst[i] = p.src[((size_t)tap * p.K_tap + k) * p.Cout_p + p.cout_off + co];
+}
+
+__global__ void __launch_bounds__(256) unpack_batch_kernel(const __grid_constant__ UnpackBatch b) {
+  const UnpackParams& p = b.u[blockIdx.y];
+  const int kk = p.ksize * p.ksize;
+  const int total = p.cout * p.cin * kk;
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
+    const int co = i / (p.cin * kk);
+    const int r1 = i - co * (p.cin * kk);
+    const int ci = r1 / kk;
+    int tap = r1 - ci * kk, k = ci;
+    if (ci >= p.split) tap += 1, k -= p.split;
+    k += p.k_off;
+    p.dst[i] = p.src[((size_t)tap * p.K_tap + k) * p.Cout_p + p.cout_off + co];
+  }
+}
+
+cudaError_t launch_unpack_batch(const UnpackParams* u, int n, cudaStream_t st) {
+  static UnpackBatch b;
+  for (int i0 = 0; i0 < n; i0 += kUnpackBatch) {
+    const int m = std::min(kUnpackBatch, n - i0);
+    for (int i = 0; i < m; ++i) b.u[i] = u[i0 + i];
+    unpack_batch_kernel<<<dim3(48, m), 256, 0, st>>>(b);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 cudaError_t launch_unpack(const UnpackParams& p, cudaStream_t st) {

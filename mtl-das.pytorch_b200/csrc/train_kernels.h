@@ -15,5 +15,6 @@ cudaError_t launch_wgrad(const WgradParams& p, int precision, cudaStream_t st);
 cudaError_t launch_stem_wgrad(const StemWgradParams& p, int precision, cudaStream_t st);
 cudaError_t launch_head_bwd(const HeadBwdParams& p, int precision, cudaStream_t st);
 cudaError_t launch_unpack(const UnpackParams& p, cudaStream_t st);
+cudaError_t launch_unpack_batch(const UnpackParams* u, int n, cudaStream_t st);
 
 }  // namespace mtldas

@@ -28,6 +28,12 @@ struct BnArrays {
   float* invstd;   // [C]
 };
 
+struct BnGradSeg {       // d gamma / d beta of one reference BatchNorm out of a tensor's reduction arrays
+  float* dgamma;
+  float* dbeta;
+  int ch_off, count;
+};
+
 struct EwParams {
   int mode;
   int ntasks;            // tasks stacked along channels that share `aux` (EW_SIGMOID_MUL), else 1
@@ -47,16 +53,11 @@ struct EwParams {
   ActView daux;          // backward: gradient w.r.t. aux
   int daux_accum;        // 1: daux += , 0: daux =
   int want_daux;
+  int ngseg;             // backward pass 1 also writes d gamma / d beta of the BatchNorm it differentiates
+  BnGradSeg gseg[2];
   int second;            // EW_ADD_RELU_SC backward: 1 = this launch handles the shortcut branch (y2/bn2 are "main")
 };
 
-struct StatsParams {     // sum / sum of squares of a raw tensor (pads are zero, so whole planes are summed)
-  ActView y;
-  int nchunks;
-  long long body;
-  double* sum;
-  double* sumsq;
-};
 
 struct FinalizeSeg {     // channels [ch_off, ch_off+count) of the tensor belong to one reference BatchNorm
   const float* gamma;
@@ -76,11 +77,16 @@ struct FinalizeParams {
   FinalizeSeg seg[2];
 };
 
-struct BnGradSeg {       // d gamma / d beta of one reference BatchNorm out of a tensor's reduction arrays
-  float* dgamma;
-  float* dbeta;
-  int ch_off, count;
+struct StatsParams {     // sum / sum of squares of a raw tensor (pads are zero, so whole planes are summed);
+  ActView y;             // the last block to finish also finalizes the BatchNorm (fin), so no second launch
+  int nchunks;
+  long long body;
+  double* sum;
+  double* sumsq;
+  unsigned int* done;    // completion counter (zeroed with the sums)
+  FinalizeParams fin;
 };
+
 struct BnGradParams {
   BnArrays bn;
   int nseg;
@@ -119,6 +125,11 @@ struct UnpackParams {    // packed fp32 gradient [tap][K][Cout_p] -> reference l
   const float* src;
   float* dst;
   int cout, cin, ksize, split, k_off, cout_off, Cout_p, K_tap;
+};
+
+constexpr int kUnpackBatch = 96;
+struct UnpackBatch {
+  UnpackParams u[kUnpackBatch];
 };
 
 }  // namespace mtldas
