@@ -190,7 +190,7 @@ def measure_train(args, dev, world, rank, barrier):
     m.precision = args.precision
     m.load_state_dict(O.synth_state_dict("MTL", seed=0), strict=True)
     m = m.to(dev).train()
-    opt = torch.optim.Adam(m.parameters(), lr=1e-3 / 1.5, weight_decay=1e-5)       # utils.py:133-134,247
+    opt = torch.optim.Adam(m.parameters(), lr=1e-3 / 1.5, weight_decay=1e-5, fused=True)   # utils.py:133-134,247
     trainer = DataParallelTrainer(m, opt)
     base, yd, ye = O.synth_patches(64, seed=4321 + rank)
     reps = (nb + 63) // 64

@@ -66,6 +66,7 @@ class DataParallelTrainer:
         self.module, self.optimizer, self.group = module, optimizer, group
         self.params = [p for _, p in module.named_parameters()]
         self._flat = None
+        self._idx = None
 
     def step(self, x_local: torch.Tensor, labels_local: Sequence[torch.Tensor]):
         """x_local / labels_local: this rank's shard. Returns the local loss (python float is NOT taken here)."""
@@ -76,16 +77,14 @@ class DataParallelTrainer:
         n = x_local.shape[0]
         douts, loss = [], 0.0
         for o, y in zip(outs, labels_local):      # NLLLoss (mean) per task, summed -- utils.py:139,361,367
-            idx = torch.arange(n, device=o.device)
-            loss = loss + (-o[idx, y.long()]).mean()
-            d = torch.zeros_like(o)
-            d[idx, y.long()] = -1.0 / n
-            douts.append(d)
-        if self._flat is None:
+            onehot = torch.nn.functional.one_hot(y.long(), o.shape[1]).to(o.dtype)
+            loss = loss - (o * onehot).sum() / n
+            douts.append(onehot * (-1.0 / n))
+        if self._flat is None or self._flat.device != x_local.device:
             self._flat = torch.empty(plan.n_params, dtype=torch.float32, device=x_local.device)
+            for p, g in zip(self.params, unflatten_like(self._flat, self.params)):
+                p.grad = g                         # views of the flat buffer: bound once, refilled every step
         plan.backward(douts, self._flat)
         allreduce_mean_(self._flat, self.group)
-        for p, g in zip(self.params, unflatten_like(self._flat, self.params)):
-            p.grad = g
         self.optimizer.step()
         return loss
