@@ -314,7 +314,7 @@ def run_ours(args):
             pass
         ach = conv_bytes / (conv_ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
-                "kernel": "conv_umma_kernel" if args.precision == "bf16" else "conv_fp32_kernel",
+                "kernel": "conv_umma_persist_kernel (+ conv_umma_kernel on the deep layers)" if args.precision == "bf16" else "conv_fp32_kernel",
                 "launches_per_step": n_conv, "avg_launch_ms": conv_ms / n_conv,
                 "algorithmic_bytes_per_step": conv_bytes, "peak_source": peak_src,
                 "share_of_step": conv_ms / sum(per_op_ms),

@@ -401,7 +401,9 @@ static EwParams ew_params(const TrainPlan& tp, const TrainPlan::EwHost& e, int n
     const TensorInfo& to = p.tensors[e.out];
     q.Ho = to.H, q.Wo = to.W, q.Wpo = to.Wp, q.Pimgo = to.Pimg;
     q.body = (long long)nb * to.Pimg;
+    q.magic_pimgo = (1ull << 40) / (unsigned long long)q.Pimgo + 1, q.magic_wpo = (1ull << 40) / (unsigned long long)q.Wpo + 1;
   }
+  q.magic_pimg = (1ull << 40) / (unsigned long long)q.Pimg + 1, q.magic_wp = (1ull << 40) / (unsigned long long)q.Wp + 1;
   return q;
 }
 

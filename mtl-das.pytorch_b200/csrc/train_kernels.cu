@@ -67,84 +67,6 @@ __device__ __forceinline__ void block_reduce8_atomic(float* v, double* dst, floa
 
 }  // namespace
 
-__device__ __forceinline__ void finalize_channel(const FinalizeParams& p, int c) {
-  if (c >= p.C) return;
-  const double mean = __ldcg(p.bn.sum + c) / p.n;  // L2 reads: the sums were produced by other blocks' atomics
-  double var = __ldcg(p.bn.sumsq + c) / p.n - mean * mean;
-  if (var < 0.0) var = 0.0;
-  const double invstd = rsqrt(var + (double)p.eps);
-  float scale = 0.f, shift = 0.f, fm = 0.f, fi = 0.f;
-  for (int s = 0; s < p.nseg; ++s) {
-    const FinalizeSeg& g = p.seg[s];
-    if (c >= g.ch_off && c < g.ch_off + g.count) {
-      const int i = c - g.ch_off;
-      fm = (float)mean, fi = (float)invstd;
-      scale = (float)((double)g.gamma[i] * invstd);
-      shift = (float)((double)g.beta[i] - mean * (double)g.gamma[i] * invstd);
-      const double bias = g.conv_bias ? (double)g.conv_bias[i] : 0.0;
-      const double unbiased = p.n > 1.0 ? var * p.n / (p.n - 1.0) : var;
-      g.running_mean[i] = (float)((1.0 - p.momentum) * (double)g.running_mean[i] + p.momentum * (mean + bias));
-      g.running_var[i] = (float)((1.0 - p.momentum) * (double)g.running_var[i] + p.momentum * unbiased);
-      if (i == 0) *g.num_batches_tracked += 1;
-    }
-  }
-  p.bn.scale[c] = scale, p.bn.shift[c] = shift, p.bn.mean[c] = fm, p.bn.invstd[c] = fi;
-}
-
-__global__ void finalize_kernel(const __grid_constant__ FinalizeParams p) { finalize_channel(p, threadIdx.x); }
-
-// ---------------------------------------------------------------------------------------------
-// batch statistics: per-channel sum and sum of squares (pads and guards are zero -> planes are summed whole)
-// grid (ceil(body/1024), nchunks), block 256
-// ---------------------------------------------------------------------------------------------
-template <typename T>
-__global__ void __launch_bounds__(256) stats_kernel(const __grid_constant__ StatsParams p) {
-  __shared__ float sh[8][8];
-  const int c = blockIdx.y;
-  float s[8], q[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
-  const long long base = (long long)blockIdx.x * 1024 + threadIdx.x;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const long long f = base + i * 256;
-    if (f < p.body) {
-      float v[8];
-      load8<T>(p.y.base + ((long long)c * p.y.plane + p.y.g_lo + f) * Gran<T>::bytes, v);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) s[j] += v[j], q[j] = fmaf(v[j], v[j], q[j]);
-    }
-  }
-  block_reduce8_atomic(s, p.sum + c * 8, sh);
-  block_reduce8_atomic(q, p.sumsq + c * 8, sh);
-  // last block to finish turns the sums into scale / shift / running statistics (no separate finalize launch)
-  __shared__ unsigned int last;
-  __threadfence();
-  if (threadIdx.x == 0) last = atomicAdd(p.done, 1u) == gridDim.x * gridDim.y - 1 ? 1u : 0u;
-  __syncthreads();
-  if (last) {
-    __threadfence();
-    finalize_channel(p.fin, threadIdx.x);
-  }
-}
-
-cudaError_t launch_stats(const StatsParams& p, int precision, cudaStream_t st) {
-  dim3 grid((unsigned)((p.body + 1023) / 1024), p.nchunks);
-  if (precision == 0)
-    stats_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(p);
-  else
-    stats_kernel<float><<<grid, 256, 0, st>>>(p);
-  return cudaGetLastError();
-}
-
-// ---------------------------------------------------------------------------------------------
-// finalize: mean / invstd / scale / shift, running statistics (one block, one thread per channel)
-// ---------------------------------------------------------------------------------------------
-cudaError_t launch_finalize(const FinalizeParams& p, cudaStream_t st) {
-  finalize_kernel<<<1, 256, 0, st>>>(p);
-  return cudaGetLastError();
-}
-
 __global__ void bn_grad_kernel(const __grid_constant__ BnGradParams p) {
   const int c = threadIdx.x;
   for (int s = 0; s < p.nseg; ++s) {
@@ -157,343 +79,6 @@ __global__ void bn_grad_kernel(const __grid_constant__ BnGradParams p) {
 }
 cudaError_t launch_bn_grad(const BnGradParams& p, cudaStream_t st) {
   bn_grad_kernel<<<1, 256, 0, st>>>(p);
-  return cudaGetLastError();
-}
-
-// ---------------------------------------------------------------------------------------------
-// fused BatchNorm apply + activation (forward)
-// thread = (position, chunk-of-a-task); EW_SIGMOID_MUL loops over the tasks that share the feature map;
-// EW_RELU_POOL: thread = (pooled position, chunk).
-// ---------------------------------------------------------------------------------------------
-#ifndef MTLDAS_EW_PPT
-#define MTLDAS_EW_PPT 1
-#endif
-constexpr int kEwPpt = MTLDAS_EW_PPT;  // positions per thread (per-channel BatchNorm constants are loaded once per thread)
-
-template <typename T>
-__global__ void __launch_bounds__(256) ew_fwd_kernel(const __grid_constant__ EwParams p) {
-  constexpr int G = Gran<T>::bytes;
-  if (p.mode == EW_RELU_POOL) {
-    const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
-    if (idx >= p.body * p.nchunks) return;
-    const int c = (int)(idx / p.body);
-    const int f = (int)(idx - (long long)c * p.body);
-    const Pos o = decode(f, p.Pimgo, p.Wpo, p.Ho, p.Wo);
-    float m[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) m[j] = 0.f;
-    if (o.valid) {
-      float sc[8], sh[8];
-      load_affine(p.bn.scale, c * 8, sc);
-      load_affine(p.bn.shift, c * 8, sh);
-#pragma unroll
-      for (int dy = 0; dy < 2; ++dy) {
-        const int h = 2 * o.h + dy;
-        if (h >= p.H) continue;
-#pragma unroll
-        for (int dx = 0; dx < 2; ++dx) {
-          const int w = 2 * o.w + dx;
-          if (w >= p.W) continue;
-          float v[8];
-          load8<T>(view_addr<T>(p.y, c, o.n * p.Pimg + h * p.Wp + w, o.n, h, w), v);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) m[j] = fmaxf(m[j], fmaf(v[j], sc[j], sh[j]));  // relu folded into max with 0
-        }
-      }
-    }
-    store8<T>(view_addr<T>(p.out, c, f, o.n, o.h, o.w), m);
-    return;
-  }
-  // thread = chunk c (of a task) x kEwPpt positions 256 apart; a block covers 1024 consecutive positions of one chunk
-  const long long per_chunk = (p.body + 256 * kEwPpt - 1) / (256 * kEwPpt) * (256 * kEwPpt);
-  const long long base = (long long)blockIdx.x * (256 * kEwPpt) + threadIdx.x;
-  const int c = (int)(base / per_chunk);
-  const int f0 = (int)(base - (long long)c * per_chunk);
-  for (int t = 0; t < p.ntasks; ++t) {
-    const int ch = t * p.nchunks + c;
-    float sc[8], sh[8], s2[8], h2[8];
-    load_affine(p.bn.scale, ch * 8, sc);
-    load_affine(p.bn.shift, ch * 8, sh);
-    if (p.mode == EW_ADD_RELU_SC) {
-      load_affine(p.bn2.scale, ch * 8, s2);
-      load_affine(p.bn2.shift, ch * 8, h2);
-    }
-#pragma unroll
-    for (int i = 0; i < kEwPpt; ++i) {
-      const int f = f0 + i * 256;
-      if (f >= p.body) continue;
-      const Pos q = decode(f, p.Pimg, p.Wp, p.H, p.W);
-      if (!q.valid && p.out.layout != LAY_P8) continue;
-      float z[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) z[j] = 0.f;
-      if (q.valid) {
-        float v[8];
-        load8<T>(p.y.base + ((long long)ch * p.y.plane + p.y.g_lo + f) * G, v);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = fmaf(v[j], sc[j], sh[j]);
-        if (p.mode == EW_RELU) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) z[j] = fmaxf(v[j], 0.f);
-        } else if (p.mode == EW_ADD_RELU_SC) {
-          float v2[8];
-          load8<T>(p.y2.base + ((long long)ch * p.y2.plane + p.y2.g_lo + f) * G, v2);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) z[j] = fmaxf(v[j] + fmaf(v2[j], s2[j], h2[j]), 0.f);
-        } else {
-          float aux[8];
-          load8<T>(view_addr<T>(p.aux, c, f, q.n, q.h, q.w), aux);
-          if (p.mode == EW_ADD_RELU_ID) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) z[j] = fmaxf(v[j] + aux[j], 0.f);
-          } else {  // EW_SIGMOID_MUL
-#pragma unroll
-            for (int j = 0; j < 8; ++j) z[j] = aux[j] / (1.f + expf(-v[j]));
-          }
-        }
-      }
-      store8<T>(view_addr<T>(p.out, ch, f, q.n, q.h, q.w), z);
-    }
-  }
-}
-
-cudaError_t launch_ew_fwd(const EwParams& p, int precision, cudaStream_t st) {
-  const long long total = p.body * p.nchunks;
-  const unsigned grid = p.mode == EW_RELU_POOL ? (unsigned)((total + 255) / 256)
-                                               : (unsigned)((p.body + 256 * kEwPpt - 1) / (256 * kEwPpt) * p.nchunks);
-  if (precision == 0)
-    ew_fwd_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(p);
-  else
-    ew_fwd_kernel<float><<<grid, 256, 0, st>>>(p);
-  return cudaGetLastError();
-}
-
-// ---------------------------------------------------------------------------------------------
-// fused elementwise backward.  PASS 0: reductions sum(g), sum(g*y_hat); PASS 1: dy (and d aux).
-// g = dz * activation'(.) is recomputed in both passes from dz and the saved raw tensors.
-// ---------------------------------------------------------------------------------------------
-// d gamma / d beta of chunk c (all tasks) from the completed reductions: written once, by the thread at f == 0
-__device__ __forceinline__ void write_bn_grads(const EwParams& p, const BnArrays& bn, int c) {
-  const int ntask = p.mode == EW_RELU_POOL ? 1 : p.ntasks;
-  for (int t = 0; t < ntask; ++t)
-    for (int j = 0; j < 8; ++j) {
-      const int ch = (t * p.nchunks + c) * 8 + j;
-      for (int s = 0; s < p.ngseg; ++s) {
-        const BnGradSeg& g = p.gseg[s];
-        if (ch >= g.ch_off && ch < g.ch_off + g.count) {
-          g.dgamma[ch - g.ch_off] = (float)bn.red_gy[ch];
-          g.dbeta[ch - g.ch_off] = (float)bn.red_g[ch];
-        }
-      }
-    }
-}
-
-template <typename T, int PASS>
-__global__ void __launch_bounds__(256) ew_bwd_kernel(const __grid_constant__ EwParams p) {
-  __shared__ float sh[8][8];
-  // a block never straddles two chunks: pool mode covers 256 pooled positions per block, the other modes 1024
-  // positions (kEwPpt per thread); the launcher sizes the grid accordingly
-  const int span = p.mode == EW_RELU_POOL ? 256 : 256 * kEwPpt;
-  const long long per_chunk = (p.body + span - 1) / span * span;
-  const long long idx2 = (long long)blockIdx.x * span + threadIdx.x;
-  const int c = (int)(idx2 / per_chunk);
-  const int f = (int)(idx2 - (long long)c * per_chunk);
-  const bool in_range = f < p.body;
-  constexpr int G = Gran<T>::bytes;
-  const BnArrays& bn = p.second ? p.bn2 : p.bn;     // the BatchNorm whose input gradient this launch produces
-  const ActView& ym = p.second ? p.y2 : p.y;
-
-  if (p.mode == EW_RELU_POOL) {
-    // thread = pooled position; the 2x2 window's four full-resolution positions belong to this thread alone
-    float rg[8], rgy[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) rg[j] = rgy[j] = 0.f;
-    Pos o = decode(in_range ? f : 0, p.Pimgo, p.Wpo, p.Ho, p.Wo);
-    if (in_range && o.valid) {
-      float sc[8], shf[8], mu[8], is[8], dzv[8];
-      load_affine(bn.scale, c * 8, sc);
-      load_affine(bn.shift, c * 8, shf);
-      load_affine(bn.mean, c * 8, mu);
-      load_affine(bn.invstd, c * 8, is);
-      load8<T>(view_addr<T>(p.dz, c, f, o.n, o.h, o.w), dzv);
-      float yv[4][8];
-      bool inb[4];
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const int h = 2 * o.h + (k >> 1), w = 2 * o.w + (k & 1);
-        inb[k] = h < p.H && w < p.W;
-        if (inb[k]) load8<T>(view_addr<T>(ym, c, o.n * p.Pimg + h * p.Wp + w, o.n, h, w), yv[k]);
-      }
-      int arg[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float best = -INFINITY;
-        arg[j] = 0;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          if (!inb[k]) continue;
-          const float r = fmaxf(fmaf(yv[k][j], sc[j], shf[j]), 0.f);
-          if (r > best) best = r, arg[j] = k;   // strict '>' : first maximum wins (scan order h, w)
-        }
-      }
-      float cg[8], cgy[8];
-      if (PASS == 1) {
-        load_affine_d(bn.red_g, c * 8, p.inv_n, cg);
-        load_affine_d(bn.red_gy, c * 8, p.inv_n, cgy);
-      }
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        if (!inb[k]) continue;
-        float dyv[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float v = fmaf(yv[k][j], sc[j], shf[j]);
-          const float g = (arg[j] == k && v > 0.f) ? dzv[j] : 0.f;
-          const float yh = (yv[k][j] - mu[j]) * is[j];
-          if (PASS == 0) {
-            rg[j] += g, rgy[j] = fmaf(g, yh, rgy[j]);
-          } else {
-            dyv[j] = sc[j] * (g - cg[j] - yh * cgy[j]);
-          }
-        }
-        if (PASS == 1) {
-          const int h = 2 * o.h + (k >> 1), w = 2 * o.w + (k & 1);
-          store8<T>(view_addr<T>(p.dy, c, o.n * p.Pimg + h * p.Wp + w, o.n, h, w), dyv);
-        }
-      }
-    }
-    if (PASS == 1 && f == 0) write_bn_grads(p, bn, c);
-    if (PASS == 0) {
-      block_reduce8_atomic(rg, bn.red_g + c * 8, sh);
-      block_reduce8_atomic(rgy, bn.red_gy + c * 8, sh);
-    } else if (f < 16) {
-      // the tensor-core weight gradient reduces 16 positions per MMA: keep [body, round_up(body,16)) zero
-      const long long full = (p.body / p.Pimgo) * p.Pimg;
-      if (full + f < (full + 15) / 16 * 16) {
-        float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        store8<T>(p.dy.base + ((long long)c * p.dy.plane + p.dy.g_lo + full + f) * G, z);
-      }
-    }
-    return;
-  }
-
-  // non-pool modes: thread = chunk c x kEwPpt positions (f, f+256, ...) of a 1024-position block
-  float dacc[kEwPpt][8];
-#pragma unroll
-  for (int i = 0; i < kEwPpt; ++i)
-#pragma unroll
-    for (int j = 0; j < 8; ++j) dacc[i][j] = 0.f;
-  const int body16 = (int)((p.body + 15) / 16 * 16);
-  for (int t = 0; t < p.ntasks; ++t) {
-    const int ch = t * p.nchunks + c;
-    float sc[8], shf[8], mu[8], is[8], s2[8], h2[8], cg[8], cgy[8], rg[8], rgy[8];
-    load_affine(bn.scale, ch * 8, sc);
-    load_affine(bn.shift, ch * 8, shf);
-    load_affine(bn.mean, ch * 8, mu);
-    load_affine(bn.invstd, ch * 8, is);
-    if (p.mode == EW_ADD_RELU_SC) {
-      const BnArrays& bo = p.second ? p.bn : p.bn2;
-      load_affine(bo.scale, ch * 8, s2);
-      load_affine(bo.shift, ch * 8, h2);
-    }
-    if (PASS == 1) {
-      load_affine_d(bn.red_g, ch * 8, p.inv_n, cg);
-      load_affine_d(bn.red_gy, ch * 8, p.inv_n, cgy);
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) rg[j] = rgy[j] = 0.f;
-#pragma unroll
-    for (int i = 0; i < kEwPpt; ++i) {
-      const int fi = f + i * 256;
-      const bool in_r = fi < p.body;
-      const Pos q = decode(in_r ? fi : 0, p.Pimg, p.Wp, p.H, p.W);
-      const bool valid = in_r && q.valid;
-      float dyv[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) dyv[j] = 0.f;
-      if (valid) {
-        float y[8], dzv[8], g[8];
-        load8<T>(ym.base + ((long long)ch * ym.plane + ym.g_lo + fi) * G, y);
-        load8<T>(view_addr<T>(p.dz, ch, fi, q.n, q.h, q.w), dzv);
-        if (p.mode == EW_RELU) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) g[j] = fmaf(y[j], sc[j], shf[j]) > 0.f ? dzv[j] : 0.f;
-        } else if (p.mode == EW_ADD_RELU_SC) {
-          const ActView& yo = p.second ? p.y : p.y2;
-          float y2[8];
-          load8<T>(yo.base + ((long long)ch * yo.plane + yo.g_lo + fi) * G, y2);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) g[j] = (fmaf(y[j], sc[j], shf[j]) + fmaf(y2[j], s2[j], h2[j])) > 0.f ? dzv[j] : 0.f;
-        } else {
-          float aux[8];
-          load8<T>(view_addr<T>(p.aux, c, fi, q.n, q.h, q.w), aux);
-          if (p.mode == EW_ADD_RELU_ID) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              g[j] = (fmaf(y[j], sc[j], shf[j]) + aux[j]) > 0.f ? dzv[j] : 0.f;
-              dacc[i][j] = g[j];
-            }
-          } else {  // EW_SIGMOID_MUL
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float sg = 1.f / (1.f + expf(-fmaf(y[j], sc[j], shf[j])));
-              g[j] = dzv[j] * aux[j] * sg * (1.f - sg);
-              dacc[i][j] = fmaf(dzv[j], sg, dacc[i][j]);
-            }
-          }
-        }
-        if (PASS == 0) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) rg[j] += g[j], rgy[j] = fmaf(g[j], (y[j] - mu[j]) * is[j], rgy[j]);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) dyv[j] = sc[j] * (g[j] - cg[j] - (y[j] - mu[j]) * is[j] * cgy[j]);
-        }
-      }
-      // zero at pads, and zero up to the next multiple of 16 positions (tensor-core wgrad granularity)
-      if (PASS == 1 && fi < body16) store8<T>(p.dy.base + ((long long)ch * p.dy.plane + p.dy.g_lo + fi) * G, dyv);
-    }
-    if (PASS == 0) {
-      block_reduce8_atomic(rg, bn.red_g + ch * 8, sh);
-      block_reduce8_atomic(rgy, bn.red_gy + ch * 8, sh);
-    }
-  }
-  if (PASS == 1 && f == 0) write_bn_grads(p, bn, c);
-  if (PASS == 1 && p.want_daux && !p.second) {
-#pragma unroll
-    for (int i = 0; i < kEwPpt; ++i) {
-      const int fi = f + i * 256;
-      if (fi >= p.body) continue;
-      const Pos q = decode(fi, p.Pimg, p.Wp, p.H, p.W);
-      if (!(q.valid || p.daux.layout == LAY_P8)) continue;
-      char* a = view_addr<T>(p.daux, c, fi, q.n, q.h, q.w);
-      if (p.daux_accum) {
-        if (!q.valid) continue;
-        float old[8];
-        load8<T>(a, old);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) dacc[i][j] += old[j];
-      }
-      store8<T>(a, dacc[i]);
-    }
-  }
-}
-
-cudaError_t launch_ew_bwd(const EwParams& p, int pass, int precision, cudaStream_t st) {
-  const int span = p.mode == EW_RELU_POOL ? 256 : 256 * kEwPpt;
-  const long long per_chunk = (p.body + span - 1) / span * span;
-  const unsigned grid = (unsigned)(per_chunk * p.nchunks / span);
-  if (precision == 0) {
-    if (pass == 0)
-      ew_bwd_kernel<__nv_bfloat16, 0><<<grid, 256, 0, st>>>(p);
-    else
-      ew_bwd_kernel<__nv_bfloat16, 1><<<grid, 256, 0, st>>>(p);
-  } else {
-    if (pass == 0)
-      ew_bwd_kernel<float, 0><<<grid, 256, 0, st>>>(p);
-    else
-      ew_bwd_kernel<float, 1><<<grid, 256, 0, st>>>(p);
-  }
   return cudaGetLastError();
 }
 
@@ -716,12 +301,17 @@ static cudaError_t launch_wgrad_umma(WgradParams p, cudaStream_t st) {
   for (int t = 0; t < p.ntaps; ++t) lo = std::max(lo, -p.tap[t].off), hi = std::max(hi, p.tap[t].off);
   p.halo_lo = lo, p.halo_hi = hi;
   const long long body16 = (p.body + 15) / 16 * 16;
-  long long want = std::max<long long>(1, 444 / ngroups);              // about three CTAs per SM
-  long long slice = std::max<long long>(1024, (body16 + want - 1) / want);
-  p.slice = (int)((slice + kWgStage - 1) / kWgStage * kWgStage);
   const int SPb = kWgStage + lo + hi;
   const size_t b_stage = ((size_t)(p.nsrc * p.nchunks) * SPb * 16 + 127) & ~(size_t)127;
   const size_t smem = kWgHeader + 2 * (size_t)16 * kWgStage * 16 + 2 * b_stage;
+  // one wave: CTAs resident per SM are bounded by the TMEM columns (ntaps*Cin rounded to a power of two) and by
+  // shared memory; the position slices are sized so that the whole grid is resident at once
+  int cols = 32;
+  while (cols < p.taps_per_cta * Cin) cols <<= 1;
+  const int resident = std::max(1, std::min({3, 512 / cols, (int)((size_t)227 * 1024 / (smem + 1024))}));
+  long long want = std::max<long long>(1, (long long)148 * resident / ngroups);
+  long long slice = std::max<long long>(512, (body16 + want - 1) / want);
+  p.slice = (int)((slice + kWgStage - 1) / kWgStage * kWgStage);
   static size_t configured = 0;
   if (smem > configured) {
     cudaError_t e = cudaFuncSetAttribute(wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -740,66 +330,6 @@ cudaError_t launch_wgrad(const WgradParams& p, int precision, cudaStream_t st) {
     return launch_wgrad_t<__nv_bfloat16>(p, st);
   }
   return launch_wgrad_t<float>(p, st);
-}
-
-// ---------------------------------------------------------------------------------------------
-// stem weight gradient: dW[tap][co] += sum_pos x[n, 3h-2+r, 3w-2+s] * dy[pos][co]
-// block 256 handles `slice` positions, 64 at a time staged in shared memory; 784 outputs over 256 threads.
-// ---------------------------------------------------------------------------------------------
-template <typename T>
-__global__ void __launch_bounds__(256) stem_wgrad_kernel(const __grid_constant__ StemWgradParams p, int slice) {
-  __shared__ float xw[64][49];
-  __shared__ float dys[64][16];
-  const long long f0 = (long long)blockIdx.x * slice, f1 = min(f0 + (long long)slice, p.body);
-  float acc[4] = {0.f, 0.f, 0.f, 0.f};
-  for (long long fb = f0; fb < f1; fb += 64) {
-    __syncthreads();
-    for (int i = threadIdx.x; i < 64 * 49; i += 256) {
-      const int pp = i / 49, t = i - pp * 49;
-      float v = 0.f;
-      if (fb + pp < f1) {
-        const Pos q = decode((int)(fb + pp), p.Pimg, p.Wp, p.H, p.W);
-        const int iy = 3 * q.h - 2 + t / 7, ix = 3 * q.w - 2 + t % 7;
-        if (q.valid && iy >= 0 && iy < p.Hin && ix >= 0 && ix < p.Win) v = p.x[((size_t)q.n * p.Hin + iy) * p.Win + ix];
-      }
-      xw[pp][t] = v;
-    }
-    for (int i = threadIdx.x; i < 64 * 2; i += 256) {
-      const int pp = i >> 1, c = i & 1;
-      float v[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = 0.f;
-      if (fb + pp < f1) load8<T>(p.dy.base + ((long long)c * p.dy.plane + p.dy.g_lo + fb + pp) * Gran<T>::bytes, v);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) dys[pp][c * 8 + j] = v[j];
-    }
-    __syncthreads();
-#pragma unroll
-    for (int r = 0; r < 4; ++r) {
-      const int o = threadIdx.x + 256 * r;
-      if (o < 784) {
-        const int t = o >> 4, co = o & 15;
-        float a = acc[r];
-        for (int pp = 0; pp < 64; ++pp) a = fmaf(xw[pp][t], dys[pp][co], a);
-        acc[r] = a;
-      }
-    }
-  }
-#pragma unroll
-  for (int r = 0; r < 4; ++r) {
-    const int o = threadIdx.x + 256 * r;
-    if (o < 784) atomicAdd(p.dw + o, acc[r]);
-  }
-}
-
-cudaError_t launch_stem_wgrad(const StemWgradParams& p, int precision, cudaStream_t st) {
-  const int slice = 2048;
-  const unsigned grid = (unsigned)((p.body + slice - 1) / slice);
-  if (precision == 0)
-    stem_wgrad_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(p, slice);
-  else
-    stem_wgrad_kernel<float><<<grid, 256, 0, st>>>(p, slice);
-  return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -56,6 +56,7 @@ struct EwParams {
   int ngseg;             // backward pass 1 also writes d gamma / d beta of the BatchNorm it differentiates
   BnGradSeg gseg[2];
   int second;            // EW_ADD_RELU_SC backward: 1 = this launch handles the shortcut branch (y2/bn2 are "main")
+  unsigned long long magic_pimg, magic_wp, magic_pimgo, magic_wpo;  // floor(2^40/d)+1 (exact f/d by multiply-shift)
 };
 
 
