@@ -138,10 +138,13 @@ int persist_stages_for(const ConvOpHost& op, size_t extra) {
   return 0;
 }
 
-void choose_tiling(ConvOpHost& op) {
+void choose_tiling(ConvOpHost& op, long long positions) {
   op.tap_bytes = op.nchunks * 8 * op.Cout * 2;
   const int total_w = op.ntaps * op.tap_bytes;
   int MT = 4;
+  // small batches: prefer more, smaller CTAs over multi-tile CTAs until every SM has about two
+  if (positions > 0)
+    while (MT > 1 && (positions + kTileM - 1) / kTileM / MT < 296) MT >>= 1;
   size_t slab = 0;
   for (;; MT >>= 1) {
     int SP = MT * kTileM + op.halo_lo + op.halo_hi;
@@ -214,7 +217,7 @@ struct Builder {
     op.halo_lo = op.halo_hi = 0;
   }
   void finish(ConvOpHost& op) {
-    choose_tiling(op);
+    choose_tiling(op, (long long)p.mb * (op.H + 1) * (op.W + 1));
     p.convs.push_back(op);
     p.program.push_back(Op{1, (int)p.convs.size() - 1});
   }

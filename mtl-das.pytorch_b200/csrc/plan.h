@@ -117,7 +117,7 @@ struct Plan {
 Plan* build_plan(int kind, int mb, int precision);
 int add_tensor(Plan& p, const std::string& name, int C, int H, int W, int layout);
 PackSeg make_seg(const Plan& p, const PackSegHost& h, const void* const* state);
-void choose_tiling(ConvOpHost& op);
+void choose_tiling(ConvOpHost& op, long long positions = 0);  // positions > 0: batch-aware tile count
 int persist_stages_for(const ConvOpHost& op, size_t extra);
 int plan_pack_eval(Plan& p, const void* const* state, cudaStream_t stream);
 int plan_forward_eval(Plan& p, const float* x, int n, float* out0, float* out1, cudaStream_t stream);

@@ -263,7 +263,7 @@ TrainPlan* build_train_plan(int kind, int batch, int precision) {
       }
       const int phase_key = d.g[0].out_phase;
       d.epi = claim(tp, dsrc, sr.chunk0, d.Cout / 8, phase_key) ? EPI_ACCUM : EPI_NONE;
-      choose_tiling(d);
+      choose_tiling(d, (long long)p.mb * (d.H + 1) * (d.W + 1));
       p.convs.push_back(d);
       dp.conv = (int)p.convs.size() - 1;
       // transposed weight placement
@@ -339,10 +339,11 @@ TrainPlan* build_train_plan(int kind, int batch, int precision) {
   };
   for (auto& t : p.tensors) t.offset = take(t.bytes);
   tp.zero_fwd_off = o;  // [zero_fwd_off, zero_fwd_end): BN sums, cleared at every forward
-  for (auto& b : tp.bns) b.sum_off = take((size_t)b.C * 2 * sizeof(double) + 16);  // + completion counter
+  // per BatchNorm: sums [2C] double + one arrival counter per chunk (the fused kernels' barrier)
+  for (auto& b : tp.bns) b.sum_off = take((size_t)b.C * 2 * sizeof(double) + round_up_sz((size_t)b.C / 8 * 4, 16));
   tp.zero_fwd_end = o;
   tp.zero_bwd_off = o;  // cleared at every backward: BN reductions and packed weight-gradient buffers
-  for (auto& b : tp.bns) b.red_off = take((size_t)b.C * 2 * sizeof(double));
+  for (auto& b : tp.bns) b.red_off = take((size_t)b.C * 2 * sizeof(double) + round_up_sz((size_t)b.C / 8 * 4, 16));
   for (auto& w : tp.wgs) {
     const ConvOpHost& f = p.convs[w.conv];
     w.dw_off = take((size_t)f.ntaps * f.nchunks * 8 * f.Cout * sizeof(float));
@@ -385,13 +386,31 @@ static BnArrays bn_arrays(const TrainPlan& tp, int bi) {
   return a;
 }
 
+static FinalizeParams finalize_params(const TrainPlan& tp, int bi, const void* const* state, int nb) {
+  const Plan& p = *tp.p;
+  const TrainPlan::BnHost& b = tp.bns[bi];
+  FinalizeParams fq{};
+  fq.bn = bn_arrays(tp, bi), fq.C = b.C, fq.n = (double)nb * b.H * b.W, fq.eps = 1e-5f, fq.momentum = 0.1f;
+  fq.nseg = (int)b.segs.size();
+  for (int s = 0; s < fq.nseg; ++s) {
+    const LayerSpec& L = p.layers[b.segs[s].layer];
+    FinalizeSeg& fs = fq.seg[s];
+    fs.gamma = (const float*)state[L.i_gamma], fs.beta = (const float*)state[L.i_beta];
+    fs.running_mean = (float*)state[L.i_rm], fs.running_var = (float*)state[L.i_rv];
+    fs.num_batches_tracked = (long long*)state[L.i_nbt];
+    fs.conv_bias = L.i_b >= 0 ? (const float*)state[L.i_b] : nullptr;
+    fs.ch_off = b.segs[s].ch_off, fs.count = b.segs[s].count;
+  }
+  return fq;
+}
+
 static EwParams ew_params(const TrainPlan& tp, const TrainPlan::EwHost& e, int nb) {
   const Plan& p = *tp.p;
   EwParams q{};
   const TensorInfo& ty = p.tensors[e.y];
   q.mode = e.mode, q.ntasks = e.ntasks, q.nchunks = e.nchunks;
   q.H = ty.H, q.W = ty.W, q.Wp = ty.Wp, q.Pimg = ty.Pimg;
-  q.body = (long long)nb * ty.Pimg;
+  q.body = (long long)nb * ty.Pimg, q.body_full = q.body;
   q.inv_n = 1.f / (float)((double)nb * ty.H * ty.W);
   q.y = p.view(e.y, 0), q.bn = bn_arrays(tp, e.bn);
   if (e.y2 >= 0) q.y2 = p.view(e.y2, 0), q.bn2 = bn_arrays(tp, e.bn2);
@@ -465,7 +484,7 @@ static int train_forward_eager(TrainPlan& tp, const void* const* state, const fl
   float* logp1 = logp0 + (size_t)p.mb * 16;
   OpTimer timer(st);
   for (auto& op : tp.fwd) {
-    if (op.kind == TOP_FINAL) continue;  // folded into the statistics kernel
+    if (op.kind == TOP_FINAL || op.kind == TOP_STATS) continue;  // inside the fused BatchNorm + activation kernel
     timer.begin(op.kind);
     if (op.kind == TOP_STEM) {
       const TensorInfo& t = p.tensors[tp.y_stem];
@@ -479,30 +498,14 @@ static int train_forward_eager(TrainPlan& tp, const void* const* state, const fl
     } else if (op.kind == TOP_CONV) {
       ConvParams q = p.conv_params(p.convs[op.a], nb);
       CK(launch_conv(q, p.precision, st));
-    } else if (op.kind == TOP_STATS) {
-      const TrainPlan::BnHost& b = tp.bns[op.a];
-      StatsParams q{};
-      q.y = p.view(b.tensor, 0), q.nchunks = b.C / 8, q.body = (long long)nb * p.tensors[b.tensor].Pimg;
-      BnArrays a = bn_arrays(tp, op.a);
-      q.sum = a.sum, q.sumsq = a.sumsq;
-      q.done = reinterpret_cast<unsigned int*>(p.ws + b.sum_off + (size_t)b.C * 2 * sizeof(double));
-      FinalizeParams& fq = q.fin;  // performed by the last stats block
-      fq.bn = a, fq.C = b.C, fq.n = (double)nb * b.H * b.W, fq.eps = 1e-5f, fq.momentum = 0.1f;
-      fq.nseg = (int)b.segs.size();
-      for (int s = 0; s < fq.nseg; ++s) {
-        const LayerSpec& L = p.layers[b.segs[s].layer];
-        FinalizeSeg& fs = fq.seg[s];
-        fs.gamma = (const float*)state[L.i_gamma], fs.beta = (const float*)state[L.i_beta];
-        fs.running_mean = (float*)state[L.i_rm], fs.running_var = (float*)state[L.i_rv];
-        fs.num_batches_tracked = (long long*)state[L.i_nbt];
-        fs.conv_bias = L.i_b >= 0 ? (const float*)state[L.i_b] : nullptr;
-        fs.ch_off = b.segs[s].ch_off, fs.count = b.segs[s].count;
-      }
-      CK(launch_stats(q, p.precision, st));
     } else if (op.kind == TOP_FINAL) {
       continue;  // folded into the statistics kernel
     } else if (op.kind == TOP_EW) {
-      EwParams q = ew_params(tp, tp.ews[op.a], nb);
+      const TrainPlan::EwHost& e = tp.ews[op.a];
+      EwParams q = ew_params(tp, e, nb);
+      q.fin = finalize_params(tp, e.bn, state, nb);
+      if (e.y2 >= 0) q.fin2 = finalize_params(tp, e.bn2, state, nb);
+      q.sync = reinterpret_cast<unsigned int*>(p.ws + tp.bns[e.bn].sum_off + (size_t)tp.bns[e.bn].C * 2 * sizeof(double));
       CK(launch_ew_fwd(q, p.precision, st));
     } else if (op.kind == TOP_HEAD) {
       const HeadOpHost& h = p.heads[op.a];
@@ -542,6 +545,31 @@ static int train_backward_eager(TrainPlan& tp, const void* const* state, const f
   float* logp1 = logp0 + (size_t)p.mb * 16;
   OpTimer timer(st);
   std::vector<UnpackParams> unpacks;  // packed weight gradients -> parameter layout, one batched launch at the end
+  static int side_env = -1;
+  if (side_env < 0) {
+    const char* e = getenv("MTLDAS_WGRAD_SIDE");
+    side_env = (e && e[0] == '0') ? 0 : 1;
+  }
+  const bool use_side = side_env && !timer.on;
+  size_t n_fork = 0;
+  if (use_side && !tp.side_stream) {
+    CK(cudaStreamCreateWithFlags(&tp.side_stream, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&tp.join_event, cudaEventDisableTiming));
+  }
+  // the side stream picks up after everything enqueued on `st` so far (the layer's dy, the zeroed dW buffers)
+  auto fork = [&](cudaStream_t& out) -> bool {
+    out = st;
+    if (!use_side) return true;
+    if (n_fork == tp.fork_events.size()) {
+      cudaEvent_t e = nullptr;
+      if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return false;
+      tp.fork_events.push_back(e);
+    }
+    cudaEvent_t e = tp.fork_events[n_fork++];
+    if (cudaEventRecord(e, st) != cudaSuccess || cudaStreamWaitEvent(tp.side_stream, e, 0) != cudaSuccess) return false;
+    out = tp.side_stream;
+    return true;
+  };
   for (auto& op : tp.bwd) {
     if (op.kind == TOP_BNGRAD) continue;  // written by the elementwise backward's second pass
     timer.begin(op.kind);
@@ -564,23 +592,21 @@ static int train_backward_eager(TrainPlan& tp, const void* const* state, const f
       q.dz = p.view(e.dz, 0), q.dy = p.view(e.dy, 0);
       q.want_daux = e.daux >= 0, q.daux_accum = e.daux_accum;
       if (e.daux >= 0) q.daux = p.view(e.daux, 0);
-      auto set_gsegs = [&](int bi) {
+      auto set_gsegs = [&](int bi, int& n, BnGradSeg* out) {
         const TrainPlan::BnHost& b = tp.bns[bi];
-        q.ngseg = (int)b.segs.size();
-        for (int s = 0; s < q.ngseg; ++s) {
+        n = (int)b.segs.size();
+        for (int s = 0; s < n; ++s) {
           const TrainPlan::ParamOff& po = tp.param_off[b.segs[s].layer];
-          q.gseg[s] = BnGradSeg{grads + po.gamma, grads + po.beta, b.segs[s].ch_off, b.segs[s].count};
+          out[s] = BnGradSeg{grads + po.gamma, grads + po.beta, b.segs[s].ch_off, b.segs[s].count};
         }
       };
-      set_gsegs(e.bn);
-      CK(launch_ew_bwd(q, 0, p.precision, st));
-      CK(launch_ew_bwd(q, 1, p.precision, st));
+      set_gsegs(e.bn, q.ngseg, q.gseg);
       if (e.mode == EW_ADD_RELU_SC) {  // the shortcut branch shares g; its own BatchNorm gives its own dy
-        q.second = 1, q.dy = p.view(e.dy2, 0), q.want_daux = 0;
-        set_gsegs(e.bn2);
-        CK(launch_ew_bwd(q, 0, p.precision, st));
-        CK(launch_ew_bwd(q, 1, p.precision, st));
+        q.dy2 = p.view(e.dy2, 0);
+        set_gsegs(e.bn2, q.ngseg2, q.gseg2);
       }
+      q.sync = reinterpret_cast<unsigned int*>(p.ws + tp.bns[e.bn].red_off + (size_t)tp.bns[e.bn].C * 2 * sizeof(double));
+      CK(launch_ew_bwd(q, p.precision, st));
     } else if (op.kind == TOP_BNGRAD) {
       continue;  // written by the elementwise backward's second pass
       const TrainPlan::BnHost& b = tp.bns[op.a];
@@ -606,7 +632,12 @@ static int train_backward_eager(TrainPlan& tp, const void* const* state, const f
       long long want = std::max<long long>(1, 592 / f.ntaps);
       q.slice = (int)std::max<long long>(256, (cp.body + want - 1) / want);
       q.slice = (q.slice + 31) / 32 * 32;
-      CK(launch_wgrad(q, p.precision, st));
+      cudaStream_t ws = st;
+      if (!fork(ws)) {
+        set_error("train_backward: side-stream fork failed: %s", cudaGetErrorString(cudaGetLastError()));
+        return -4;
+      }
+      CK(launch_wgrad(q, p.precision, ws));
       for (auto& sh : f.g[w.group].segs) {
         const LayerSpec& L = p.layers[sh.layer];
         UnpackParams u{};
@@ -624,7 +655,12 @@ static int train_backward_eager(TrainPlan& tp, const void* const* state, const f
       q.x = tp.x, q.dy = p.view(tp.dy_stem, 0), q.dw = reinterpret_cast<float*>(p.ws + tp.stem_dw_off);
       q.Hin = kPatchH, q.Win = kPatchW, q.H = t.H, q.W = t.W, q.Wp = t.Wp, q.Pimg = t.Pimg;
       q.body = (long long)nb * t.Pimg;
-      CK(launch_stem_wgrad(q, p.precision, st));
+      cudaStream_t ws = st;
+      if (!fork(ws)) {
+        set_error("train_backward: side-stream fork failed: %s", cudaGetErrorString(cudaGetLastError()));
+        return -4;
+      }
+      CK(launch_stem_wgrad(q, p.precision, ws));
       UnpackParams u{};
       u.src = q.dw, u.dst = grads + tp.param_off[p.stem_layer].w;
       u.cout = 16, u.cin = 1, u.ksize = 7, u.split = INT_MAX, u.k_off = 0, u.cout_off = 0, u.Cout_p = 16, u.K_tap = 1;
@@ -632,6 +668,10 @@ static int train_backward_eager(TrainPlan& tp, const void* const* state, const f
     }
     timer.end();
     ++tp.launches;
+  }
+  if (use_side && n_fork) {  // join: the unpack reads every dW buffer
+    CK(cudaEventRecord(tp.join_event, tp.side_stream));
+    CK(cudaStreamWaitEvent(st, tp.join_event, 0));
   }
   CK(launch_unpack_batch(unpacks.data(), (int)unpacks.size(), st));
   ++tp.launches;
@@ -729,6 +769,9 @@ TrainPlan::~TrainPlan() {
     for (auto& g : *c)
       if (g.exec) cudaGraphExecDestroy(g.exec);
   if (cap_stream) cudaStreamDestroy(cap_stream);
+  if (side_stream) cudaStreamDestroy(side_stream);
+  for (auto e : fork_events) cudaEventDestroy(e);
+  if (join_event) cudaEventDestroy(join_event);
   delete p;
 }
 

@@ -71,6 +71,11 @@ struct TrainPlan {
   };
   std::vector<GraphEntry> fwd_graphs, bwd_graphs;
   cudaStream_t cap_stream = nullptr;
+  // weight gradients run on a side stream (forked after the layer's dy is complete, joined before the unpack):
+  // they are off the dgrad -> elementwise chain, so the small latency-bound launches overlap
+  cudaStream_t side_stream = nullptr;
+  std::vector<cudaEvent_t> fork_events;
+  cudaEvent_t join_event = nullptr;
   // state of the last forward
   int nb = 0, launches = 0;
   const float* x = nullptr;

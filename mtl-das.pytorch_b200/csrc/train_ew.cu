@@ -106,6 +106,77 @@ inline unsigned blocks_per_chunk(long long positions, int chunks) {
   return (unsigned)std::max<long long>(1, std::min(need, want));
 }
 
+
+// Barrier among the gridDim.x blocks that own one chunk (arrival counter zeroed by the host-side memset of the
+// sums).  Every block of the grid is resident (the launchers size the grid from the occupancy query), so the
+// spin cannot starve a block that has not started; the clock bound turns a broken invariant into a trap, not a hang.
+__device__ __forceinline__ void chunk_barrier(unsigned int* ctr, unsigned int nblocks) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(ctr, 1u);
+    const long long t0 = clock64();
+    while (*reinterpret_cast<volatile unsigned int*>(ctr) < nblocks) {
+      __nanosleep(40);
+      if (clock64() - t0 > 8000000000ll) __trap();
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+// per-thread partial sum / sum of squares of one chunk plane (pads and guards are zero: no position decoding)
+template <typename T>
+__device__ __forceinline__ void plane_sums(const char* base, long long body, long long first, long long stride,
+                                           float* s, float* q) {
+  constexpr int G = Gran<T>::bytes;
+  long long f = first;
+  for (; f + 3 * stride < body; f += 4 * stride) {  // four independent loads in flight
+    float v[4][8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) load8<T>(base + (f + i * stride) * G, v[i]);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s[j] += v[i][j], q[j] = fmaf(v[i][j], v[i][j], q[j]);
+  }
+  for (; f < body; f += stride) {
+    float v[8];
+    load8<T>(base + f * G, v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] += v[j], q[j] = fmaf(v[j], v[j], q[j]);
+  }
+}
+
+// scale / shift of channel c from the completed sums (every block of the chunk computes its own copy)
+__device__ __forceinline__ void affine_of(const FinalizeParams& p, int c, float& scale, float& shift) {
+  const double mean = __ldcg(p.bn.sum + c) / p.n;
+  double var = __ldcg(p.bn.sumsq + c) / p.n - mean * mean;
+  if (var < 0.0) var = 0.0;
+  const double invstd = rsqrt(var + (double)p.eps);
+  scale = 0.f, shift = 0.f;
+  for (int s = 0; s < p.nseg; ++s) {
+    const FinalizeSeg& g = p.seg[s];
+    if (c >= g.ch_off && c < g.ch_off + g.count) {
+      const int i = c - g.ch_off;
+      scale = (float)((double)g.gamma[i] * invstd);
+      shift = (float)((double)g.beta[i] - mean * (double)g.gamma[i] * invstd);
+    }
+  }
+}
+
+// grid.x of a fused (barrier) kernel: all blocks resident at once
+template <typename K>
+inline unsigned resident_blocks_per_chunk(K kernel, long long positions, int chunks) {
+  int sms = 148, dev = 0, occ = 1;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kEwThreads, 0) != cudaSuccess || occ < 1) occ = 1;
+  const long long need = (positions + kEwThreads - 1) / kEwThreads;
+  const long long cap = std::max<long long>(1, (long long)sms * std::min(occ, 4) / chunks);
+  return (unsigned)std::max<long long>(1, std::min(need, cap));
+}
+
 }  // namespace
 
 __global__ void finalize_kernel(const __grid_constant__ FinalizeParams p) { finalize_channel(p, threadIdx.x); }
@@ -116,73 +187,62 @@ cudaError_t launch_finalize(const FinalizeParams& p, cudaStream_t st) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// batch statistics (pads and guards are zero -> planes are summed whole, no position decoding)
+// fused forward of one BatchNorm + activation: batch statistics -> per-chunk barrier -> finalize -> apply.
+// The raw tensor is read twice (the second time out of L2); scale / shift never leave the SM between the phases.
+// EW_SIGMOID_MUL loops over the tasks that share the feature map; EW_ADD_RELU_SC normalises the main and the
+// shortcut branch in one go; EW_RELU_POOL applies over pooled positions (four full-resolution loads per thread).
 // ---------------------------------------------------------------------------------------------
-template <typename T>
-__global__ void __launch_bounds__(kEwThreads) stats_kernel(const __grid_constant__ StatsParams p) {
-  __shared__ float sh[kEwThreads / 32][8];
-  constexpr int G = Gran<T>::bytes;
-  const int c = blockIdx.y;
-  const char* base = p.y.base + ((long long)c * p.y.plane + p.y.g_lo) * G;
-  float s[8], q[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
-  const long long stride = (long long)gridDim.x * kEwThreads;
-  long long f = (long long)blockIdx.x * kEwThreads + threadIdx.x;
-  for (; f + 3 * stride < p.body; f += 4 * stride) {  // four independent loads in flight
-    float v[4][8];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) load8<T>(base + (f + i * stride) * G, v[i]);
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-      for (int j = 0; j < 8; ++j) s[j] += v[i][j], q[j] = fmaf(v[i][j], v[i][j], q[j]);
-  }
-  for (; f < p.body; f += stride) {
-    float v[8];
-    load8<T>(base + f * G, v);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) s[j] += v[j], q[j] = fmaf(v[j], v[j], q[j]);
-  }
-  block_reduce8(s, p.sum + c * 8, sh);
-  block_reduce8(q, p.sumsq + c * 8, sh);
-  // last block to finish turns the sums into scale / shift / running statistics (no separate finalize launch)
-  __shared__ unsigned int last;
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) last = atomicAdd(p.done, 1u) == gridDim.x * gridDim.y - 1 ? 1u : 0u;
-  __syncthreads();
-  if (last) {
-    __threadfence();
-    finalize_channel(p.fin, threadIdx.x);
-  }
-}
+constexpr int kMaxTasks = 2;  // tasks stacked on one feature map (MTL_Net: distance + event)
 
-cudaError_t launch_stats(const StatsParams& p, int precision, cudaStream_t st) {
-  dim3 grid(blocks_per_chunk(p.body, p.nchunks), p.nchunks);
-  if (precision == 0)
-    stats_kernel<__nv_bfloat16><<<grid, kEwThreads, 0, st>>>(p);
-  else
-    stats_kernel<float><<<grid, kEwThreads, 0, st>>>(p);
-  return cudaGetLastError();
-}
-
-// ---------------------------------------------------------------------------------------------
-// fused BatchNorm apply + activation (forward).  EW_SIGMOID_MUL loops over the tasks that share the feature map;
-// EW_RELU_POOL iterates pooled positions (four full-resolution loads per thread and chunk).
-// ---------------------------------------------------------------------------------------------
 template <typename T, int MODE>
 __global__ void __launch_bounds__(kEwThreads) ew_fwd_kernel(const __grid_constant__ EwParams p) {
   constexpr int G = Gran<T>::bytes;
+  __shared__ float sh[kEwThreads / 32][8];
+  __shared__ float aff[kMaxTasks][4][8];  // per task: scale, shift, scale2, shift2 of the chunk's 8 channels
   const int c = blockIdx.y;
   const int stride = gridDim.x * kEwThreads;
+  const int first = blockIdx.x * kEwThreads + threadIdx.x;
   const int body = (int)p.body;
+  const int ntasks = MODE == EW_RELU_POOL ? 1 : p.ntasks;
+
+  // ---- phase 1: statistics of this chunk (all tasks; both branches) ------------------------------
+  for (int t = 0; t < ntasks; ++t) {
+    const int ch = t * p.nchunks + c;
+    float s[8], q[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
+    plane_sums<T>(p.y.base + ((long long)ch * p.y.plane + p.y.g_lo) * G, p.body_full, first, stride, s, q);
+    block_reduce8(s, p.fin.bn.sum + ch * 8, sh);
+    block_reduce8(q, p.fin.bn.sumsq + ch * 8, sh);
+    if (MODE == EW_ADD_RELU_SC) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
+      plane_sums<T>(p.y2.base + ((long long)ch * p.y2.plane + p.y2.g_lo) * G, p.body_full, first, stride, s, q);
+      block_reduce8(s, p.fin2.bn.sum + ch * 8, sh);
+      block_reduce8(q, p.fin2.bn.sumsq + ch * 8, sh);
+    }
+  }
+  chunk_barrier(p.sync + c, gridDim.x);
+
+  // ---- phase 2: finalize (every block for itself; block 0 of the chunk also publishes) -------------
+  if (threadIdx.x < ntasks * 8) {
+    const int t = threadIdx.x >> 3, j = threadIdx.x & 7, chn = (t * p.nchunks + c) * 8 + j;
+    affine_of(p.fin, chn, aff[t][0][j], aff[t][1][j]);
+    if (MODE == EW_ADD_RELU_SC) affine_of(p.fin2, chn, aff[t][2][j], aff[t][3][j]);
+    if (blockIdx.x == 0) {
+      finalize_channel(p.fin, chn);
+      if (MODE == EW_ADD_RELU_SC) finalize_channel(p.fin2, chn);
+    }
+  }
+  __syncthreads();
+
+  // ---- phase 3: apply ------------------------------------------------------------------------------
   if (MODE == EW_RELU_POOL) {
-    float sc[8], sh[8];
-    ld_affine(p.bn.scale, c * 8, sc);
-    ld_affine(p.bn.shift, c * 8, sh);
+    float sc[8], shf[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sc[j] = aff[0][0][j], shf[j] = aff[0][1][j];
     const char* ybase = p.y.base + ((long long)c * p.y.plane + p.y.g_lo) * G;
-    for (int f = blockIdx.x * kEwThreads + threadIdx.x; f < body; f += stride) {
+    for (int f = first; f < body; f += stride) {
       const Pos3 o = decode3(f, p.Pimgo, p.Wpo, p.magic_pimgo, p.magic_wpo);
       float m[8];
 #pragma unroll
@@ -198,77 +258,89 @@ __global__ void __launch_bounds__(kEwThreads) ew_fwd_kernel(const __grid_constan
         if (hb && wb) load8<T>(a + (long long)(p.Wp + 1) * G, v[3]);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {  // relu folded into the max with 0
-          m[j] = fmaxf(m[j], fmaf(v[0][j], sc[j], sh[j]));
-          if (wb) m[j] = fmaxf(m[j], fmaf(v[1][j], sc[j], sh[j]));
-          if (hb) m[j] = fmaxf(m[j], fmaf(v[2][j], sc[j], sh[j]));
-          if (hb && wb) m[j] = fmaxf(m[j], fmaf(v[3][j], sc[j], sh[j]));
+          m[j] = fmaxf(m[j], fmaf(v[0][j], sc[j], shf[j]));
+          if (wb) m[j] = fmaxf(m[j], fmaf(v[1][j], sc[j], shf[j]));
+          if (hb) m[j] = fmaxf(m[j], fmaf(v[2][j], sc[j], shf[j]));
+          if (hb && wb) m[j] = fmaxf(m[j], fmaf(v[3][j], sc[j], shf[j]));
         }
       }
       store8<T>(view_addr<T>(p.out, c, f, o.n, o.h, o.w), m);
     }
     return;
   }
-  for (int t = 0; t < p.ntasks; ++t) {
+  for (int t = 0; t < ntasks; ++t) {
     const int ch = t * p.nchunks + c;
-    float sc[8], sh[8], s2[8], h2[8];
-    ld_affine(p.bn.scale, ch * 8, sc);
-    ld_affine(p.bn.shift, ch * 8, sh);
-    if (MODE == EW_ADD_RELU_SC) {
-      ld_affine(p.bn2.scale, ch * 8, s2);
-      ld_affine(p.bn2.shift, ch * 8, h2);
+    float sc[8], shf[8], s2[8], h2[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      sc[j] = aff[t][0][j], shf[j] = aff[t][1][j];
+      if (MODE == EW_ADD_RELU_SC) s2[j] = aff[t][2][j], h2[j] = aff[t][3][j];
     }
     const char* ybase = p.y.base + ((long long)ch * p.y.plane + p.y.g_lo) * G;
     const char* y2base = MODE == EW_ADD_RELU_SC ? p.y2.base + ((long long)ch * p.y2.plane + p.y2.g_lo) * G : nullptr;
-#pragma unroll 2
-    for (int f = blockIdx.x * kEwThreads + threadIdx.x; f < body; f += stride) {
-      const Pos3 q = decode3(f, p.Pimg, p.Wp, p.magic_pimg, p.magic_wp);
-      const bool valid = q.h < p.H && q.w < p.W;
-      if (!valid && p.out.layout != LAY_P8) continue;
-      float z[8];
+    constexpr int U = Batch<T>::n;
+    for (int f0 = first; f0 < body; f0 += U * stride) {
+      Raw<T> ry[U], ro[U];
+      Pos3 q[U];
+      bool valid[U];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) z[j] = 0.f;
-      if (valid) {
-        float v[8];
-        load8<T>(ybase + (long long)f * G, v);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = fmaf(v[j], sc[j], sh[j]);
-        if (MODE == EW_RELU) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) z[j] = fmaxf(v[j], 0.f);
-        } else if (MODE == EW_ADD_RELU_SC) {
-          float v2[8];
-          load8<T>(y2base + (long long)f * G, v2);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) z[j] = fmaxf(v[j] + fmaf(v2[j], s2[j], h2[j]), 0.f);
-        } else {
-          float aux[8];
-          load8<T>(view_addr<T>(p.aux, c, f, q.n, q.h, q.w), aux);
-          if (MODE == EW_ADD_RELU_ID) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) z[j] = fmaxf(v[j] + aux[j], 0.f);
-          } else {  // EW_SIGMOID_MUL
-#pragma unroll
-            for (int j = 0; j < 8; ++j) z[j] = aux[j] / (1.f + expf(-v[j]));
-          }
+      for (int i = 0; i < U; ++i) {  // issue every load of the batch before the first use
+        const int f = f0 + i * stride;
+        q[i] = decode3(f < body ? f : 0, p.Pimg, p.Wp, p.magic_pimg, p.magic_wp);
+        valid[i] = f < body && q[i].h < p.H && q[i].w < p.W;
+        if (valid[i]) {
+          load_raw(ybase + (long long)f * G, ry[i]);
+          if (MODE == EW_ADD_RELU_SC) load_raw(y2base + (long long)f * G, ro[i]);
+          if (MODE == EW_ADD_RELU_ID || MODE == EW_SIGMOID_MUL)
+            load_raw(view_addr<T>(p.aux, c, f, q[i].n, q[i].h, q[i].w), ro[i]);
         }
       }
-      store8<T>(view_addr<T>(p.out, ch, f, q.n, q.h, q.w), z);
+#pragma unroll
+      for (int i = 0; i < U; ++i) {
+        const int f = f0 + i * stride;
+        if (f >= body || (!valid[i] && p.out.layout != LAY_P8)) continue;
+        float z[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) z[j] = 0.f;
+        if (valid[i]) {
+          float v[8], o[8];
+          unpack(ry[i], v);
+          if (MODE != EW_RELU) unpack(ro[i], o);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float bn = fmaf(v[j], sc[j], shf[j]);
+            if (MODE == EW_RELU) z[j] = fmaxf(bn, 0.f);
+            else if (MODE == EW_ADD_RELU_SC) z[j] = fmaxf(bn + fmaf(o[j], s2[j], h2[j]), 0.f);
+            else if (MODE == EW_ADD_RELU_ID) z[j] = fmaxf(bn + o[j], 0.f);
+            else z[j] = o[j] / (1.f + expf(-bn));  // EW_SIGMOID_MUL
+          }
+        }
+        store8<T>(view_addr<T>(p.out, ch, f, q[i].n, q[i].h, q[i].w), z);
+      }
     }
   }
 }
 
+template <typename T, int MODE>
+static cudaError_t launch_ew_fwd_m(const EwParams& p, cudaStream_t st) {
+  static unsigned per_sm_cache = 0;  // occupancy of this instantiation
+  (void)per_sm_cache;
+  dim3 grid(resident_blocks_per_chunk(ew_fwd_kernel<T, MODE>, std::max(p.body, p.body_full), p.nchunks), p.nchunks);
+  ew_fwd_kernel<T, MODE><<<grid, kEwThreads, 0, st>>>(p);
+  return cudaGetLastError();
+}
+
 template <typename T>
 static cudaError_t launch_ew_fwd_t(const EwParams& p, cudaStream_t st) {
-  dim3 grid(blocks_per_chunk(p.body, p.nchunks), p.nchunks);
+  if (p.ntasks > kMaxTasks || !p.sync) return cudaErrorInvalidValue;
   switch (p.mode) {
-    case EW_RELU: ew_fwd_kernel<T, EW_RELU><<<grid, kEwThreads, 0, st>>>(p); break;
-    case EW_ADD_RELU_ID: ew_fwd_kernel<T, EW_ADD_RELU_ID><<<grid, kEwThreads, 0, st>>>(p); break;
-    case EW_ADD_RELU_SC: ew_fwd_kernel<T, EW_ADD_RELU_SC><<<grid, kEwThreads, 0, st>>>(p); break;
-    case EW_SIGMOID_MUL: ew_fwd_kernel<T, EW_SIGMOID_MUL><<<grid, kEwThreads, 0, st>>>(p); break;
-    case EW_RELU_POOL: ew_fwd_kernel<T, EW_RELU_POOL><<<grid, kEwThreads, 0, st>>>(p); break;
+    case EW_RELU: return launch_ew_fwd_m<T, EW_RELU>(p, st);
+    case EW_ADD_RELU_ID: return launch_ew_fwd_m<T, EW_ADD_RELU_ID>(p, st);
+    case EW_ADD_RELU_SC: return launch_ew_fwd_m<T, EW_ADD_RELU_SC>(p, st);
+    case EW_SIGMOID_MUL: return launch_ew_fwd_m<T, EW_SIGMOID_MUL>(p, st);
+    case EW_RELU_POOL: return launch_ew_fwd_m<T, EW_RELU_POOL>(p, st);
     default: return cudaErrorInvalidValue;
   }
-  return cudaGetLastError();
 }
 
 cudaError_t launch_ew_fwd(const EwParams& p, int precision, cudaStream_t st) {
@@ -276,119 +348,148 @@ cudaError_t launch_ew_fwd(const EwParams& p, int precision, cudaStream_t st) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// fused elementwise backward.  PASS 0: reductions sum(g), sum(g*y_hat); PASS 1: dy (and d aux).
-// g = dz * activation'(.) is recomputed in both passes from dz and the saved raw tensors.
-// PASS 1 uses dy = scale*g + A + B*y with A = -scale*(mean(g) - mean(g*y_hat)*mean*invstd) and
-// B = -scale*mean(g*y_hat)*invstd (formed in double per thread, once), i.e. scale*(g - mean(g) - y_hat*mean(g*y_hat)).
+// fused elementwise backward of one BatchNorm + activation:
+//   phase 1  reductions sum(g), sum(g*y_hat)            (g = dz * activation'(.), recomputed from the saved raw tensors)
+//   barrier  among the blocks of the chunk
+//   phase 2  dy = scale*g + A + B*y with A = -scale*(mean(g) - mean(g*y_hat)*mean*invstd), B = -scale*mean(g*y_hat)*invstd
+//            (formed in double, once per thread), i.e. scale*(g - mean(g) - y_hat*mean(g*y_hat)); d aux where the
+//            activation has a second input; d gamma / d beta written by block 0 of the chunk.
+// EW_ADD_RELU_SC differentiates the main and the shortcut BatchNorm together (they share g).
 // ---------------------------------------------------------------------------------------------
 struct BwdConst {
-  float sc[8], shf[8], a[8], b[8];  // PASS 0: a = mean, b = invstd;  PASS 1: a = A, b = B
+  float sc[8], shf[8], a[8], b[8];  // phase 1: a = mean, b = invstd;  phase 2: a = A, b = B
 };
 
-template <int PASS>
-__device__ __forceinline__ void load_bwd_const(const BnArrays& bn, int ch, float inv_n, BwdConst& k) {
+__device__ __forceinline__ void load_fwd_const(const BnArrays& bn, int ch, BwdConst& k) {
   ld_affine(bn.scale, ch * 8, k.sc);
   ld_affine(bn.shift, ch * 8, k.shf);
   ld_affine(bn.mean, ch * 8, k.a);
   ld_affine(bn.invstd, ch * 8, k.b);
-  if (PASS == 1) {
+}
+
+// a = mean, b = invstd  ->  a = A, b = B from the completed reductions (L2 reads: other blocks' atomics)
+__device__ __forceinline__ void to_grad_const(const BnArrays& bn, int ch, float inv_n, BwdConst& k) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const double cg = bn.red_g[ch * 8 + j] * (double)inv_n, cgy = bn.red_gy[ch * 8 + j] * (double)inv_n;
-      const double mu = k.a[j], is = k.b[j], sc = k.sc[j];
-      k.a[j] = (float)(-sc * (cg - cgy * mu * is));
-      k.b[j] = (float)(-sc * cgy * is);
-    }
+  for (int j = 0; j < 8; ++j) {
+    const double cg = __ldcg(bn.red_g + ch * 8 + j) * (double)inv_n, cgy = __ldcg(bn.red_gy + ch * 8 + j) * (double)inv_n;
+    const double mu = k.a[j], is = k.b[j], sc = k.sc[j];
+    k.a[j] = (float)(-sc * (cg - cgy * mu * is));
+    k.b[j] = (float)(-sc * cgy * is);
   }
 }
 
 // d gamma / d beta of chunk c (all tasks) from the completed reductions: written once per chunk
-__device__ __forceinline__ void write_bn_grads(const EwParams& p, const BnArrays& bn, int c, int ntask) {
+__device__ __forceinline__ void write_bn_grads(const BnArrays& bn, const BnGradSeg* gseg, int ngseg, int nchunks, int c,
+                                               int ntask) {
   for (int t = 0; t < ntask; ++t)
     for (int j = 0; j < 8; ++j) {
-      const int ch = (t * p.nchunks + c) * 8 + j;
-      for (int s = 0; s < p.ngseg; ++s) {
-        const BnGradSeg& g = p.gseg[s];
+      const int ch = (t * nchunks + c) * 8 + j;
+      for (int s = 0; s < ngseg; ++s) {
+        const BnGradSeg& g = gseg[s];
         if (ch >= g.ch_off && ch < g.ch_off + g.count) {
-          g.dgamma[ch - g.ch_off] = (float)bn.red_gy[ch];
-          g.dbeta[ch - g.ch_off] = (float)bn.red_g[ch];
+          g.dgamma[ch - g.ch_off] = (float)__ldcg(bn.red_gy + ch);
+          g.dbeta[ch - g.ch_off] = (float)__ldcg(bn.red_g + ch);
         }
       }
     }
 }
 
-template <typename T, int MODE, int PASS>
-__global__ void __launch_bounds__(kEwThreads) ew_bwd_kernel(const __grid_constant__ EwParams p) {
+// g of one position for the non-pool modes (y, dz, and the mode's second input already loaded)
+template <int MODE>
+__device__ __forceinline__ void act_grad(const float* y, const float* dzv, const float* other, const BwdConst& k,
+                                         const float* s2, const float* h2, float* g, float* sgm) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float v = fmaf(y[j], k.sc[j], k.shf[j]);
+    if (MODE == EW_RELU) {
+      g[j] = v > 0.f ? dzv[j] : 0.f;
+    } else if (MODE == EW_ADD_RELU_SC) {
+      g[j] = (v + fmaf(other[j], s2[j], h2[j])) > 0.f ? dzv[j] : 0.f;
+    } else if (MODE == EW_ADD_RELU_ID) {
+      g[j] = (v + other[j]) > 0.f ? dzv[j] : 0.f;
+    } else {  // EW_SIGMOID_MUL
+      const float sg = 1.f / (1.f + expf(-v));
+      g[j] = dzv[j] * other[j] * sg * (1.f - sg);
+      sgm[j] = sg;
+    }
+  }
+}
+
+template <typename T, int MODE>
+__global__ void __launch_bounds__(kEwThreads, 2) ew_bwd_kernel(const __grid_constant__ EwParams p) {
   __shared__ float sh[kEwThreads / 32][8];
   constexpr int G = Gran<T>::bytes;
   const int c = blockIdx.y;
   const int stride = gridDim.x * kEwThreads;
   const int body = (int)p.body;
   const int first = blockIdx.x * kEwThreads + threadIdx.x;
-  const BnArrays& bn = p.second ? p.bn2 : p.bn;     // the BatchNorm whose input gradient this launch produces
-  const ActView& ym = p.second ? p.y2 : p.y;
 
   if (MODE == EW_RELU_POOL) {
     // thread = pooled position; the 2x2 window's four full-resolution positions belong to this thread alone
     BwdConst k;
-    load_bwd_const<PASS>(bn, c, p.inv_n, k);
+    load_fwd_const(p.bn, c, k);
+    const char* ybase = p.y.base + ((long long)c * p.y.plane + p.y.g_lo) * G;
+    char* dybase = p.dy.base + ((long long)c * p.dy.plane + p.dy.g_lo) * G;
     float rg[8], rgy[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) rg[j] = rgy[j] = 0.f;
-    const char* ybase = ym.base + ((long long)c * ym.plane + ym.g_lo) * G;
-    char* dybase = p.dy.base + ((long long)c * p.dy.plane + p.dy.g_lo) * G;
-    for (int f = first; f < body; f += stride) {
-      const Pos3 o = decode3(f, p.Pimgo, p.Wpo, p.magic_pimgo, p.magic_wpo);
-      if (!(o.h < p.Ho && o.w < p.Wo)) continue;
-      float dzv[8];
-      load8<T>(view_addr<T>(p.dz, c, f, o.n, o.h, o.w), dzv);
-      const int h0 = 2 * o.h, w0 = 2 * o.w;
-      const long long pos0 = (long long)o.n * p.Pimg + h0 * p.Wp + w0;
-      bool inb[4];
-      inb[0] = true, inb[1] = w0 + 1 < p.W, inb[2] = h0 + 1 < p.H, inb[3] = inb[1] && inb[2];
-      float yv[4][8];
+#pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+      for (int f = first; f < body; f += stride) {
+        const Pos3 o = decode3(f, p.Pimgo, p.Wpo, p.magic_pimgo, p.magic_wpo);
+        if (!(o.h < p.Ho && o.w < p.Wo)) continue;
+        float dzv[8];
+        load8<T>(view_addr<T>(p.dz, c, f, o.n, o.h, o.w), dzv);
+        const int h0 = 2 * o.h, w0 = 2 * o.w;
+        const long long pos0 = (long long)o.n * p.Pimg + h0 * p.Wp + w0;
+        bool inb[4];
+        inb[0] = true, inb[1] = w0 + 1 < p.W, inb[2] = h0 + 1 < p.H, inb[3] = inb[1] && inb[2];
+        float yv[4][8];
 #pragma unroll
-      for (int q = 0; q < 4; ++q)
-        if (inb[q]) load8<T>(ybase + (pos0 + (q >> 1) * p.Wp + (q & 1)) * G, yv[q]);
-      int arg[8];
+        for (int q = 0; q < 4; ++q)
+          if (inb[q]) load8<T>(ybase + (pos0 + (q >> 1) * p.Wp + (q & 1)) * G, yv[q]);
+        int arg[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float best = -INFINITY;
-        arg[j] = 0;
+        for (int j = 0; j < 8; ++j) {
+          float best = -INFINITY;
+          arg[j] = 0;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if (!inb[q]) continue;
+            const float r = fmaxf(fmaf(yv[q][j], k.sc[j], k.shf[j]), 0.f);
+            if (r > best) best = r, arg[j] = q;   // strict '>' : first maximum wins (scan order h, w)
+          }
+        }
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           if (!inb[q]) continue;
-          const float r = fmaxf(fmaf(yv[q][j], k.sc[j], k.shf[j]), 0.f);
-          if (r > best) best = r, arg[j] = q;   // strict '>' : first maximum wins (scan order h, w)
+          float dyv[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float v = fmaf(yv[q][j], k.sc[j], k.shf[j]);
+            const float g = (arg[j] == q && v > 0.f) ? dzv[j] : 0.f;
+            if (pass == 0) {
+              rg[j] += g, rgy[j] = fmaf(g, (yv[q][j] - k.a[j]) * k.b[j], rgy[j]);
+            } else {
+              dyv[j] = fmaf(k.sc[j], g, fmaf(k.b[j], yv[q][j], k.a[j]));
+            }
+          }
+          if (pass == 1) store8<T>(dybase + (pos0 + (q >> 1) * p.Wp + (q & 1)) * G, dyv);
         }
       }
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        if (!inb[q]) continue;
-        float dyv[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float v = fmaf(yv[q][j], k.sc[j], k.shf[j]);
-          const float g = (arg[j] == q && v > 0.f) ? dzv[j] : 0.f;
-          if (PASS == 0) {
-            rg[j] += g, rgy[j] = fmaf(g, (yv[q][j] - k.a[j]) * k.b[j], rgy[j]);
-          } else {
-            dyv[j] = fmaf(k.sc[j], g, fmaf(k.b[j], yv[q][j], k.a[j]));
-          }
-        }
-        if (PASS == 1) store8<T>(dybase + (pos0 + (q >> 1) * p.Wp + (q & 1)) * G, dyv);
+      if (pass == 0) {
+        block_reduce8(rg, p.bn.red_g + c * 8, sh);
+        block_reduce8(rgy, p.bn.red_gy + c * 8, sh);
+        chunk_barrier(p.sync + c, gridDim.x);
+        to_grad_const(p.bn, c, p.inv_n, k);
       }
     }
-    if (PASS == 0) {
-      block_reduce8(rg, bn.red_g + c * 8, sh);
-      block_reduce8(rgy, bn.red_gy + c * 8, sh);
-    } else if (blockIdx.x == 0) {
-      if (threadIdx.x == 0) write_bn_grads(p, bn, c, 1);
+    if (blockIdx.x == 0) {
+      if (threadIdx.x == 0) write_bn_grads(p.bn, p.gseg, p.ngseg, p.nchunks, c, 1);
       // the tensor-core weight gradient reduces 16 positions per MMA: keep [body, round_up(body,16)) zero
-      const long long full = (p.body / p.Pimgo) * p.Pimg;
-      if (threadIdx.x < 16 && full + threadIdx.x < (full + 15) / 16 * 16) {
+      if (threadIdx.x < 16 && p.body_full + threadIdx.x < (p.body_full + 15) / 16 * 16) {
         float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        store8<T>(dybase + (full + threadIdx.x) * G, z);
+        store8<T>(dybase + (p.body_full + threadIdx.x) * G, z);
       }
     }
     return;
@@ -396,171 +497,252 @@ __global__ void __launch_bounds__(kEwThreads) ew_bwd_kernel(const __grid_constan
 
   const int body16 = (body + 15) / 16 * 16;
   const bool dz_flat = p.dz.layout == LAY_P8;
-  if (PASS == 0 || MODE != EW_SIGMOID_MUL) {
-    // tasks outer, positions inner: the constants of (task, chunk) stay in registers
-    for (int t = 0; t < p.ntasks; ++t) {
-      const int ch = t * p.nchunks + c;
-      BwdConst k;
-      load_bwd_const<PASS>(bn, ch, p.inv_n, k);
-      float s2[8], h2[8], rg[8], rgy[8];
-      if (MODE == EW_ADD_RELU_SC) {
-        const BnArrays& bo = p.second ? p.bn : p.bn2;
-        ld_affine(bo.scale, ch * 8, s2);
-        ld_affine(bo.shift, ch * 8, h2);
+  const bool need_pos = !dz_flat || ((MODE == EW_ADD_RELU_ID || MODE == EW_SIGMOID_MUL) && p.aux.layout != LAY_P8);
+  constexpr int U = MODE == EW_RELU ? Batch<T>::n : Batch<T>::n / 2;  // three-input modes: smaller batches (registers)
+  constexpr bool kOther = MODE != EW_RELU;   // a second saved input (shortcut raw tensor / residual / feature map)
+
+  // ---- phase 1: reductions (tasks outer; the constants of (task, chunk) stay in registers) -------------------
+  for (int t = 0; t < p.ntasks; ++t) {
+    const int ch = t * p.nchunks + c;
+    BwdConst k;
+    load_fwd_const(p.bn, ch, k);
+    float s2[8], h2[8], m2[8], i2[8], rg[8], rgy[8], rgy2[8];
+    if (MODE == EW_ADD_RELU_SC) {
+      ld_affine(p.bn2.scale, ch * 8, s2);
+      ld_affine(p.bn2.shift, ch * 8, h2);
+      ld_affine(p.bn2.mean, ch * 8, m2);
+      ld_affine(p.bn2.invstd, ch * 8, i2);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) rg[j] = rgy[j] = rgy2[j] = 0.f;
+    const char* ybase = p.y.base + ((long long)ch * p.y.plane + p.y.g_lo) * G;
+    const char* y2base = MODE == EW_ADD_RELU_SC ? p.y2.base + ((long long)ch * p.y2.plane + p.y2.g_lo) * G : nullptr;
+    const char* dzbase = p.dz.base + ((long long)ch * p.dz.plane + p.dz.g_lo) * G;
+    for (int f0 = first; f0 < body; f0 += U * stride) {
+      Raw<T> ry[U], rdz[U], ro[U];
+      bool ok[U];
+#pragma unroll
+      for (int i = 0; i < U; ++i) {  // issue every load of the batch before the first use
+        const int f = f0 + i * stride;
+        ok[i] = f < body;
+        // over flat tensors no coordinates are needed: dz, y and aux are zero at pads, so g is zero there
+        Pos3 q{0, 0, 0};
+        if (need_pos) {
+          q = decode3(ok[i] ? f : 0, p.Pimg, p.Wp, p.magic_pimg, p.magic_wp);
+          ok[i] = ok[i] && q.h < p.H && q.w < p.W;
+        }
+        if (ok[i]) {
+          load_raw(ybase + (long long)f * G, ry[i]);
+          load_raw(dz_flat ? dzbase + (long long)f * G : view_addr<T>(p.dz, ch, f, q.n, q.h, q.w), rdz[i]);
+          if (MODE == EW_ADD_RELU_SC) load_raw(y2base + (long long)f * G, ro[i]);
+          if (MODE == EW_ADD_RELU_ID || MODE == EW_SIGMOID_MUL) load_raw(view_addr<T>(p.aux, c, f, q.n, q.h, q.w), ro[i]);
+        }
       }
 #pragma unroll
-      for (int j = 0; j < 8; ++j) rg[j] = rgy[j] = 0.f;
-      const char* ybase = ym.base + ((long long)ch * ym.plane + ym.g_lo) * G;
-      const ActView& yo = p.second ? p.y : p.y2;
-      const char* y2base = MODE == EW_ADD_RELU_SC ? yo.base + ((long long)ch * yo.plane + yo.g_lo) * G : nullptr;
-      char* dybase = p.dy.base + ((long long)ch * p.dy.plane + p.dy.g_lo) * G;
-      const char* dzbase = p.dz.base + ((long long)ch * p.dz.plane + p.dz.g_lo) * G;
-      const int limit = PASS == 0 ? body : body16;
-#pragma unroll 2
-      for (int f = first; f < limit; f += stride) {
-        // PASS 0 over flat tensors needs no coordinates: dz, y and aux are zero at pads, so g is zero there
-        bool valid = true;
-        Pos3 q{0, 0, 0};
-        if (PASS == 1 || !dz_flat || (MODE != EW_RELU && MODE != EW_ADD_RELU_SC && p.aux.layout != LAY_P8)) {
-          q = decode3(f < body ? f : 0, p.Pimg, p.Wp, p.magic_pimg, p.magic_wp);
-          valid = f < body && q.h < p.H && q.w < p.W;
+      for (int i = 0; i < U; ++i) {
+        if (!ok[i]) continue;
+        float y[8], dzv[8], other[8], g[8], sg[8];
+        unpack(ry[i], y);
+        unpack(rdz[i], dzv);
+        if (kOther) unpack(ro[i], other);
+        act_grad<MODE>(y, dzv, other, k, s2, h2, g, sg);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          rg[j] += g[j], rgy[j] = fmaf(g[j], (y[j] - k.a[j]) * k.b[j], rgy[j]);
+          if (MODE == EW_ADD_RELU_SC) rgy2[j] = fmaf(g[j], (other[j] - m2[j]) * i2[j], rgy2[j]);
         }
-        float dyv[8];
+      }
+    }
+    if (MODE == EW_ADD_RELU_SC) {
+      float rg2[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) dyv[j] = 0.f;
-        if (valid) {
-          float y[8], dzv[8], g[8];
-          load8<T>(ybase + (long long)f * G, y);
-          load8<T>(dz_flat ? dzbase + (long long)f * G : view_addr<T>(p.dz, ch, f, q.n, q.h, q.w), dzv);
-          if (MODE == EW_RELU) {
+      for (int j = 0; j < 8; ++j) rg2[j] = rg[j];
+      block_reduce8(rg2, p.bn2.red_g + ch * 8, sh);
+      block_reduce8(rgy2, p.bn2.red_gy + ch * 8, sh);
+    }
+    block_reduce8(rg, p.bn.red_g + ch * 8, sh);
+    block_reduce8(rgy, p.bn.red_gy + ch * 8, sh);
+  }
+  chunk_barrier(p.sync + c, gridDim.x);
+  if (first == 0) {
+    write_bn_grads(p.bn, p.gseg, p.ngseg, p.nchunks, c, p.ntasks);
+    if (MODE == EW_ADD_RELU_SC) write_bn_grads(p.bn2, p.gseg2, p.ngseg2, p.nchunks, c, p.ntasks);
+  }
+
+  // ---- phase 2: gradients ------------------------------------------------------------------------------------
+  if (MODE != EW_SIGMOID_MUL) {
+    for (int t = 0; t < p.ntasks; ++t) {
+      const int ch = t * p.nchunks + c;
+      BwdConst k, k2;
+      load_fwd_const(p.bn, ch, k);
+      to_grad_const(p.bn, ch, p.inv_n, k);
+      if (MODE == EW_ADD_RELU_SC) {
+        load_fwd_const(p.bn2, ch, k2);
+        to_grad_const(p.bn2, ch, p.inv_n, k2);
+      }
+      const char* ybase = p.y.base + ((long long)ch * p.y.plane + p.y.g_lo) * G;
+      const char* y2base = MODE == EW_ADD_RELU_SC ? p.y2.base + ((long long)ch * p.y2.plane + p.y2.g_lo) * G : nullptr;
+      const char* dzbase = p.dz.base + ((long long)ch * p.dz.plane + p.dz.g_lo) * G;
+      char* dybase = p.dy.base + ((long long)ch * p.dy.plane + p.dy.g_lo) * G;
+      char* dy2base = MODE == EW_ADD_RELU_SC ? p.dy2.base + ((long long)ch * p.dy2.plane + p.dy2.g_lo) * G : nullptr;
+      const bool rmw = MODE == EW_ADD_RELU_ID && p.want_daux && p.daux_accum;
+      for (int f0 = first; f0 < body16; f0 += U * stride) {
+        Raw<T> ry[U], rdz[U], ro[U], rold[U];
+        Pos3 q[U];
+        bool valid[U];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) g[j] = fmaf(y[j], k.sc[j], k.shf[j]) > 0.f ? dzv[j] : 0.f;
-          } else if (MODE == EW_ADD_RELU_SC) {
-            float y2[8];
-            load8<T>(y2base + (long long)f * G, y2);
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-              g[j] = (fmaf(y[j], k.sc[j], k.shf[j]) + fmaf(y2[j], s2[j], h2[j])) > 0.f ? dzv[j] : 0.f;
-          } else {
-            float aux[8];
-            load8<T>(view_addr<T>(p.aux, c, f, q.n, q.h, q.w), aux);
-            if (MODE == EW_ADD_RELU_ID) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) g[j] = (fmaf(y[j], k.sc[j], k.shf[j]) + aux[j]) > 0.f ? dzv[j] : 0.f;
-            } else {  // EW_SIGMOID_MUL (PASS 0 only on this path)
-#pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                const float sg = 1.f / (1.f + expf(-fmaf(y[j], k.sc[j], k.shf[j])));
-                g[j] = dzv[j] * aux[j] * sg * (1.f - sg);
-              }
-            }
+        for (int i = 0; i < U; ++i) {
+          const int f = f0 + i * stride;
+          q[i] = decode3(f < body ? f : 0, p.Pimg, p.Wp, p.magic_pimg, p.magic_wp);
+          valid[i] = f < body && q[i].h < p.H && q[i].w < p.W;
+          if (valid[i]) {
+            load_raw(ybase + (long long)f * G, ry[i]);
+            load_raw(dz_flat ? dzbase + (long long)f * G : view_addr<T>(p.dz, ch, f, q[i].n, q[i].h, q[i].w), rdz[i]);
+            if (MODE == EW_ADD_RELU_SC) load_raw(y2base + (long long)f * G, ro[i]);
+            if (MODE == EW_ADD_RELU_ID) load_raw(view_addr<T>(p.aux, c, f, q[i].n, q[i].h, q[i].w), ro[i]);
+            if (rmw) load_raw(view_addr<T>(p.daux, c, f, q[i].n, q[i].h, q[i].w), rold[i]);
           }
-          if (PASS == 0) {
+        }
 #pragma unroll
-            for (int j = 0; j < 8; ++j) rg[j] += g[j], rgy[j] = fmaf(g[j], (y[j] - k.a[j]) * k.b[j], rgy[j]);
-          } else {
+        for (int i = 0; i < U; ++i) {
+          const int f = f0 + i * stride;
+          if (f >= body16) continue;
+          float dyv[8], dyv2[8];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) dyv[j] = fmaf(k.sc[j], g[j], fmaf(k.b[j], y[j], k.a[j]));
+          for (int j = 0; j < 8; ++j) dyv[j] = dyv2[j] = 0.f;
+          if (valid[i]) {
+            float y[8], dzv[8], other[8], g[8], sg[8];
+            unpack(ry[i], y);
+            unpack(rdz[i], dzv);
+            if (kOther) unpack(ro[i], other);
+            // the sign test needs the forward scale / shift: k keeps them (only a / b changed meaning)
+            act_grad<MODE>(y, dzv, other, k, k2.sc, k2.shf, g, sg);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              dyv[j] = fmaf(k.sc[j], g[j], fmaf(k.b[j], y[j], k.a[j]));
+              if (MODE == EW_ADD_RELU_SC) dyv2[j] = fmaf(k2.sc[j], g[j], fmaf(k2.b[j], other[j], k2.a[j]));
+            }
             if (MODE == EW_ADD_RELU_ID && p.want_daux) {  // d residual = g
-              char* a = view_addr<T>(p.daux, c, f, q.n, q.h, q.w);
-              if (p.daux_accum) {
+              if (rmw) {
                 float old[8];
-                load8<T>(a, old);
+                unpack(rold[i], old);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) g[j] += old[j];
               }
-              store8<T>(a, g);
+              store8<T>(view_addr<T>(p.daux, c, f, q[i].n, q[i].h, q[i].w), g);
             }
+          } else if (MODE == EW_ADD_RELU_ID && p.want_daux && !p.daux_accum && f < body && p.daux.layout == LAY_P8) {
+            store8<T>(view_addr<T>(p.daux, c, f, q[i].n, q[i].h, q[i].w), dyv);  // zero at the pads of a fresh tensor
           }
-        } else if (PASS == 1 && MODE == EW_ADD_RELU_ID && p.want_daux && !p.daux_accum && f < body &&
-                   p.daux.layout == LAY_P8) {
-          store8<T>(view_addr<T>(p.daux, c, f, q.n, q.h, q.w), dyv);  // zero at the pads of a freshly written tensor
+          // zero at pads, and zero up to the next multiple of 16 positions (tensor-core wgrad granularity)
+          store8<T>(dybase + (long long)f * G, dyv);
+          if (MODE == EW_ADD_RELU_SC) store8<T>(dy2base + (long long)f * G, dyv2);
         }
-        // zero at pads, and zero up to the next multiple of 16 positions (tensor-core wgrad granularity)
-        if (PASS == 1) store8<T>(dybase + (long long)f * G, dyv);
-      }
-      if (PASS == 0) {
-        block_reduce8(rg, bn.red_g + ch * 8, sh);
-        block_reduce8(rgy, bn.red_gy + ch * 8, sh);
       }
     }
-    if (PASS == 1 && first == 0) write_bn_grads(p, bn, c, p.ntasks);
     return;
   }
 
-  // EW_SIGMOID_MUL, PASS 1: d feat sums over the tasks at one position, so the tasks are the inner loop and
-  // their constants sit in shared memory
-  constexpr int kMaxTasks = 4;
+  // EW_SIGMOID_MUL: d feat sums over the tasks at one position, so the tasks are the inner loop and their
+  // constants sit in shared memory
   __shared__ float cst[kMaxTasks][4][8];
   if (threadIdx.x < p.ntasks * 8) {
     const int t = threadIdx.x >> 3, j = threadIdx.x & 7, chn = (t * p.nchunks + c) * 8 + j;
-    const double cg = bn.red_g[chn] * (double)p.inv_n, cgy = bn.red_gy[chn] * (double)p.inv_n;
-    const double mu = bn.mean[chn], is = bn.invstd[chn], sc = bn.scale[chn];
-    cst[t][0][j] = bn.scale[chn], cst[t][1][j] = bn.shift[chn];
+    const double cg = __ldcg(p.bn.red_g + chn) * (double)p.inv_n, cgy = __ldcg(p.bn.red_gy + chn) * (double)p.inv_n;
+    const double mu = p.bn.mean[chn], is = p.bn.invstd[chn], sc = p.bn.scale[chn];
+    cst[t][0][j] = p.bn.scale[chn], cst[t][1][j] = p.bn.shift[chn];
     cst[t][2][j] = (float)(-sc * (cg - cgy * mu * is));
     cst[t][3][j] = (float)(-sc * cgy * is);
   }
   __syncthreads();
-  for (int f = first; f < body16; f += stride) {
-    const Pos3 q = decode3(f < body ? f : 0, p.Pimg, p.Wp, p.magic_pimg, p.magic_wp);
-    const bool valid = f < body && q.h < p.H && q.w < p.W;
-    float dacc[8], aux[8];
+  constexpr int V = Batch<T>::n / 2;  // every position carries 1 + 2*ntasks (+1) loads already
+  const bool rmw = p.want_daux && p.daux_accum;
+  for (int f0 = first; f0 < body16; f0 += V * stride) {
+    Raw<T> raux[V], rold[V], ry[V][kMaxTasks], rdz[V][kMaxTasks];
+    Pos3 q[V];
+    bool valid[V];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) dacc[j] = 0.f;
-    if (valid) load8<T>(view_addr<T>(p.aux, c, f, q.n, q.h, q.w), aux);
-    for (int t = 0; t < p.ntasks; ++t) {
-      const int ch = t * p.nchunks + c;
-      float dyv[8];
+    for (int i = 0; i < V; ++i) {
+      const int f = f0 + i * stride;
+      q[i] = decode3(f < body ? f : 0, p.Pimg, p.Wp, p.magic_pimg, p.magic_wp);
+      valid[i] = f < body && q[i].h < p.H && q[i].w < p.W;
+      if (valid[i]) {
+        load_raw(view_addr<T>(p.aux, c, f, q[i].n, q[i].h, q[i].w), raux[i]);
+        if (rmw) load_raw(view_addr<T>(p.daux, c, f, q[i].n, q[i].h, q[i].w), rold[i]);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) dyv[j] = 0.f;
-      if (valid) {
-        float y[8], dzv[8];
-        load8<T>(ym.base + ((long long)ch * ym.plane + ym.g_lo + f) * G, y);
-        load8<T>(view_addr<T>(p.dz, ch, f, q.n, q.h, q.w), dzv);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float sg = 1.f / (1.f + expf(-fmaf(y[j], cst[t][0][j], cst[t][1][j])));
-          const float g = dzv[j] * aux[j] * sg * (1.f - sg);
-          dacc[j] = fmaf(dzv[j], sg, dacc[j]);
-          dyv[j] = fmaf(cst[t][0][j], g, fmaf(cst[t][3][j], y[j], cst[t][2][j]));
-        }
+        for (int t = 0; t < kMaxTasks; ++t)
+          if (t < p.ntasks) {
+            const int ch = t * p.nchunks + c;
+            load_raw(p.y.base + ((long long)ch * p.y.plane + p.y.g_lo + f) * G, ry[i][t]);
+            load_raw(view_addr<T>(p.dz, ch, f, q[i].n, q[i].h, q[i].w), rdz[i][t]);
+          }
       }
-      store8<T>(p.dy.base + ((long long)ch * p.dy.plane + p.dy.g_lo + f) * G, dyv);
     }
-    if (p.want_daux && f < body && (valid || p.daux.layout == LAY_P8)) {
-      char* a = view_addr<T>(p.daux, c, f, q.n, q.h, q.w);
-      if (p.daux_accum) {
-        if (!valid) continue;
-        float old[8];
-        load8<T>(a, old);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) dacc[j] += old[j];
+    for (int i = 0; i < V; ++i) {
+      const int f = f0 + i * stride;
+      if (f >= body16) continue;
+      float dacc[8], aux[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) dacc[j] = 0.f;
+      if (valid[i]) unpack(raux[i], aux);
+#pragma unroll
+      for (int t = 0; t < kMaxTasks; ++t) {
+        if (t >= p.ntasks) continue;
+        const int ch = t * p.nchunks + c;
+        float dyv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dyv[j] = 0.f;
+        if (valid[i]) {
+          float y[8], dzv[8];
+          unpack(ry[i][t], y);
+          unpack(rdz[i][t], dzv);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float sg = 1.f / (1.f + expf(-fmaf(y[j], cst[t][0][j], cst[t][1][j])));
+            const float g = dzv[j] * aux[j] * sg * (1.f - sg);
+            dacc[j] = fmaf(dzv[j], sg, dacc[j]);
+            dyv[j] = fmaf(cst[t][0][j], g, fmaf(cst[t][3][j], y[j], cst[t][2][j]));
+          }
+        }
+        store8<T>(p.dy.base + ((long long)ch * p.dy.plane + p.dy.g_lo + f) * G, dyv);
       }
-      store8<T>(a, dacc);
+      if (p.want_daux && f < body && (valid[i] || p.daux.layout == LAY_P8)) {
+        if (p.daux_accum) {
+          if (!valid[i]) continue;
+          float old[8];
+          unpack(rold[i], old);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) dacc[j] += old[j];
+        }
+        store8<T>(view_addr<T>(p.daux, c, f, q[i].n, q[i].h, q[i].w), dacc);
+      }
     }
   }
-  if (first == 0) write_bn_grads(p, bn, c, p.ntasks);
 }
 
-template <typename T, int PASS>
-static cudaError_t launch_ew_bwd_t(const EwParams& p, cudaStream_t st) {
-  if (p.mode == EW_SIGMOID_MUL && p.ntasks > 4) return cudaErrorInvalidValue;
-  dim3 grid(blocks_per_chunk(p.body, p.nchunks), p.nchunks);
-  switch (p.mode) {
-    case EW_RELU: ew_bwd_kernel<T, EW_RELU, PASS><<<grid, kEwThreads, 0, st>>>(p); break;
-    case EW_ADD_RELU_ID: ew_bwd_kernel<T, EW_ADD_RELU_ID, PASS><<<grid, kEwThreads, 0, st>>>(p); break;
-    case EW_ADD_RELU_SC: ew_bwd_kernel<T, EW_ADD_RELU_SC, PASS><<<grid, kEwThreads, 0, st>>>(p); break;
-    case EW_SIGMOID_MUL: ew_bwd_kernel<T, EW_SIGMOID_MUL, PASS><<<grid, kEwThreads, 0, st>>>(p); break;
-    case EW_RELU_POOL: ew_bwd_kernel<T, EW_RELU_POOL, PASS><<<grid, kEwThreads, 0, st>>>(p); break;
-    default: return cudaErrorInvalidValue;
-  }
+template <typename T, int MODE>
+static cudaError_t launch_ew_bwd_m(const EwParams& p, cudaStream_t st) {
+  dim3 grid(resident_blocks_per_chunk(ew_bwd_kernel<T, MODE>, std::max(p.body, p.body_full), p.nchunks), p.nchunks);
+  ew_bwd_kernel<T, MODE><<<grid, kEwThreads, 0, st>>>(p);
   return cudaGetLastError();
 }
 
-cudaError_t launch_ew_bwd(const EwParams& p, int pass, int precision, cudaStream_t st) {
-  if (precision == 0)
-    return pass == 0 ? launch_ew_bwd_t<__nv_bfloat16, 0>(p, st) : launch_ew_bwd_t<__nv_bfloat16, 1>(p, st);
-  return pass == 0 ? launch_ew_bwd_t<float, 0>(p, st) : launch_ew_bwd_t<float, 1>(p, st);
+template <typename T>
+static cudaError_t launch_ew_bwd_t(const EwParams& p, cudaStream_t st) {
+  if (p.ntasks > kMaxTasks || !p.sync) return cudaErrorInvalidValue;
+  switch (p.mode) {
+    case EW_RELU: return launch_ew_bwd_m<T, EW_RELU>(p, st);
+    case EW_ADD_RELU_ID: return launch_ew_bwd_m<T, EW_ADD_RELU_ID>(p, st);
+    case EW_ADD_RELU_SC: return launch_ew_bwd_m<T, EW_ADD_RELU_SC>(p, st);
+    case EW_SIGMOID_MUL: return launch_ew_bwd_m<T, EW_SIGMOID_MUL>(p, st);
+    case EW_RELU_POOL: return launch_ew_bwd_m<T, EW_RELU_POOL>(p, st);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+cudaError_t launch_ew_bwd(const EwParams& p, int precision, cudaStream_t st) {
+  return precision == 0 ? launch_ew_bwd_t<__nv_bfloat16>(p, st) : launch_ew_bwd_t<float>(p, st);
 }
 
 // ---------------------------------------------------------------------------------------------

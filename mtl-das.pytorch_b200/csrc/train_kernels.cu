@@ -18,54 +18,6 @@
 
 namespace mtldas {
 
-namespace {
-
-struct Pos {
-  int n, h, w;
-  bool valid;
-};
-__device__ __forceinline__ Pos decode(int f, int Pimg, int Wp, int H, int W) {
-  Pos p;
-  p.n = f / Pimg;
-  const int rem = f - p.n * Pimg;
-  p.h = rem / Wp;
-  p.w = rem - p.h * Wp;
-  p.valid = p.h < H && p.w < W;
-  return p;
-}
-
-__device__ __forceinline__ void load_affine(const float* a, int c0, float* v) {
-  const float4 x = reinterpret_cast<const float4*>(a + c0)[0], y = reinterpret_cast<const float4*>(a + c0)[1];
-  v[0] = x.x, v[1] = x.y, v[2] = x.z, v[3] = x.w, v[4] = y.x, v[5] = y.y, v[6] = y.z, v[7] = y.w;
-}
-
-__device__ __forceinline__ void load_affine_d(const double* a, int c0, float k, float* v) {
-#pragma unroll
-  for (int j = 0; j < 8; ++j) v[j] = (float)(a[c0 + j] * (double)k);
-}
-
-// block-wide sum of 8 per-thread values -> atomicAdd(double) by warp 0; blockDim.x == 256
-__device__ __forceinline__ void block_reduce8_atomic(float* v, double* dst, float (*sh)[8]) {
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v[j] += __shfl_xor_sync(0xffffffffu, v[j], o);
-  }
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (lane == 0) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) sh[warp][j] = v[j];
-  }
-  __syncthreads();
-  if (threadIdx.x < 8) {
-    float s = 0.f;
-    for (int wv = 0; wv < 8; ++wv) s += sh[wv][threadIdx.x];
-    atomicAdd(dst + threadIdx.x, (double)s);
-  }
-  __syncthreads();
-}
-
-}  // namespace
 
 __global__ void bn_grad_kernel(const __grid_constant__ BnGradParams p) {
   const int c = threadIdx.x;

@@ -6,11 +6,10 @@
 
 namespace mtldas {
 
-cudaError_t launch_stats(const StatsParams& p, int precision, cudaStream_t st);
 cudaError_t launch_finalize(const FinalizeParams& p, cudaStream_t st);
 cudaError_t launch_bn_grad(const BnGradParams& p, cudaStream_t st);
 cudaError_t launch_ew_fwd(const EwParams& p, int precision, cudaStream_t st);
-cudaError_t launch_ew_bwd(const EwParams& p, int pass, int precision, cudaStream_t st);
+cudaError_t launch_ew_bwd(const EwParams& p, int precision, cudaStream_t st);
 cudaError_t launch_wgrad(const WgradParams& p, int precision, cudaStream_t st);
 cudaError_t launch_stem_wgrad(const StemWgradParams& p, int precision, cudaStream_t st);
 cudaError_t launch_head_bwd(const HeadBwdParams& p, int precision, cudaStream_t st);

@@ -34,32 +34,6 @@ struct BnGradSeg {       // d gamma / d beta of one reference BatchNorm out of a
   int ch_off, count;
 };
 
-struct EwParams {
-  int mode;
-  int ntasks;            // tasks stacked along channels that share `aux` (EW_SIGMOID_MUL), else 1
-  int nchunks;           // chunks per task of y / out / dz / dy
-  int H, W, Wp, Pimg;    // geometry of y (full resolution)
-  int Ho, Wo, Wpo, Pimgo;  // pooled geometry (EW_RELU_POOL)
-  long long body;        // nb * Pimg   (EW_RELU_POOL: nb * Pimgo, threads iterate pooled positions)
-  float inv_n;           // 1 / (nb*H*W)
-  ActView y;             // raw conv output
-  BnArrays bn;
-  ActView y2;            // EW_ADD_RELU_SC: raw shortcut conv output
-  BnArrays bn2;
-  ActView aux;           // identity residual / feature map (EW_ADD_RELU_ID, EW_SIGMOID_MUL)
-  ActView out;           // forward result
-  ActView dz;            // backward: gradient w.r.t. the forward result
-  ActView dy;            // backward: gradient w.r.t. y (written, zero at pads)
-  ActView daux;          // backward: gradient w.r.t. aux
-  int daux_accum;        // 1: daux += , 0: daux =
-  int want_daux;
-  int ngseg;             // backward pass 1 also writes d gamma / d beta of the BatchNorm it differentiates
-  BnGradSeg gseg[2];
-  int second;            // EW_ADD_RELU_SC backward: 1 = this launch handles the shortcut branch (y2/bn2 are "main")
-  unsigned long long magic_pimg, magic_wp, magic_pimgo, magic_wpo;  // floor(2^40/d)+1 (exact f/d by multiply-shift)
-};
-
-
 struct FinalizeSeg {     // channels [ch_off, ch_off+count) of the tensor belong to one reference BatchNorm
   const float* gamma;
   const float* beta;
@@ -78,15 +52,37 @@ struct FinalizeParams {
   FinalizeSeg seg[2];
 };
 
-struct StatsParams {     // sum / sum of squares of a raw tensor (pads are zero, so whole planes are summed);
-  ActView y;             // the last block to finish also finalizes the BatchNorm (fin), so no second launch
-  int nchunks;
-  long long body;
-  double* sum;
-  double* sumsq;
-  unsigned int* done;    // completion counter (zeroed with the sums)
-  FinalizeParams fin;
+struct EwParams {
+  int mode;
+  int ntasks;            // tasks stacked along channels that share `aux` (EW_SIGMOID_MUL), else 1
+  int nchunks;           // chunks per task of y / out / dz / dy
+  int H, W, Wp, Pimg;    // geometry of y (full resolution)
+  int Ho, Wo, Wpo, Pimgo;  // pooled geometry (EW_RELU_POOL)
+  long long body;        // nb * Pimg   (EW_RELU_POOL: nb * Pimgo, threads iterate pooled positions)
+  float inv_n;           // 1 / (nb*H*W)
+  ActView y;             // raw conv output
+  BnArrays bn;
+  ActView y2;            // EW_ADD_RELU_SC: raw shortcut conv output
+  BnArrays bn2;
+  ActView aux;           // identity residual / feature map (EW_ADD_RELU_ID, EW_SIGMOID_MUL)
+  ActView out;           // forward result
+  ActView dz;            // backward: gradient w.r.t. the forward result
+  ActView dy;            // backward: gradient w.r.t. y (written, zero at pads)
+  ActView dy2;           // backward, EW_ADD_RELU_SC: gradient w.r.t. y2
+  ActView daux;          // backward: gradient w.r.t. aux
+  int daux_accum;        // 1: daux += , 0: daux =
+  int want_daux;
+  int ngseg;             // the backward kernel also writes d gamma / d beta of the BatchNorm it differentiates
+  BnGradSeg gseg[2];
+  int ngseg2;            // EW_ADD_RELU_SC: the shortcut BatchNorm's d gamma / d beta
+  BnGradSeg gseg2[2];
+  unsigned long long magic_pimg, magic_wp, magic_pimgo, magic_wpo;  // floor(2^40/d)+1 (exact f/d by multiply-shift)
+  // fused kernels: statistics -> per-chunk barrier -> apply (forward), reductions -> barrier -> gradients (backward)
+  FinalizeParams fin, fin2;  // forward: BatchNorm finalize of bn (and bn2, EW_ADD_RELU_SC) done inside the kernel
+  unsigned int* sync;        // [chunks] arrival counters, zeroed with the sums (forward) / reductions (backward)
+  long long body_full;       // nb * Pimg (== body except EW_RELU_POOL, where body counts pooled positions)
 };
+
 
 struct BnGradParams {
   BnArrays bn;
