@@ -156,6 +156,28 @@ void choose_tiling(ConvOpHost& op, long long positions) {
     if (MT * op.Cout <= 512 && op.Cout >= 128 && op.nchunks >= 16 && slab + 2 * (size_t)op.tap_bytes <= 216 * 1024) break;
   }
   op.MT = MT;
+  // weights too large for two CTAs per SM but small enough to stay resident next to two input slabs: one persistent
+  // CTA per SM with two TMEM accumulator sets (epilogue of tile i under the MMAs of tile i+1) instead of the
+  // one-tile-per-CTA ring kernel whose phases run back to back
+  static int big_resident = -1;
+  if (big_resident < 0) {
+    const char* e = getenv("MTLDAS_BIG_RESIDENT");
+    big_resident = (e && e[0] == '0') ? 0 : 1;
+  }
+  if (big_resident && slab + total_w > 96 * 1024) {
+    for (int m = 2; m >= 2; m >>= 1) {  // MT = 1 (64 -> 128 layers) measured slower than the ring kernel
+      if (m > MT) continue;
+      const size_t sl = (size_t)op.nsrc * op.nchunks * (m * kTileM + op.halo_lo + op.halo_hi) * 16;
+      if ((size_t)total_w + 2 * sl <= 196 * 1024 && 2 * m * op.Cout <= 512) {
+        MT = m, slab = sl;
+        op.MT = MT, op.tps = op.ntaps, op.NS = 1, op.nstages = 1, op.ksplit = 0;
+        int c = 32;
+        while (c < MT * op.Cout) c <<= 1;
+        op.tmem_cols = c;
+        return;
+      }
+    }
+  }
   if (slab + total_w <= 96 * 1024) {
     op.tps = op.ntaps;
     op.NS = 1;
