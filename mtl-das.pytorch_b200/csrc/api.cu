@@ -46,10 +46,10 @@ mtldas_plan* mtldas_plan_create(int model_kind, int micro_batch, int precision) 
   h->p->use_graphs = (ng && ng[0] == '1') ? 0 : 1;
   const char* np = getenv("MTLDAS_NO_PDL");
   h->p->use_pdl = (np && np[0] == '1') ? 0 : 1;
-  // tensor-core stem (stem_umma.cu) is correct but measured slower than the FFMA2 stem on B200 (0.85 vs 0.58 ms per
-  // 4096 patches: its stage/build/drain phases serialise per tile); opt in with MTLDAS_UMMA_STEM=1
+  // tensor-core stem (stem_umma.cu, one banded GEMM per output row): 0.25 vs 0.58 ms per 4096 patches for the FFMA2
+  // kernel; MTLDAS_UMMA_STEM=0 falls back to the CUDA-core stem
   const char* nus = getenv("MTLDAS_UMMA_STEM");
-  h->p->use_umma_stem = (nus && nus[0] == '1') ? 1 : 0;
+  h->p->use_umma_stem = (nus && nus[0] == '0') ? 0 : 1;
   const char* npz = getenv("MTLDAS_NO_PERSIST");
   h->p->use_persist = (npz && npz[0] == '1') ? 0 : 1;
   return h;
@@ -239,6 +239,8 @@ mtldas_train* mtldas_train_create(int model_kind, int batch, int precision) {
   }
   mtldas_train* h = new mtldas_train();
   h->tp = build_train_plan(model_kind, batch, precision);
+  const char* nus = getenv("MTLDAS_UMMA_STEM");
+  if (h->tp && h->tp->p) h->tp->p->use_umma_stem = (nus && nus[0] == '0') ? 0 : 1;
   return h;
 }
 void mtldas_train_destroy(mtldas_train* t) {

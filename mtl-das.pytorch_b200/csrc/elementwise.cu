@@ -97,7 +97,12 @@ __global__ void __launch_bounds__(128) stem_kernel(const __grid_constant__ StemP
 cudaError_t launch_stem_umma(const StemParams& p, cudaStream_t stream, bool pdl);
 
 cudaError_t launch_stem(const StemParams& p, int precision, cudaStream_t stream, bool pdl) {
-  if (precision == 0 && p.w_umma) return launch_stem_umma(p, stream, pdl);
+  if (precision == 0 && p.w_umma) {
+    // the tensor-core stem needs a 16-byte aligned patch tensor (bulk copies); anything else takes the FFMA kernel
+    cudaError_t e = launch_stem_umma(p, stream, pdl);
+    if (e != cudaErrorInvalidValue) return e;
+    cudaGetLastError();
+  }
   unsigned grid = (unsigned)((p.body + 255) / 256);
   if (precision == 0) return launch_ex(stem_kernel<__nv_bfloat16>, dim3(grid), dim3(128), stream, pdl, p);
   return launch_ex(stem_kernel<float>, dim3(grid), dim3(128), stream, pdl, p);
@@ -219,8 +224,8 @@ __device__ __forceinline__ void pack_element(const PackParams& p, int i) {
   }
   const float v = s.w[i] * scale;
   int tap = rs, k = ci, cop;
-  if (s.k_from_tap) {
-    tap = 0, k = rs, cop = s.cout_off + co;
+  if (s.k_from_tap) {  // 1: k = tap index; 2: banded stem image, k = filter row * 8 + filter column
+    tap = 0, k = s.k_from_tap == 2 ? (rs / s.ksize) * 8 + rs % s.ksize : rs, cop = s.cout_off + co;
   } else if (s.transpose) {
     if (ci < s.ci_lo || ci >= s.ci_lo + s.ci_n) return;
     tap = s.tap_map[rs];

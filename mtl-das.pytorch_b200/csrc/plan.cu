@@ -523,7 +523,7 @@ int plan_pack_eval(Plan& p, const void* const* state, cudaStream_t stream) {
     CK(launch_pack(q, stream));
     if (p.precision == 0) {  // bf16 tensor-core stem: taps are the K dimension (49 -> 64)
       CK(cudaMemsetAsync(p.ws + p.stem_wu_off, 0, 2048, stream));
-      q.seg.k_from_tap = 1, q.dst = p.ws + p.stem_wu_off, q.K_tap = 64, q.fp32 = 0;
+      q.seg.k_from_tap = 2, q.dst = p.ws + p.stem_wu_off, q.K_tap = 64, q.fp32 = 0;
       CK(launch_pack(q, stream));
     }
   }

@@ -361,6 +361,7 @@ TrainPlan* build_train_plan(int kind, int batch, int precision) {
     }
   }
   p.stem_w_off = take(49 * 16 * 4);
+  p.stem_wu_off = take(2048);  // banded bf16 image of the tensor-core stem (zeroed with the other packs, then packed)
   tp.pack_end = o;
   tp.zero_bias_off = take(256 * sizeof(float));
   p.stem_b_off = tp.zero_bias_off;
@@ -460,6 +461,10 @@ static int pack_train(TrainPlan& tp, const void* const* state, cudaStream_t st) 
     q.dst = p.ws + p.stem_w_off, q.bias_dst = nullptr;
     q.Cout_p = 16, q.K_tap = 1, q.fp32 = 1, q.fold = 0;
     packs.push_back(q);
+    if (p.precision == 0 && p.use_umma_stem) {  // banded bf16 image of the tensor-core stem (its pads were zeroed by the memset above)
+      q.seg.k_from_tap = 2, q.dst = p.ws + p.stem_wu_off, q.K_tap = 64, q.fp32 = 0;
+      packs.push_back(q);
+    }
   }
   CK(launch_pack_batch(packs.data(), (int)packs.size(), st));
   return 0;
@@ -494,6 +499,7 @@ static int train_forward_eager(TrainPlan& tp, const void* const* state, const fl
       q.out = p.view(tp.y_stem, 0);
       q.Hin = kPatchH, q.Win = kPatchW, q.H = t.H, q.W = t.W, q.Wp = t.Wp, q.Pimg = t.Pimg;
       q.body = (long long)nb * t.Pimg, q.raw = 1;
+      q.w_umma = (p.precision == 0 && p.use_umma_stem) ? p.ws + p.stem_wu_off : nullptr;
       CK(launch_stem(q, p.precision, st));
     } else if (op.kind == TOP_CONV) {
       ConvParams q = p.conv_params(p.convs[op.a], nb);

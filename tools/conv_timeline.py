@@ -5,7 +5,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "mtl-das.pytorch_b200")]
 import torch
 from mtldas_b200 import conv2d_nchw
-N = 256
+N = int(sys.argv[1]) if len(sys.argv) > 1 else 256
 for (cin, cout, k, s, H, W, cin2) in [(16, 16, 3, 1, 33, 83, 0), (64, 128, 1, 2, 9, 21, 0), (128, 128, 3, 1, 5, 11, 0),
                                       (128, 64, 1, 1, 5, 11, 128), (16, 32, 3, 1, 33, 83, 0)]:
     x = torch.randn(N, cin, H, W, device="cuda")
