@@ -633,6 +633,13 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
     const int aux_nchunks = g.aux_nchunks;
     const int Cout = p.Cout, MT = p.MT, H = p.H, W = p.W, Wp = p.Wp, Pimg = p.Pimg, body = (int)p.body;
     const unsigned long long m_pimg = p.magic_pimg, m_wp = p.magic_wp;
+    // fused pool: exact multiply-shift divisors of the pooled index math (per-thread, once)
+    unsigned long long m_per_chunk = 0, m_wph = 0, m_hph = 0;
+    if (EPI == EPI_RELU && p.pool_k > 0) {
+      m_per_chunk = (1ull << 40) / (unsigned long long)(p.pool_k * (Wp >> 1)) + 1;
+      m_wph = (1ull << 40) / (unsigned long long)(Wp >> 1) + 1;
+      m_hph = (1ull << 40) / (unsigned long long)((H + 1) >> 1) + 1;
+    }
     int it = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       const int a = nsets == 2 ? (it & 1) : 0;
@@ -659,15 +666,20 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
         if (EPI == EPI_RELU && p.pool_k > 0) {
           // fused max-pool: relu(acc + bias) of this row goes to the shared-memory staging tile (zero at pads)
           const int row = mt * kTileM + quarter * 32 + lane;
-          for (int c0 = 0; c0 < Cout; c0 += 16) {
-            uint32_t r[16];
-            ptx::tmem_ld16_issue(trow + (uint32_t)c0, r);
-            ptx::tmem_wait16(r);
-            float v[16];
+          for (int c0 = 0; c0 < Cout; c0 += 32) {  // Cout is a multiple of 32 on the pooled layers (32 / 64 / 128)
+            uint32_t r[32];
+            ptx::tmem_ld32_issue(trow + (uint32_t)c0, r);
+            ptx::tmem_wait32(r);
 #pragma unroll
-            for (int j = 0; j < 16; ++j) v[j] = valid ? fmaxf(__uint_as_float(r[j]) + bias_s[c0 + j], 0.f) : 0.f;
-            store8<__nv_bfloat16>(reinterpret_cast<char*>(staging) + ((size_t)(c0 >> 3) * tile_rows + row) * 16, v);
-            store8<__nv_bfloat16>(reinterpret_cast<char*>(staging) + ((size_t)((c0 >> 3) + 1) * tile_rows + row) * 16, v + 8);
+            for (int hlf = 0; hlf < 2; ++hlf) {
+              float v[16];
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                v[j] = valid ? fmaxf(__uint_as_float(r[hlf * 16 + j]) + bias_s[c0 + hlf * 16 + j], 0.f) : 0.f;
+              const int ch = (c0 >> 3) + 2 * hlf;
+              store8<__nv_bfloat16>(reinterpret_cast<char*>(staging) + ((size_t)ch * tile_rows + row) * 16, v);
+              store8<__nv_bfloat16>(reinterpret_cast<char*>(staging) + ((size_t)(ch + 1) * tile_rows + row) * 16, v + 8);
+            }
           }
         } else if (Cout >= 32) {
           for (int c0 = 0; c0 < Cout; c0 += 32) {
@@ -711,8 +723,8 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
         const int hp_half = (H + 1) >> 1;                      // row pairs per image (Hp is even)
         const ActView pv = g.pool_out;
         for (int o = e; o < per_chunk * nch; o += nthr) {
-          const int c = o / per_chunk, q = o - c * per_chunk;
-          const int rp = q / Wph, cp = q - rp * Wph;
+          const int c = fast_div(o, m_per_chunk), q = o - c * per_chunk;
+          const int rp = fast_div(q, m_wph), cp = q - rp * Wph;
           const int r0 = 2 * rp * Wp + 2 * cp;                 // row in the staging tile
           if ((long long)tile * tile_pos + r0 >= p.body) continue;
           const uint4* sp = reinterpret_cast<const uint4*>(staging + ((size_t)c * tile_rows + r0) * 16);
@@ -725,11 +737,12 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
 #pragma unroll
           for (int j = 0; j < 4; ++j) mm[j] = __hmax2(__hmax2(mm[j], x1[j]), __hmax2(x2[j], x3[j]));
           const int R = tile * p.pool_k + rp;                  // global row-pair index
-          const int n = R / hp_half, ho = R - n * hp_half;
+          const int n = fast_div(R, m_hph), ho = R - n * hp_half;
           const long long pos = (long long)c * pv.plane + pv.g_lo + (long long)n * p.pool_Pimgo + ho * p.pool_Wpo + cp;
           *reinterpret_cast<uint4*>(pv.base + pos * 16) = m;
         }
         asm volatile("bar.sync 1, %0;" ::"r"(nthr) : "memory");  // staging is reused by the next tile
+        if (dbg_on) p.dbg[it * 8 + 7] = clock64();
       }
     }
   }

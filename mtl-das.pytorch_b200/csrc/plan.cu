@@ -561,6 +561,30 @@ static int run_pass(Plan& p, const float* x, int nb, float* out0, float* out1, c
       CK(launch_stem(q, p.precision, stream, pdl));
     } else if (op.kind == 1) {
       ConvParams q = p.conv_params(p.convs[op.index], nb);
+      static int pool_dbg = -1;
+      if (pool_dbg < 0) {
+        const char* e = getenv("MTLDAS_POOL_DEBUG");
+        pool_dbg = (e && e[0] == '1') ? 1 : 0;
+      }
+      if (pool_dbg && q.pool_k > 0 && q.persist_stages > 0) {  // diagnostic: per-iteration timeline of CTA 0
+        long long* dbg = nullptr;
+        CK(cudaMalloc(&dbg, 16 * 8 * sizeof(long long)));
+        CK(cudaMemset(dbg, 0, 16 * 8 * sizeof(long long)));
+        q.dbg = dbg;
+        CK(launch_conv(q, p.precision, stream, false));
+        CK(cudaStreamSynchronize(stream));
+        long long h[16 * 8];
+        CK(cudaMemcpy(h, dbg, sizeof(h), cudaMemcpyDeviceToHost));
+        cudaFree(dbg);
+        fprintf(stderr, "[pooldbg] %s MT %d pool_k %d Cout %d:\n", p.convs[op.index].name.c_str(), q.MT, q.pool_k, q.Cout);
+        for (int it = 0; it < 12; ++it) {
+          const long long* r = &h[(size_t)it * 8];
+          if (!r[0]) break;
+          fprintf(stderr, "[pooldbg]  it %2d mma: start %lld slab-ready +%lld acc-free +%lld issued +%lld | epi(w2): wait-start %lld acc-ready +%lld drained +%lld pooled +%lld\n",
+                  it, r[0] - h[0], r[1] - r[0], r[2] - r[1], r[3] - r[2], r[4] - h[0], r[5] - r[4], r[6] - r[5], r[7] - r[6]);
+        }
+        continue;
+      }
       CK(launch_conv(q, p.precision, stream, pdl));
     } else if (op.kind == 2) {
       const PoolOpHost& po = p.pools[op.index];
