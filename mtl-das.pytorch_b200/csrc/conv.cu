@@ -252,7 +252,7 @@ __device__ __forceinline__ void drain_with_aux(int ntile, int Cout, const float*
 }
 
 template <int EPI>
-__global__ void __launch_bounds__(128, 3) conv_umma_kernel(const __grid_constant__ ConvParams p) {
+__global__ void __launch_bounds__(256) conv_umma_kernel(const __grid_constant__ ConvParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   const ConvGroupDev& g = p.g[blockIdx.y];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
@@ -280,7 +280,7 @@ __global__ void __launch_bounds__(128, 3) conv_umma_kernel(const __grid_constant
     ptx::fence_mbar_init();
   }
   if (warp == 1) ptx::tmem_alloc(tmem_slot, (uint32_t)p.tmem_cols);
-  for (int i = threadIdx.x; i < p.Cout; i += 128) bias_s[i] = g.bias[i];
+  for (int i = threadIdx.x; i < p.Cout; i += blockDim.x) bias_s[i] = g.bias[i];
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
@@ -403,12 +403,16 @@ __global__ void __launch_bounds__(128, 3) conv_umma_kernel(const __grid_constant
     const long long out_plane_bytes = outv.plane * 16, aux_plane_bytes = auxv.plane * 16;
     const int aux_nchunks = g.aux_nchunks;
     const int Cout = p.Cout, MT = p.MT, H = p.H, W = p.W, Wp = p.Wp, Pimg = p.Pimg, body = (int)p.body;
+    // launched with 256 threads (layers that own the SM alone): warps w and w+4 share TMEM lane quarter w % 4 and
+    // take alternate accumulator tiles, halving the serial epilogue of the CTA
+    const int quarter = warp & 3, mt0 = warp >> 2, mt_step = (int)(blockDim.x >> 7);
     if ((EPI == EPI_ADD_RELU || EPI == EPI_SIGMOID_MUL) && !p.ksplit) {
       // the aux fetches below run ahead of every barrier of this kernel: order them after the previous grid here
       // (only the producer thread waited so far)
       ptx::pdl_grid_wait();
-      auto row_of = [&](int mt) {
-        const int f = tile_start + mt * kTileM + warp * 32 + lane;
+      auto row_of = [&](int i) {
+        const int mt = mt0 + i * mt_step;
+        const int f = tile_start + mt * kTileM + quarter * 32 + lane;
         const bool in_body = f < body;
         int n = 0, h = 0, w = 0;
         if (in_body) {
@@ -422,17 +426,18 @@ __global__ void __launch_bounds__(128, 3) conv_umma_kernel(const __grid_constant
         r.do_store = in_body && (r.valid || outv.layout == LAY_P8);
         r.out_addr0 = view_addr<__nv_bfloat16>(outv, 0, f, n, h, w);
         r.aux_addr0 = view_addr<__nv_bfloat16>(auxv, 0, f, n, h, w);
-        r.trow = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(mt * Cout);
+        r.trow = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(mt * Cout);
         return r;
       };
-      auto ready = [&](int mt) {
-        ptx::mbar_wait(bars + kBarAcc + mt, 0);
+      auto ready = [&](int i) {
+        ptx::mbar_wait(bars + kBarAcc + mt0 + i * mt_step, 0);
         ptx::tc_fence_after();
       };
-      drain_with_aux<EPI>(MT, Cout, bias_s, aux_plane_bytes, aux_nchunks, out_plane_bytes, row_of, ready);
+      const int nmine = mt0 < MT ? (MT - mt0 + mt_step - 1) / mt_step : 0;
+      if (nmine > 0) drain_with_aux<EPI>(nmine, Cout, bias_s, aux_plane_bytes, aux_nchunks, out_plane_bytes, row_of, ready);
     } else
-    for (int mt = 0; mt < MT; ++mt) {
-      const int f = tile_start + mt * kTileM + warp * 32 + lane;
+    for (int mt = mt0; mt < MT; mt += mt_step) {
+      const int f = tile_start + mt * kTileM + quarter * 32 + lane;
       const bool in_body = f < body;
       int n = 0, h = 0, w = 0;
       if (in_body) {
@@ -448,7 +453,7 @@ __global__ void __launch_bounds__(128, 3) conv_umma_kernel(const __grid_constant
       ptx::mbar_wait(bars + kBarAcc + mt, 0);
       ptx::tc_fence_after();
       if (mt == 0 && threadIdx.x == 64) DBG(5)
-      const uint32_t trow = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(mt * Cout);
+      const uint32_t trow = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(mt * Cout);
       if (Cout >= 32) {
         for (int c0 = 0; c0 < Cout; c0 += 32) {
           uint32_t r[32];
@@ -882,12 +887,14 @@ cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream,
     }
     int tile = p.MT * kTileM;
     dim3 grid((unsigned)((p.body + tile - 1) / tile), p.ngroups, 1);
+    // one CTA per SM anyway (all of TMEM or most of shared memory): give it a second set of epilogue warps
+    const dim3 block(p.tmem_cols > 256 && p.MT == 4 ? 256 : 128);  // (MT = 2 layers measured slower with 256)
     switch (p.epi) {
-      case EPI_NONE: return launch_ex(conv_umma_kernel<EPI_NONE>, grid, dim3(128), smem, stream, pdl, p);
-      case EPI_RELU: return launch_ex(conv_umma_kernel<EPI_RELU>, grid, dim3(128), smem, stream, pdl, p);
-      case EPI_ADD_RELU: return launch_ex(conv_umma_kernel<EPI_ADD_RELU>, grid, dim3(128), smem, stream, pdl, p);
-      case EPI_ACCUM: return launch_ex(conv_umma_kernel<EPI_ACCUM>, grid, dim3(128), smem, stream, pdl, p);
-      default: return launch_ex(conv_umma_kernel<EPI_SIGMOID_MUL>, grid, dim3(128), smem, stream, pdl, p);
+      case EPI_NONE: return launch_ex(conv_umma_kernel<EPI_NONE>, grid, block, smem, stream, pdl, p);
+      case EPI_RELU: return launch_ex(conv_umma_kernel<EPI_RELU>, grid, block, smem, stream, pdl, p);
+      case EPI_ADD_RELU: return launch_ex(conv_umma_kernel<EPI_ADD_RELU>, grid, block, smem, stream, pdl, p);
+      case EPI_ACCUM: return launch_ex(conv_umma_kernel<EPI_ACCUM>, grid, block, smem, stream, pdl, p);
+      default: return launch_ex(conv_umma_kernel<EPI_SIGMOID_MUL>, grid, block, smem, stream, pdl, p);
     }
   } else {
     size_t smem = (size_t)p.nchunks * 8 * kFp32CoutBlock * sizeof(float);

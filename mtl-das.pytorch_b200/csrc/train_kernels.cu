@@ -244,6 +244,203 @@ __global__ void __launch_bounds__(128) wgrad_umma_kernel(const __grid_constant__
   if (warp == 1) ptx::tmem_dealloc(tmem_base, cols);
 }
 
+// ---------------------------------------------------------------------------------------------
+// weight gradient, narrow layers (Cin <= 64, 3x3): the taps side by side along the MMA's N dimension.
+// An M = 128, K = 16 instruction costs ~45 cycles of A-operand reads whatever N <= 64 is, so nine N = Cin instructions
+// per 16 positions waste the tensor pipe; here the stage's input slab (128 positions + halo, one bulk copy per chunk
+// plane as before) is re-laid by six copy warps into one slot per (tap, chunk) holding the positions ALREADY SHIFTED
+// by the tap, and ONE instruction with N = taps*Cin (<= 256) covers them all.  The replication stays inside shared
+// memory: doing it with shifted bulk copies would multiply the L2 traffic by the tap count.
+// A (dy) needs only Cout/8 real chunk slots: the instruction reads 16, the rest alias whatever follows in shared
+// memory and feed accumulator lanes >= Cout that nobody reads.
+// ---------------------------------------------------------------------------------------------
+constexpr int kWg2Threads = 256, kWg2Rep = 6;
+constexpr int kWg2AFull = 0, kWg2RawFull = 2, kWg2RawEmpty = 4, kWg2BFull = 6, kWg2MmaDone = 8, kWg2Acc = 10;
+
+__global__ void __launch_bounds__(kWg2Threads) wgrad_umma2_kernel(const __grid_constant__ WgradParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 128);
+  const int Cin = p.nchunks * 8, Cout = p.Cout;
+  const int tap0 = blockIdx.y * p.taps_per_cta;
+  const int ntap = min(p.taps_per_cta, p.ntaps - tap0);
+  const uint32_t chunk2k = kWgStage * 16u;
+  const uint32_t a_real = (uint32_t)(Cout / 8) * chunk2k;
+  const int SPb = kWgStage + p.halo_lo + p.halo_hi;
+  const uint32_t raw_chunk = (uint32_t)SPb * 16u;
+  const uint32_t raw_stage = ((uint32_t)(p.nsrc * p.nchunks) * raw_chunk + 127u) & ~127u;
+  const uint32_t b_stage = (uint32_t)(p.taps_per_cta * p.nchunks) * chunk2k;
+  uint8_t* a_slab = smem + kWgHeader;
+  uint8_t* raw = a_slab + 2 * a_real;
+  uint8_t* bexp = raw + 2 * raw_stage;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long f0 = (long long)blockIdx.x * p.slice;
+  const long long f1 = min(f0 + (long long)p.slice, (p.body + 15) / 16 * 16);
+  const int nstage = (int)((f1 - f0 + kWgStage - 1) / kWgStage);
+  uint32_t cols = 32;
+  while ((int)cols < ntap * Cin) cols <<= 1;
+
+  if (threadIdx.x == 0) {
+    ptx::mbar_init(bars + kWg2AFull + 0, 1), ptx::mbar_init(bars + kWg2AFull + 1, 1);
+    ptx::mbar_init(bars + kWg2RawFull + 0, 1), ptx::mbar_init(bars + kWg2RawFull + 1, 1);
+    ptx::mbar_init(bars + kWg2RawEmpty + 0, kWg2Rep), ptx::mbar_init(bars + kWg2RawEmpty + 1, kWg2Rep);
+    ptx::mbar_init(bars + kWg2BFull + 0, kWg2Rep), ptx::mbar_init(bars + kWg2BFull + 1, kWg2Rep);
+    ptx::mbar_init(bars + kWg2MmaDone + 0, 1), ptx::mbar_init(bars + kWg2MmaDone + 1, 1);
+    ptx::mbar_init(bars + kWg2Acc, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 1) ptx::tmem_alloc(tmem_slot, cols);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ---- producer: dy chunks -> A stage, input slab (tile + halo) -> raw stage ---------------------------------
+    if (ptx::elect_one()) {
+      for (int s = 0; s < nstage; ++s) {
+        const int b = s & 1;
+        if (s >= 2) {
+          ptx::mbar_wait(bars + kWg2MmaDone + b, ((s >> 1) - 1) & 1);   // A stage b consumed
+          ptx::mbar_wait(bars + kWg2RawEmpty + b, ((s >> 1) - 1) & 1);  // raw stage b re-laid
+        }
+        const long long fb = f0 + (long long)s * kWgStage;
+        ptx::mbar_arrive_expect_tx(bars + kWg2AFull + b, a_real);
+        for (int c = 0; c < Cout / 8; ++c)
+          ptx::bulk_g2s(a_slab + b * a_real + c * chunk2k, p.dy + (long long)c * p.dy_plane_bytes + fb * 16, chunk2k,
+                        bars + kWg2AFull + b);
+        ptx::mbar_arrive_expect_tx(bars + kWg2RawFull + b, (uint32_t)(p.nsrc * p.nchunks) * raw_chunk);
+        for (int sr = 0; sr < p.nsrc; ++sr)
+          for (int c = 0; c < p.nchunks; ++c)
+            ptx::bulk_g2s(raw + b * raw_stage + (size_t)(sr * p.nchunks + c) * raw_chunk,
+                          p.src[sr].base + (long long)c * p.src[sr].plane_bytes + (fb - p.halo_lo) * 16, raw_chunk,
+                          bars + kWg2RawFull + b);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ---- MMA issuer --------------------------------------------------------------------------------------------
+    if (ptx::elect_one()) {
+      // MN-major interleaved: LBO = distance between 8-position groups (128 B), SBO = distance between 8-channel chunks
+      const uint64_t ab_hi = ptx::umma_desc(0, 128u, chunk2k);
+      const uint32_t a16 = ptx::smem_u32(a_slab) >> 4, b16 = ptx::smem_u32(bexp) >> 4;
+      const int tpg = max(1, 256 / Cin), ngrp = (ntap + tpg - 1) / tpg;  // taps per instruction (N <= 256)
+      const uint32_t idesc_full = ptx::umma_idesc_bf16(128, min(tpg, ntap) * Cin, 1, 1);
+      const uint32_t idesc_last = ptx::umma_idesc_bf16(128, (ntap - (ngrp - 1) * tpg) * Cin, 1, 1);
+      uint32_t acc = 0u;
+      for (int s = 0; s < nstage; ++s) {
+        const int b = s & 1;
+        ptx::mbar_wait(bars + kWg2AFull + b, (s >> 1) & 1);
+        ptx::mbar_wait(bars + kWg2BFull + b, (s >> 1) & 1);
+        ptx::tc_fence_after();
+        const long long fb = f0 + (long long)s * kWgStage;
+        const int ksteps = (int)min((long long)(kWgStage / 16), (f1 - fb + 15) / 16);
+        for (int j = 0; j < ksteps; ++j) {
+          const uint32_t a_lo = a16 + (uint32_t)b * (a_real >> 4) + (uint32_t)j * 16u;
+          const uint32_t b_j = b16 + (uint32_t)b * (b_stage >> 4) + (uint32_t)(j * 16);
+          for (int gq = 0; gq < ngrp; ++gq)
+            ptx::umma_bf16(tmem_base + (uint32_t)(gq * tpg * Cin), ab_hi | a_lo,
+                           ab_hi | (b_j + (uint32_t)(gq * tpg * p.nchunks) * (chunk2k >> 4)),
+                           gq == ngrp - 1 ? idesc_last : idesc_full, acc);
+          acc = 1u;
+        }
+        ptx::umma_commit(bars + kWg2MmaDone + b);
+      }
+      ptx::umma_commit(bars + kWg2Acc);
+    }
+    __syncwarp();
+  } else {
+    // ---- copy warps: slot (tap, chunk) = the raw chunk plane shifted by the tap --------------------------------
+    const int tr = threadIdx.x - 64, nslot = ntap * p.nchunks;
+    for (int s = 0; s < nstage; ++s) {
+      const int b = s & 1;
+      ptx::mbar_wait(bars + kWg2RawFull + b, (s >> 1) & 1);
+      if (s >= 2) ptx::mbar_wait(bars + kWg2MmaDone + b, ((s >> 1) - 1) & 1);  // expanded stage b consumed
+      const uint8_t* rsrc = raw + b * raw_stage;
+      uint8_t* dst = bexp + b * b_stage;
+      for (int i = tr; i < nslot * (kWgStage / 2); i += kWg2Rep * 32) {   // two granules per thread and step
+        const int slot = i >> 6, pos = (i & 63) * 2;
+        const int t = slot / p.nchunks, c = slot - t * p.nchunks;
+        const ConvTapDev tp = p.tap[tap0 + t];
+        const uint4* sp = reinterpret_cast<const uint4*>(rsrc + (size_t)(tp.src * p.nchunks + c) * raw_chunk +
+                                                         (size_t)(p.halo_lo + tp.off + pos) * 16);
+        uint4* dp = reinterpret_cast<uint4*>(dst + (size_t)slot * chunk2k + (size_t)pos * 16);
+        const uint4 v0 = sp[0], v1 = sp[1];
+        dp[0] = v0, dp[1] = v1;
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> tensor-core reads
+      __syncwarp();
+      if (lane == 0) {
+        ptx::mbar_arrive(bars + kWg2BFull + b);
+        ptx::mbar_arrive(bars + kWg2RawEmpty + b);
+      }
+    }
+  }
+
+  // ---- epilogue: lane = output channel (row of D); columns = (tap, ci); the two warps of a lane quarter split the taps
+  ptx::mbar_wait(bars + kWg2Acc, 0);
+  ptx::tc_fence_after();
+  const int quarter = warp & 3, co = quarter * 32 + lane;
+  if (quarter * 32 < Cout) {
+    for (int t = warp >> 2; t < ntap; t += 2) {
+      for (int c0 = 0; c0 < Cin; c0 += 16) {
+        uint32_t r[16];
+        ptx::tmem_ld16_issue(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(t * Cin + c0), r);
+        ptx::tmem_wait16(r);
+        if (co < Cout && nstage > 0) {
+          float* dst = p.dw + ((size_t)(tap0 + t) * Cin + c0) * Cout + co;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) atomicAdd(dst + (size_t)j * Cout, __uint_as_float(r[j]));
+        }
+      }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem_base, cols);
+}
+
+// shared memory of wgrad_umma2_kernel; the A operand reads 32 KB from each A stage base whatever Cout is
+static size_t wgrad2_smem(const WgradParams& p, int taps_per_cta) {
+  const size_t a_real = (size_t)(p.Cout / 8) * kWgStage * 16;
+  const size_t raw_stage = ((size_t)(p.nsrc * p.nchunks) * (kWgStage + p.halo_lo + p.halo_hi) * 16 + 127) & ~(size_t)127;
+  const size_t b_stage = (size_t)taps_per_cta * p.nchunks * kWgStage * 16;
+  const size_t used = kWgHeader + 2 * a_real + 2 * raw_stage + 2 * b_stage;
+  return std::max(used, (size_t)kWgHeader + a_real + 16 * (size_t)kWgStage * 16);
+}
+
+static cudaError_t launch_wgrad_umma2(WgradParams p, cudaStream_t st, bool* handled) {
+  const int Cin = p.nchunks * 8;
+  *handled = false;
+  if (Cin > 64 || p.ntaps < 3) return cudaSuccess;
+  int lo = 0, hi = 0;
+  for (int t = 0; t < p.ntaps; ++t) lo = std::max(lo, -p.tap[t].off), hi = std::max(hi, p.tap[t].off);
+  p.halo_lo = lo, p.halo_hi = hi;
+  int tpc = std::min(p.ntaps, 512 / Cin);
+  while (tpc > 1 && wgrad2_smem(p, tpc) > 200 * 1024) --tpc;
+  if (wgrad2_smem(p, tpc) > 200 * 1024) return cudaSuccess;
+  const int ngroups = (p.ntaps + tpc - 1) / tpc;
+  p.taps_per_cta = (p.ntaps + ngroups - 1) / ngroups;
+  const size_t smem = wgrad2_smem(p, p.taps_per_cta);
+  int cols = 32;
+  while (cols < p.taps_per_cta * Cin) cols <<= 1;
+  const int resident = std::max(1, std::min({2, 512 / cols, (int)((size_t)227 * 1024 / (smem + 1024))}));
+  const long long body16 = (p.body + 15) / 16 * 16;
+  const long long want = std::max<long long>(1, (long long)148 * resident / ngroups);
+  const long long slice = std::max<long long>(512, (body16 + want - 1) / want);
+  p.slice = (int)((slice + kWgStage - 1) / kWgStage * kWgStage);
+  static size_t configured = 0;
+  if (smem > configured) {
+    cudaError_t e = cudaFuncSetAttribute(wgrad_umma2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    configured = smem;
+  }
+  dim3 grid((unsigned)((body16 + p.slice - 1) / p.slice), ngroups);
+  wgrad_umma2_kernel<<<grid, kWg2Threads, smem, st>>>(p);
+  *handled = true;
+  return cudaGetLastError();
+}
+
 static cudaError_t launch_wgrad_umma(WgradParams p, cudaStream_t st) {
   const int Cin = p.nchunks * 8;
   const int tg_max = std::max(1, 512 / Cin);
@@ -278,7 +475,19 @@ static cudaError_t launch_wgrad_umma(WgradParams p, cudaStream_t st) {
 cudaError_t launch_wgrad(const WgradParams& p, int precision, cudaStream_t st) {
   if (precision == 0) {
     const char* e = getenv("MTLDAS_WGRAD_CUDA_CORES");
-    if (!(e && e[0] == '1')) return launch_wgrad_umma(p, st);
+    if (!(e && e[0] == '1')) {
+      static int wide = -1;
+      if (wide < 0) {
+        const char* w = getenv("MTLDAS_WGRAD_WIDE");
+        wide = (w && w[0] == '0') ? 0 : 1;
+      }
+      if (wide) {
+        bool handled = false;
+        cudaError_t ce = launch_wgrad_umma2(p, st, &handled);
+        if (ce != cudaSuccess || handled) return ce;
+      }
+      return launch_wgrad_umma(p, st);
+    }
     return launch_wgrad_t<__nv_bfloat16>(p, st);
   }
   return launch_wgrad_t<float>(p, st);
