@@ -255,13 +255,14 @@ __global__ void __launch_bounds__(128) wgrad_umma_kernel(const __grid_constant__
 // memory and feed accumulator lanes >= Cout that nobody reads.
 // ---------------------------------------------------------------------------------------------
 constexpr int kWg2Threads = 256, kWg2Rep = 6;
-constexpr int kWg2AFull = 0, kWg2RawFull = 2, kWg2RawEmpty = 4, kWg2BFull = 6, kWg2MmaDone = 8, kWg2Acc = 10;
+constexpr int kWg2Ring = 4;  // max stages of the dy / raw-slab ring (the bulk-copy latency is ~4 stages of MMA work)
+constexpr int kWg2AFull = 0, kWg2RawFull = 4, kWg2RawEmpty = 8, kWg2AEmpty = 12, kWg2BFull = 16, kWg2MmaDone = 18, kWg2Acc = 20;
 
 __global__ void __launch_bounds__(kWg2Threads) wgrad_umma2_kernel(const __grid_constant__ WgradParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 128);
-  const int Cin = p.nchunks * 8, Cout = p.Cout;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 200);
+  const int Cin = p.nchunks * 8, Cout = p.Cout, NR = p.nring;
   const int tap0 = blockIdx.y * p.taps_per_cta;
   const int ntap = min(p.taps_per_cta, p.ntaps - tap0);
   const uint32_t chunk2k = kWgStage * 16u;
@@ -271,8 +272,8 @@ __global__ void __launch_bounds__(kWg2Threads) wgrad_umma2_kernel(const __grid_c
   const uint32_t raw_stage = ((uint32_t)(p.nsrc * p.nchunks) * raw_chunk + 127u) & ~127u;
   const uint32_t b_stage = (uint32_t)(p.taps_per_cta * p.nchunks) * chunk2k;
   uint8_t* a_slab = smem + kWgHeader;
-  uint8_t* raw = a_slab + 2 * a_real;
-  uint8_t* bexp = raw + 2 * raw_stage;
+  uint8_t* raw = a_slab + NR * a_real;
+  uint8_t* bexp = raw + NR * raw_stage;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long f0 = (long long)blockIdx.x * p.slice;
   const long long f1 = min(f0 + (long long)p.slice, (p.body + 15) / 16 * 16);
@@ -281,9 +282,10 @@ __global__ void __launch_bounds__(kWg2Threads) wgrad_umma2_kernel(const __grid_c
   while ((int)cols < ntap * Cin) cols <<= 1;
 
   if (threadIdx.x == 0) {
-    ptx::mbar_init(bars + kWg2AFull + 0, 1), ptx::mbar_init(bars + kWg2AFull + 1, 1);
-    ptx::mbar_init(bars + kWg2RawFull + 0, 1), ptx::mbar_init(bars + kWg2RawFull + 1, 1);
-    ptx::mbar_init(bars + kWg2RawEmpty + 0, kWg2Rep), ptx::mbar_init(bars + kWg2RawEmpty + 1, kWg2Rep);
+    for (int i = 0; i < kWg2Ring; ++i) {
+      ptx::mbar_init(bars + kWg2AFull + i, 1), ptx::mbar_init(bars + kWg2RawFull + i, 1);
+      ptx::mbar_init(bars + kWg2RawEmpty + i, kWg2Rep), ptx::mbar_init(bars + kWg2AEmpty + i, 1);
+    }
     ptx::mbar_init(bars + kWg2BFull + 0, kWg2Rep), ptx::mbar_init(bars + kWg2BFull + 1, kWg2Rep);
     ptx::mbar_init(bars + kWg2MmaDone + 0, 1), ptx::mbar_init(bars + kWg2MmaDone + 1, 1);
     ptx::mbar_init(bars + kWg2Acc, 1);
@@ -299,10 +301,10 @@ __global__ void __launch_bounds__(kWg2Threads) wgrad_umma2_kernel(const __grid_c
     // ---- producer: dy chunks -> A stage, input slab (tile + halo) -> raw stage ---------------------------------
     if (ptx::elect_one()) {
       for (int s = 0; s < nstage; ++s) {
-        const int b = s & 1;
-        if (s >= 2) {
-          ptx::mbar_wait(bars + kWg2MmaDone + b, ((s >> 1) - 1) & 1);   // A stage b consumed
-          ptx::mbar_wait(bars + kWg2RawEmpty + b, ((s >> 1) - 1) & 1);  // raw stage b re-laid
+        const int b = s % NR;
+        if (s >= NR) {
+          ptx::mbar_wait(bars + kWg2AEmpty + b, ((s / NR) - 1) & 1);    // A stage b consumed
+          ptx::mbar_wait(bars + kWg2RawEmpty + b, ((s / NR) - 1) & 1);  // raw stage b re-laid
         }
         const long long fb = f0 + (long long)s * kWgStage;
         ptx::mbar_arrive_expect_tx(bars + kWg2AFull + b, a_real);
@@ -329,14 +331,14 @@ __global__ void __launch_bounds__(kWg2Threads) wgrad_umma2_kernel(const __grid_c
       const uint32_t idesc_last = ptx::umma_idesc_bf16(128, (ntap - (ngrp - 1) * tpg) * Cin, 1, 1);
       uint32_t acc = 0u;
       for (int s = 0; s < nstage; ++s) {
-        const int b = s & 1;
-        ptx::mbar_wait(bars + kWg2AFull + b, (s >> 1) & 1);
+        const int b = s & 1, ra = s % NR;
+        ptx::mbar_wait(bars + kWg2AFull + ra, (s / NR) & 1);
         ptx::mbar_wait(bars + kWg2BFull + b, (s >> 1) & 1);
         ptx::tc_fence_after();
         const long long fb = f0 + (long long)s * kWgStage;
         const int ksteps = (int)min((long long)(kWgStage / 16), (f1 - fb + 15) / 16);
-        for (int j = 0; j < ksteps; ++j) {
-          const uint32_t a_lo = a16 + (uint32_t)b * (a_real >> 4) + (uint32_t)j * 16u;
+        for (int j = 0; j < ksteps && !(p.dbg_flags & 2); ++j) {
+          const uint32_t a_lo = a16 + (uint32_t)ra * (a_real >> 4) + (uint32_t)j * 16u;
           const uint32_t b_j = b16 + (uint32_t)b * (b_stage >> 4) + (uint32_t)(j * 16);
           for (int gq = 0; gq < ngrp; ++gq)
             ptx::umma_bf16(tmem_base + (uint32_t)(gq * tpg * Cin), ab_hi | a_lo,
@@ -344,6 +346,7 @@ __global__ void __launch_bounds__(kWg2Threads) wgrad_umma2_kernel(const __grid_c
                            gq == ngrp - 1 ? idesc_last : idesc_full, acc);
           acc = 1u;
         }
+        ptx::umma_commit(bars + kWg2AEmpty + ra);
         ptx::umma_commit(bars + kWg2MmaDone + b);
       }
       ptx::umma_commit(bars + kWg2Acc);
@@ -353,12 +356,12 @@ __global__ void __launch_bounds__(kWg2Threads) wgrad_umma2_kernel(const __grid_c
     // ---- copy warps: slot (tap, chunk) = the raw chunk plane shifted by the tap --------------------------------
     const int tr = threadIdx.x - 64, nslot = ntap * p.nchunks;
     for (int s = 0; s < nstage; ++s) {
-      const int b = s & 1;
-      ptx::mbar_wait(bars + kWg2RawFull + b, (s >> 1) & 1);
+      const int b = s & 1, rr = s % NR;
+      ptx::mbar_wait(bars + kWg2RawFull + rr, (s / NR) & 1);
       if (s >= 2) ptx::mbar_wait(bars + kWg2MmaDone + b, ((s >> 1) - 1) & 1);  // expanded stage b consumed
-      const uint8_t* rsrc = raw + b * raw_stage;
+      const uint8_t* rsrc = raw + rr * raw_stage;
       uint8_t* dst = bexp + b * b_stage;
-      for (int i = tr; i < nslot * (kWgStage / 2); i += kWg2Rep * 32) {   // two granules per thread and step
+      for (int i = tr; i < nslot * (kWgStage / 2) && !(p.dbg_flags & 1); i += kWg2Rep * 32) {   // two granules per thread and step
         const int slot = i >> 6, pos = (i & 63) * 2;
         const int t = slot / p.nchunks, c = slot - t * p.nchunks;
         const ConvTapDev tp = p.tap[tap0 + t];
@@ -372,7 +375,7 @@ __global__ void __launch_bounds__(kWg2Threads) wgrad_umma2_kernel(const __grid_c
       __syncwarp();
       if (lane == 0) {
         ptx::mbar_arrive(bars + kWg2BFull + b);
-        ptx::mbar_arrive(bars + kWg2RawEmpty + b);
+        ptx::mbar_arrive(bars + kWg2RawEmpty + rr);
       }
     }
   }
@@ -401,12 +404,12 @@ __global__ void __launch_bounds__(kWg2Threads) wgrad_umma2_kernel(const __grid_c
 }
 
 // shared memory of wgrad_umma2_kernel; the A operand reads 32 KB from each A stage base whatever Cout is
-static size_t wgrad2_smem(const WgradParams& p, int taps_per_cta) {
+static size_t wgrad2_smem(const WgradParams& p, int taps_per_cta, int nring) {
   const size_t a_real = (size_t)(p.Cout / 8) * kWgStage * 16;
   const size_t raw_stage = ((size_t)(p.nsrc * p.nchunks) * (kWgStage + p.halo_lo + p.halo_hi) * 16 + 127) & ~(size_t)127;
   const size_t b_stage = (size_t)taps_per_cta * p.nchunks * kWgStage * 16;
-  const size_t used = kWgHeader + 2 * a_real + 2 * raw_stage + 2 * b_stage;
-  return std::max(used, (size_t)kWgHeader + a_real + 16 * (size_t)kWgStage * 16);
+  const size_t used = kWgHeader + nring * (a_real + raw_stage) + 2 * b_stage;
+  return std::max(used, (size_t)kWgHeader + (size_t)(nring - 1) * a_real + 16 * (size_t)kWgStage * 16);
 }
 
 static cudaError_t launch_wgrad_umma2(WgradParams p, cudaStream_t st, bool* handled) {
@@ -417,11 +420,23 @@ static cudaError_t launch_wgrad_umma2(WgradParams p, cudaStream_t st, bool* hand
   for (int t = 0; t < p.ntaps; ++t) lo = std::max(lo, -p.tap[t].off), hi = std::max(hi, p.tap[t].off);
   p.halo_lo = lo, p.halo_hi = hi;
   int tpc = std::min(p.ntaps, 512 / Cin);
-  while (tpc > 1 && wgrad2_smem(p, tpc) > 200 * 1024) --tpc;
-  if (wgrad2_smem(p, tpc) > 200 * 1024) return cudaSuccess;
+  while (tpc > 1 && wgrad2_smem(p, tpc, 2) > 200 * 1024) --tpc;
+  if (wgrad2_smem(p, tpc, 2) > 200 * 1024) return cudaSuccess;
   const int ngroups = (p.ntaps + tpc - 1) / tpc;
   p.taps_per_cta = (p.ntaps + ngroups - 1) / ngroups;
-  const size_t smem = wgrad2_smem(p, p.taps_per_cta);
+  {
+    const char* d = getenv("MTLDAS_WG2_DEBUG");
+    p.dbg_flags = d ? atoi(d) : 0;
+  }
+  // deepest ring that still lets two CTAs share an SM (measured: two CTAs with a 2-stage ring beat one CTA with
+  // four stages, 50 vs 59 us on the 16-channel layers at batch 256); otherwise the deepest that fits
+  p.nring = 0;
+  for (int r = kWg2Ring; r >= 2 && !p.nring; --r)
+    if (wgrad2_smem(p, p.taps_per_cta, r) <= 113 * 1024) p.nring = r;
+  for (int r = kWg2Ring; r >= 2 && !p.nring; --r)
+    if (wgrad2_smem(p, p.taps_per_cta, r) <= 220 * 1024) p.nring = r;
+  if (!p.nring) return cudaSuccess;
+  const size_t smem = wgrad2_smem(p, p.taps_per_cta, p.nring);
   int cols = 32;
   while (cols < p.taps_per_cta * Cin) cols <<= 1;
   const int resident = std::max(1, std::min({2, 512 / cols, (int)((size_t)227 * 1024 / (smem + 1024))}));

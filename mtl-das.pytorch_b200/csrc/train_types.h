@@ -101,6 +101,8 @@ struct WgradParams {     // dW[tap][k][cout] += sum_pos zin[pos + off_tap][k] * 
   int slice;                 // positions per CTA
   int nsrc;                  // sources referenced by the taps
   int taps_per_cta, halo_lo, halo_hi;  // tensor-core kernel only (filled by the launcher)
+  int nring;                 // wide-N kernel: stages of the dy / input-slab ring (2..4)
+  int dbg_flags;             // diagnostics (MTLDAS_WG2_DEBUG): 1 = skip the re-lay copies, 2 = skip the MMAs (results invalid)
 };
 
 struct HeadBwdParams {   // d(log_softmax(group mean(GAP(a4)))) -> d a4
