@@ -166,6 +166,17 @@ MTLDAS_API int mtldas_train_last_launch_count(const mtldas_train* t);
 MTLDAS_API int mtldas_train_read_tensor(mtldas_train* t, const char* name, int nb, float* dev_out_nchw, void* stream);
 MTLDAS_API size_t mtldas_train_describe(const mtldas_train* t, char* buf, size_t cap);
 
+/* joint loss of the task heads and its gradient ----------------------------------------------------
+ * Replaces `criterion(pred1, y1) + criterion(pred2, y2)` with criterion = nn.NLLLoss() (utils.py:139,361,367) and
+ * its autograd: *dev_loss = -(1/n) sum_i logp0[i, y0[i]] - (1/n) sum_i logp1[i, y1[i]];
+ * dev_dlogp_t[i, j] = -(1/n) [j == y_t[i]] (dense [n, classes_t] fp32, the upstream gradients mtldas_train_backward
+ * takes).  Labels are int64 as after `.long()`.  The second task (logp1 / y1 / dlogp1) may be NULL for the
+ * single-task nets; either dlogp may be NULL (loss only).  dev_status (int, may be NULL) is set to 1 when a label
+ * lies outside [0, classes) -- torch raises there; the caller checks it where it would have synchronised anyway. */
+MTLDAS_API int mtldas_nll_loss(const float* dev_logp0, const long long* dev_y0, int classes0, float* dev_dlogp0,
+                               const float* dev_logp1, const long long* dev_y1, int classes1, float* dev_dlogp1,
+                               int n, float* dev_loss, int* dev_status, void* stream);
+
 /* streaming inference over a large DAS array --------------------------------------------------------
  * No counterpart in the reference (its README only motivates it): cuts the [100 x 250] patches the
  * network expects (utils.py:128) out of dev_array [n_channels, n_time] fp32 row-major: window wi covers fibre

@@ -6,6 +6,7 @@
 #include "kernels.h"
 #include "plan.h"
 #include "train.h"
+#include "train_kernels.h"
 
 using namespace mtldas;
 
@@ -202,6 +203,22 @@ int mtldas_conv2d_nchw(const float* dev_x, const float* dev_x2, const float* dev
   const char* sw = getenv("MTLDAS_UMMA_SWAP_DESC");
   return single_conv(dev_x, dev_x2, dev_weight, dev_bias, dev_aux, dev_out, n, cin, cin2, h, w, cout, ksize, stride,
                      epilogue, precision, aux_phase_split, (sw && sw[0] == '1') ? 1 : 0);
+}
+
+int mtldas_nll_loss(const float* dev_logp0, const long long* dev_y0, int classes0, float* dev_dlogp0,
+                    const float* dev_logp1, const long long* dev_y1, int classes1, float* dev_dlogp1, int n,
+                    float* dev_loss, int* dev_status, void* stream) {
+  if (!dev_logp0 || !dev_y0 || classes0 < 1 || n < 1 || !dev_loss || (dev_logp1 && (!dev_y1 || classes1 < 1))) {
+    set_error("nll_loss: bad arguments (n %d, classes %d / %d)", n, classes0, classes1);
+    return MTLDAS_ERR_ARG;
+  }
+  cudaError_t e = launch_nll_loss(dev_logp0, dev_y0, classes0, dev_dlogp0, dev_logp1, dev_y1, classes1, dev_dlogp1, n,
+                                  dev_loss, dev_status, (cudaStream_t)stream);
+  if (e != cudaSuccess) {
+    set_error("nll_loss: %s", cudaGetErrorString(e));
+    return MTLDAS_ERR_CUDA;
+  }
+  return 0;
 }
 
 int mtldas_window_gather(const float* dev_array, long long n_channels, long long n_time, int first_channel,

@@ -509,6 +509,48 @@ cudaError_t launch_wgrad(const WgradParams& p, int precision, cudaStream_t st) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// joint NLL loss of the task heads and its gradient (utils.py:139,361,367: NLLLoss(mean) per task, summed):
+//   L = -(1/n) sum_i logp_t[i, y_t[i]] summed over the tasks;  dL/dlogp_t[i, j] = -(1/n) [j == y_t[i]]
+// One block: the loss is a deterministic tree sum; the gradients are written densely (they feed head_bwd).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) nll_loss_kernel(const float* logp0, const long long* y0, int c0, float* d0,
+                                                       const float* logp1, const long long* y1, int c1, float* d1,
+                                                       int n, float* loss, int* bad_label) {
+  __shared__ float sh[8];
+  const float k = 1.f / (float)n;
+  float acc = 0.f;
+  for (int t = 0; t < 2; ++t) {
+    const float* lp = t ? logp1 : logp0;
+    const long long* y = t ? y1 : y0;
+    float* d = t ? d1 : d0;
+    const int c = t ? c1 : c0;
+    if (!lp) continue;
+    for (int i = threadIdx.x; i < n * c; i += 256) {
+      const int row = i / c, col = i - row * c;
+      const long long lab = y[row];
+      const bool hit = lab == col;
+      if (d) d[i] = hit ? -k : 0.f;
+      if (hit) acc -= lp[i] * k;
+      if (bad_label && col == 0 && (lab < 0 || lab >= c)) *bad_label = 1;
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float s = 0.f;
+    for (int w = 0; w < 8; ++w) s += sh[w];
+    *loss = s;
+  }
+}
+
+cudaError_t launch_nll_loss(const float* logp0, const long long* y0, int c0, float* d0, const float* logp1,
+                            const long long* y1, int c1, float* d1, int n, float* loss, int* bad_label, cudaStream_t st) {
+  nll_loss_kernel<<<1, 256, 0, st>>>(logp0, y0, c0, d0, logp1, y1, c1, d1, n, loss, bad_label);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
 // head backward: d a4[n,c,h,w] = dz[n, c / group] / (H*W*group), dz = dlogp - softmax * sum(dlogp)
 // one block per sample, thread t: chunk t%16, positions t/16, t/16+8, ...
 // ---------------------------------------------------------------------------------------------

@@ -7,7 +7,7 @@ modelB_singleTask.py:53-178) while their compute runs in hand-written CUDA kerne
 There is no CPU fallback: without the built library and a B200 the compute calls raise.
 """
 from ._lib import lib, MtldasError, library_path  # noqa: F401
-from .engine import EvalPlan, TrainPlan, conv2d_nchw, conv2d_nchw_static, umma_selftest  # noqa: F401
+from .engine import EvalPlan, TrainPlan, conv2d_nchw, conv2d_nchw_static, nll_loss, umma_selftest  # noqa: F401
 from .nets import MTL_Net, Single_Task_Net  # noqa: F401
 from . import synth  # noqa: F401
 

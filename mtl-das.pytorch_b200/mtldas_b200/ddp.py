@@ -66,20 +66,18 @@ class DataParallelTrainer:
         self.module, self.optimizer, self.group = module, optimizer, group
         self.params = [p for _, p in module.named_parameters()]
         self._flat = None
-        self._idx = None
+        self._loss_bufs = None
 
     def step(self, x_local: torch.Tensor, labels_local: Sequence[torch.Tensor]):
         """x_local / labels_local: this rank's shard. Returns the local loss (python float is NOT taken here)."""
+        from .engine import nll_loss
         m = self.module
         plan = m._train_plan(x_local.device, x_local.shape[0])
         state = [v.detach() for v in m.state_dict(keep_vars=True).values()]
         outs = plan.forward(state, x_local)
-        n = x_local.shape[0]
-        douts, loss = [], 0.0
-        for o, y in zip(outs, labels_local):      # NLLLoss (mean) per task, summed -- utils.py:139,361,367
-            onehot = torch.nn.functional.one_hot(y.long(), o.shape[1]).to(o.dtype)
-            loss = loss - (o * onehot).sum() / n
-            douts.append(onehot * (-1.0 / n))
+        # NLLLoss (mean) per task, summed, and its gradient: one fused launch (utils.py:139,361,367)
+        self._loss_bufs = nll_loss(list(outs), [y.long().contiguous() for y in labels_local], out=self._loss_bufs)
+        loss, douts = self._loss_bufs
         if self._flat is None or self._flat.device != x_local.device:
             self._flat = torch.empty(plan.n_params, dtype=torch.float32, device=x_local.device)
             for p, g in zip(self.params, unflatten_like(self._flat, self.params)):

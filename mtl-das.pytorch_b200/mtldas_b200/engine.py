@@ -14,12 +14,19 @@ def _stream_ptr(device):
     return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
+_OK_DEVICES = set()
+
+
 def _require_b200(device):
+    key = str(device)
+    if key in _OK_DEVICES:          # the device query behind mtldas_device_ok costs tens of milliseconds
+        return
     if not torch.cuda.is_available():
         raise MtldasError("mtldas_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
     with torch.cuda.device(device):
         if not lib.mtldas_device_ok():
             raise MtldasError("mtldas_b200 kernels are built for sm_100a (B200) only")
+    _OK_DEVICES.add(key)
 
 
 class EvalPlan:
@@ -258,6 +265,35 @@ def conv2d_nchw_static(x, weight, bias=None, aux=None, x2=None, stride=1, epilog
                                             k, stride, epilogue, PRECISIONS[precision], int(aux_phase_split),
                                             _stream_ptr(x.device)), "conv2d_nchw_static")
     return out
+
+
+def nll_loss(logps, labels, want_grads=True, status=None, out=None):
+    """Joint NLLLoss(mean) of the task heads (utils.py:139,361,367) and its gradient through mtldas_nll_loss.
+
+    logps: one or two fp32 [n, classes] log-prob tensors; labels: matching int64 [n] tensors.
+    Returns (loss [1] fp32 on the device, [d loss / d logp per task] or None).  Asynchronous on the current stream;
+    `status` (int32 [1], optional) is set to 1 by the kernel when a label is out of range; `out` = (loss, grads) from an
+    earlier call reuses those buffers (stable addresses keep the training plan's CUDA graph replaying)."""
+    dev = logps[0].device
+    _require_b200(dev)
+    n = logps[0].shape[0]
+    for lp, y in zip(logps, labels):
+        if not (lp.is_contiguous() and lp.dtype == torch.float32 and y.is_contiguous() and y.dtype == torch.int64
+                and lp.shape[0] == n and y.shape[0] == n and y.device == dev and lp.device == dev):
+            raise MtldasError("nll_loss needs contiguous fp32 [n, classes] log-probs and int64 [n] labels on one device")
+    if out is not None and out[1] is not None and all(g.shape == lp.shape and g.device == dev for g, lp in zip(out[1], logps)):
+        loss, grads = out
+    else:
+        loss = torch.empty(1, dtype=torch.float32, device=dev)
+        grads = [torch.empty_like(lp) for lp in logps] if want_grads else None
+    p = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None  # noqa: E731
+    two = len(logps) > 1
+    with torch.cuda.device(dev):
+        check(lib.mtldas_nll_loss(p(logps[0]), p(labels[0]), logps[0].shape[1], p(grads[0]) if grads else None,
+                                  p(logps[1]) if two else None, p(labels[1]) if two else None,
+                                  logps[1].shape[1] if two else 0, p(grads[1]) if (grads and two) else None,
+                                  n, p(loss), p(status), _stream_ptr(dev)), "nll_loss")
+    return loss, grads
 
 
 def umma_selftest(n_cols=16, row_shift=0, swap=0):

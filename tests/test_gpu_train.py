@@ -174,3 +174,30 @@ def test_bf16_training_loss_tracks_fp32_reference():
     print("bf16 loss curve", [round(v, 4) for v in ours]); print("fp32 ref curve ", [round(v, 4) for v in theirs])
     assert ours[-1] < ours[0] and theirs[-1] < theirs[0]
     assert max(abs(a - b) for a, b in zip(ours, theirs)) <= 0.05 * max(theirs)
+
+
+def test_nll_loss_matches_torch():
+    """mtldas_nll_loss = criterion(pred1, y1) + criterion(pred2, y2) with nn.NLLLoss() (utils.py:139,361,367) and its
+    autograd; integer bookkeeping (which entry gets -1/n) is exact, the sum is fp32."""
+    from mtldas_b200 import nll_loss
+    g = torch.Generator().manual_seed(7)
+    for n in (1, 5, 256, 1000):
+        lp0 = torch.log_softmax(torch.randn(n, 16, generator=g), 1).cuda().requires_grad_(True)
+        lp1 = torch.log_softmax(torch.randn(n, 2, generator=g), 1).cuda().requires_grad_(True)
+        y0 = torch.randint(0, 16, (n,), generator=g).cuda()
+        y1 = torch.randint(0, 2, (n,), generator=g).cuda()
+        crit = torch.nn.NLLLoss()
+        ref = crit(lp0, y0) + crit(lp1, y1)
+        ref.backward()
+        status = torch.zeros(1, dtype=torch.int32, device="cuda")
+        loss, grads = nll_loss([lp0.detach(), lp1.detach()], [y0, y1], status=status)
+        assert abs(float(loss) - float(ref)) <= 1e-5 * max(1.0, abs(float(ref)))
+        assert torch.equal(grads[0] != 0, lp0.grad != 0) and torch.equal(grads[1] != 0, lp1.grad != 0)
+        assert float((grads[0] - lp0.grad).abs().max()) <= 1e-7 and float((grads[1] - lp1.grad).abs().max()) <= 1e-7
+        assert int(status) == 0
+        # single task (model B) and loss only
+        l1, g1 = nll_loss([lp0.detach()], [y0], want_grads=False)
+        assert g1 is None and abs(float(l1) - float(crit(lp0, y0))) <= 1e-5
+    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+    nll_loss([lp0.detach()], [torch.full((n,), 16, device="cuda")], status=bad)
+    assert int(bad) == 1      # torch raises on an out-of-range label; the kernel reports it
