@@ -503,7 +503,7 @@ static int train_forward_eager(TrainPlan& tp, const void* const* state, const fl
       CK(launch_stem(q, p.precision, st));
     } else if (op.kind == TOP_CONV) {
       ConvParams q = p.conv_params(p.convs[op.a], nb);
-      CK(launch_conv(q, p.precision, st));
+      CK(launch_conv(q, p.precision, st, p.use_pdl != 0));
     } else if (op.kind == TOP_FINAL) {
       continue;  // folded into the statistics kernel
     } else if (op.kind == TOP_EW) {
@@ -654,7 +654,7 @@ static int train_backward_eager(TrainPlan& tp, const void* const* state, const f
       }
     } else if (op.kind == TOP_DGRAD) {
       ConvParams q = p.conv_params(p.convs[tp.dgrads[op.a].conv], nb);
-      CK(launch_conv(q, p.precision, st));
+      CK(launch_conv(q, p.precision, st, p.use_pdl != 0));
     } else if (op.kind == TOP_STEMWG) {
       const TensorInfo& t = p.tensors[tp.dy_stem];
       StemWgradParams q{};

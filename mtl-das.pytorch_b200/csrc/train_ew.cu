@@ -17,6 +17,7 @@
 #include <cstdlib>
 
 #include "gran.cuh"
+#include "ptx.cuh"
 #include "train_kernels.h"
 
 namespace mtldas {
@@ -199,6 +200,9 @@ __global__ void __launch_bounds__(kEwThreads) ew_fwd_kernel(const __grid_constan
   constexpr int G = Gran<T>::bytes;
   __shared__ float sh[kEwThreads / 32][8];
   __shared__ float aff[kMaxTasks][4][8];  // per task: scale, shift, scale2, shift2 of the chunk's 8 channels
+  // programmatic dependent launch: let the next kernel's CTAs get scheduled, then wait for everything before us
+  ptx::pdl_launch_dependents();
+  ptx::pdl_grid_wait();
   const int c = blockIdx.y;
   const int stride = gridDim.x * kEwThreads;
   const int first = blockIdx.x * kEwThreads + threadIdx.x;
@@ -321,13 +325,30 @@ __global__ void __launch_bounds__(kEwThreads) ew_fwd_kernel(const __grid_constan
   }
 }
 
+
+// launch with the programmatic-stream-serialization attribute (the kernels above call griddepcontrol.wait first)
+template <typename K>
+static cudaError_t launch_pdl(K kernel, dim3 grid, const EwParams& p, cudaStream_t st) {
+  static int use_pdl = -1;
+  if (use_pdl < 0) {
+    const char* e = getenv("MTLDAS_NO_PDL");
+    use_pdl = (e && e[0] == '1') ? 0 : 1;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid, cfg.blockDim = dim3(kEwThreads), cfg.dynamicSmemBytes = 0, cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr, cfg.numAttrs = use_pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, p);
+}
+
 template <typename T, int MODE>
 static cudaError_t launch_ew_fwd_m(const EwParams& p, cudaStream_t st) {
   static unsigned per_sm_cache = 0;  // occupancy of this instantiation
   (void)per_sm_cache;
   dim3 grid(resident_blocks_per_chunk(ew_fwd_kernel<T, MODE>, std::max(p.body, p.body_full), p.nchunks), p.nchunks);
-  ew_fwd_kernel<T, MODE><<<grid, kEwThreads, 0, st>>>(p);
-  return cudaGetLastError();
+  return launch_pdl(ew_fwd_kernel<T, MODE>, grid, p, st);
 }
 
 template <typename T>
@@ -419,6 +440,8 @@ template <typename T, int MODE>
 __global__ void __launch_bounds__(kEwThreads, 2) ew_bwd_kernel(const __grid_constant__ EwParams p) {
   __shared__ float sh[kEwThreads / 32][8];
   constexpr int G = Gran<T>::bytes;
+  ptx::pdl_launch_dependents();
+  ptx::pdl_grid_wait();
   const int c = blockIdx.y;
   const int stride = gridDim.x * kEwThreads;
   const int body = (int)p.body;
@@ -724,8 +747,7 @@ __global__ void __launch_bounds__(kEwThreads, 2) ew_bwd_kernel(const __grid_cons
 template <typename T, int MODE>
 static cudaError_t launch_ew_bwd_m(const EwParams& p, cudaStream_t st) {
   dim3 grid(resident_blocks_per_chunk(ew_bwd_kernel<T, MODE>, std::max(p.body, p.body_full), p.nchunks), p.nchunks);
-  ew_bwd_kernel<T, MODE><<<grid, kEwThreads, 0, st>>>(p);
-  return cudaGetLastError();
+  return launch_pdl(ew_bwd_kernel<T, MODE>, grid, p, st);
 }
 
 template <typename T>
