@@ -62,8 +62,8 @@ struct OpTimer {
   void report(const char* what) {
     if (!on) return;
     cudaStreamSynchronize(st);
-    static const char* names[] = {"stem", "conv", "stats", "finalize", "ew_fwd", "head", "head_bwd", "ew_bwd",
-                                  "bn_grad", "wgrad+unpack", "dgrad", "stem_wgrad"};
+    static const char* names[] = {"stem", "conv", "bn+act", "head", "head_bwd", "bn+act_bwd", "wgrad", "dgrad",
+                                  "stem_wgrad", "", "", ""};
     float tot[12] = {0};
     int cnt[12] = {0};
     for (size_t i = 0; i < kind.size(); ++i) {
@@ -149,8 +149,6 @@ TrainPlan* build_train_plan(int kind, int batch, int precision) {
     tp.ew_stem = 0;
   }
   tp.fwd.push_back({TOP_STEM, 0, 0});
-  tp.fwd.push_back({TOP_STATS, tp.bn_stem, 0});
-  tp.fwd.push_back({TOP_FINAL, tp.bn_stem, 0});
   tp.fwd.push_back({TOP_EW, tp.ew_stem, 0});
 
   // ---- forward program from the inference program -----------------------------------------------------
@@ -181,8 +179,6 @@ TrainPlan* build_train_plan(int kind, int batch, int precision) {
     p.convs.push_back(f);
     tp.fconv_of[ci] = (int)p.convs.size() - 1;
     tp.fwd.push_back({TOP_CONV, tp.fconv_of[ci], 0});
-    tp.fwd.push_back({TOP_STATS, bn, 0});
-    tp.fwd.push_back({TOP_FINAL, bn, 0});
     if (inf.epi == EPI_NONE) continue;  // shortcut conv: its BatchNorm is applied by the consumer (EW_ADD_RELU_SC)
     TrainPlan::EwHost e{};
     e.conv = ci, e.y = y, e.bn = bn, e.y2 = e.bn2 = e.aux = -1, e.out = out_t;
@@ -302,8 +298,6 @@ TrainPlan* build_train_plan(int kind, int batch, int precision) {
       }
       if (e.mode == EW_ADD_RELU_SC) e.dy2 = tp.dy_of[e.sc_conv];
       tp.bwd.push_back({TOP_EWB, tp.ew_of[ci], 0});
-      tp.bwd.push_back({TOP_BNGRAD, tp.bn_of[ci], 0});
-      if (e.mode == EW_ADD_RELU_SC) tp.bwd.push_back({TOP_BNGRAD, tp.bn_of[e.sc_conv], 0});
     }
     // weight gradients (one per group)
     for (int g = 0; g < inf.ngroups; ++g) {
@@ -326,7 +320,6 @@ TrainPlan* build_train_plan(int kind, int batch, int precision) {
   tp.ews[tp.ew_stem].dz = grad_of(tp, p.stem_out), tp.ews[tp.ew_stem].dy = tp.dy_stem;
   tp.ews[tp.ew_stem].dy2 = tp.ews[tp.ew_stem].daux = -1;
   tp.bwd.push_back({TOP_EWB, tp.ew_stem, 0});
-  tp.bwd.push_back({TOP_BNGRAD, tp.bn_stem, 0});
   tp.bwd.push_back({TOP_STEMWG, 0, 0});
   (void)T;
 
@@ -489,7 +482,6 @@ static int train_forward_eager(TrainPlan& tp, const void* const* state, const fl
   float* logp1 = logp0 + (size_t)p.mb * 16;
   OpTimer timer(st);
   for (auto& op : tp.fwd) {
-    if (op.kind == TOP_FINAL || op.kind == TOP_STATS) continue;  // inside the fused BatchNorm + activation kernel
     timer.begin(op.kind);
     if (op.kind == TOP_STEM) {
       const TensorInfo& t = p.tensors[tp.y_stem];
@@ -504,8 +496,6 @@ static int train_forward_eager(TrainPlan& tp, const void* const* state, const fl
     } else if (op.kind == TOP_CONV) {
       ConvParams q = p.conv_params(p.convs[op.a], nb);
       CK(launch_conv(q, p.precision, st, p.use_pdl != 0));
-    } else if (op.kind == TOP_FINAL) {
-      continue;  // folded into the statistics kernel
     } else if (op.kind == TOP_EW) {
       const TrainPlan::EwHost& e = tp.ews[op.a];
       EwParams q = ew_params(tp, e, nb);
@@ -577,7 +567,6 @@ static int train_backward_eager(TrainPlan& tp, const void* const* state, const f
     return true;
   };
   for (auto& op : tp.bwd) {
-    if (op.kind == TOP_BNGRAD) continue;  // written by the elementwise backward's second pass
     timer.begin(op.kind);
     if (op.kind == TOP_HEADBWD) {
       const HeadOpHost& h = p.heads[op.a];
@@ -613,16 +602,6 @@ static int train_backward_eager(TrainPlan& tp, const void* const* state, const f
       }
       q.sync = reinterpret_cast<unsigned int*>(p.ws + tp.bns[e.bn].red_off + (size_t)tp.bns[e.bn].C * 2 * sizeof(double));
       CK(launch_ew_bwd(q, p.precision, st));
-    } else if (op.kind == TOP_BNGRAD) {
-      continue;  // written by the elementwise backward's second pass
-      const TrainPlan::BnHost& b = tp.bns[op.a];
-      BnGradParams q{};
-      q.bn = bn_arrays(tp, op.a), q.nseg = (int)b.segs.size();
-      for (int s = 0; s < q.nseg; ++s) {
-        const TrainPlan::ParamOff& po = tp.param_off[b.segs[s].layer];
-        q.seg[s] = BnGradSeg{grads + po.gamma, grads + po.beta, b.segs[s].ch_off, b.segs[s].count};
-      }
-      CK(launch_bn_grad(q, st));
     } else if (op.kind == TOP_WGRAD) {
       const TrainPlan::WgHost& w = tp.wgs[op.a];
       const ConvOpHost& f = p.convs[w.conv];

@@ -11,8 +11,8 @@
 namespace mtldas {
 
 enum : int {
-  TOP_STEM = 0, TOP_CONV, TOP_STATS, TOP_FINAL, TOP_EW, TOP_HEAD,           // forward
-  TOP_HEADBWD, TOP_EWB, TOP_BNGRAD, TOP_WGRAD, TOP_DGRAD, TOP_STEMWG       // backward
+  TOP_STEM = 0, TOP_CONV, TOP_EW, TOP_HEAD,              // forward (BatchNorm statistics + finalize live inside TOP_EW)
+  TOP_HEADBWD, TOP_EWB, TOP_WGRAD, TOP_DGRAD, TOP_STEMWG  // backward (BatchNorm gradients are written by TOP_EWB)
 };
 
 struct TrainPlan {

@@ -1,7 +1,7 @@
 // Streaming training kernels of the MTL-DAS hot path, written as chunk-resident grid-stride loops:
-//   stats_kernel        per-channel sum / sum of squares of a raw conv output (+ BatchNorm finalize in the last block)
-//   ew_fwd_kernel       fused BatchNorm apply + activation (ReLU / residual / sigmoid*feature / ReLU+maxpool)
-//   ew_bwd_kernel       fused activation' + BatchNorm backward: PASS 0 reductions, PASS 1 input gradient
+//   ew_fwd_kernel       batch statistics -> chunk barrier -> BatchNorm finalize -> apply + activation (ReLU / residual /
+//                       sigmoid*feature / ReLU+maxpool), one launch
+//   ew_bwd_kernel       activation' + BatchNorm backward: reductions -> chunk barrier -> input gradient, one launch
 //   stem_wgrad_kernel   weight gradient of the 7x7/s3 stem from the fp32 patches
 // grid = (blocks per chunk, chunks): a block owns ONE 8-channel chunk, so the per-channel BatchNorm constants
 // live in registers for the whole loop, the per-thread partial sums are reduced once per block (not once per
@@ -93,21 +93,6 @@ __device__ __forceinline__ void finalize_channel(const FinalizeParams& p, int c)
   p.bn.scale[c] = scale, p.bn.shift[c] = shift, p.bn.mean[c] = fm, p.bn.invstd[c] = fi;
 }
 
-// blocks per chunk: about four blocks of 256 threads per SM over the whole grid, never more than the work
-inline unsigned blocks_per_chunk(long long positions, int chunks) {
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (sms <= 0) sms = 148;
-  }
-  const long long need = (positions + kEwThreads - 1) / kEwThreads;
-  const long long want = std::max<long long>(1, ((long long)sms * 4 + chunks - 1) / chunks);
-  return (unsigned)std::max<long long>(1, std::min(need, want));
-}
-
-
 // Barrier among the gridDim.x blocks that own one chunk (arrival counter zeroed by the host-side memset of the
 // sums).  Every block of the grid is resident (the launchers size the grid from the occupancy query), so the
 // spin cannot starve a block that has not started; the clock bound turns a broken invariant into a trap, not a hang.
@@ -179,13 +164,6 @@ inline unsigned resident_blocks_per_chunk(K kernel, long long positions, int chu
 }
 
 }  // namespace
-
-__global__ void finalize_kernel(const __grid_constant__ FinalizeParams p) { finalize_channel(p, threadIdx.x); }
-
-cudaError_t launch_finalize(const FinalizeParams& p, cudaStream_t st) {
-  finalize_kernel<<<1, 256, 0, st>>>(p);
-  return cudaGetLastError();
-}
 
 // ---------------------------------------------------------------------------------------------
 // fused forward of one BatchNorm + activation: batch statistics -> per-chunk barrier -> finalize -> apply.

@@ -1,6 +1,5 @@
-// Training-mode kernels of the MTL-DAS hot path: batch-statistics BatchNorm (stats / finalize / fused apply),
-// fused elementwise backward (ReLU / residual / sigmoid*feature / ReLU+maxpool with BN backward), weight gradients,
-// head backward.  All streaming kernels move 16/32-byte granules with consecutive threads on consecutive positions.
+// Training-mode kernels of the MTL-DAS hot path: weight gradients (tcgen05 and CUDA-core), joint NLL loss, head
+// backward, gradient unpack.  The BatchNorm / activation kernels live in train_ew.cu.
 //
 // Reference semantics restated (autograd of /root/reference/model/modelA_MTL.py:127-174 under utils.py:359-373):
 //   BatchNorm2d train: y_hat = (y - mean) * invstd (biased batch variance), out = gamma*y_hat + beta;
@@ -18,21 +17,6 @@
 
 namespace mtldas {
 
-
-__global__ void bn_grad_kernel(const __grid_constant__ BnGradParams p) {
-  const int c = threadIdx.x;
-  for (int s = 0; s < p.nseg; ++s) {
-    const BnGradSeg& g = p.seg[s];
-    if (c >= g.ch_off && c < g.ch_off + g.count) {
-      g.dgamma[c - g.ch_off] = (float)p.bn.red_gy[c];
-      g.dbeta[c - g.ch_off] = (float)p.bn.red_g[c];
-    }
-  }
-}
-cudaError_t launch_bn_grad(const BnGradParams& p, cudaStream_t st) {
-  bn_grad_kernel<<<1, 256, 0, st>>>(p);
-  return cudaGetLastError();
-}
 
 // ---------------------------------------------------------------------------------------------
 // weight gradient on CUDA cores: dW[tap][k][cout] += sum_pos zin[pos+off][k] * dy[pos][cout]
@@ -592,20 +576,6 @@ cudaError_t launch_head_bwd(const HeadBwdParams& p, int precision, cudaStream_t 
 // ---------------------------------------------------------------------------------------------
 // packed fp32 weight gradient -> reference parameter layout (inverse of pack_kernel's placement)
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) unpack_kernel(const __grid_constant__ UnpackParams p) {
-  const int kk = p.ksize * p.ksize;
-  const int total = p.cout * p.cin * kk;
-  const int i = blockIdx.x * 256 + threadIdx.x;
-  if (i >= total) return;
-  const int co = i / (p.cin * kk);
-  const int r1 = i - co * (p.cin * kk);
-  const int ci = r1 / kk;
-  int tap = r1 - ci * kk, k = ci;
-  if (ci >= p.split) tap += 1, k -= p.split;
-  k += p.k_off;
-  p.dst[i] = p.src[((size_t)tap * p.K_tap + k) * p.Cout_p + p.cout_off + co];
-}
-
 __global__ void __launch_bounds__(256) unpack_batch_kernel(const __grid_constant__ UnpackBatch b) {
   const UnpackParams& p = b.u[blockIdx.y];
   const int kk = p.ksize * p.ksize;
@@ -633,10 +603,5 @@ cudaError_t launch_unpack_batch(const UnpackParams* u, int n, cudaStream_t st) {
   return cudaSuccess;
 }
 
-cudaError_t launch_unpack(const UnpackParams& p, cudaStream_t st) {
-  const int total = p.cout * p.cin * p.ksize * p.ksize;
-  unpack_kernel<<<(total + 255) / 256, 256, 0, st>>>(p);
-  return cudaGetLastError();
-}
 
 }  // namespace mtldas

@@ -84,12 +84,6 @@ struct EwParams {
 };
 
 
-struct BnGradParams {
-  BnArrays bn;
-  int nseg;
-  BnGradSeg seg[2];
-};
-
 struct WgradParams {     // dW[tap][k][cout] += sum_pos zin[pos + off_tap][k] * dy[pos][cout]   (fp32 result)
   ConvSrcDev src[kMaxSrc];   // forward input sources (as in ConvParams, body position 0)
   ConvTapDev tap[kMaxTaps];
