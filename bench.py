@@ -190,8 +190,8 @@ def measure_train(args, dev, world, rank, barrier):
     m.precision = args.precision
     m.load_state_dict(O.synth_state_dict("MTL", seed=0), strict=True)
     m = m.to(dev).train()
-    opt = torch.optim.Adam(m.parameters(), lr=1e-3 / 1.5, weight_decay=1e-5, fused=True)   # utils.py:133-134,247
-    trainer = DataParallelTrainer(m, opt)
+    # Adam(lr 1e-3 / 1.5, L2 weight decay 1e-5) as utils.py:133-134,247, stepped over the flattened parameter buffer
+    trainer = DataParallelTrainer(m, flat_adam=dict(lr=1e-3 / 1.5, weight_decay=1e-5))
     base, yd, ye = O.synth_patches(64, seed=4321 + rank)
     reps = (nb + 63) // 64
     xh = base.repeat(reps, 1, 1, 1)[:nb].contiguous().pin_memory()
@@ -211,10 +211,29 @@ def measure_train(args, dev, world, rank, barrier):
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     # end to end: H2D of the batch from pinned memory + D2H of the loss every step
+    # (double-buffered: the copy of step i+1 is issued on a side stream before the loss of step i is read back)
+    copy_stream = torch.cuda.Stream(device=dev)
+    slots = [torch.empty_like(x), torch.empty_like(x)]
+    ready = [torch.cuda.Event(), torch.cuda.Event()]
+    consumed = [torch.cuda.Event(), torch.cuda.Event()]
+
+    def upload(i):
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[i & 1])
+            slots[i & 1].copy_(xh, non_blocking=True)
+            ready[i & 1].record(copy_stream)
+
+    for ev in consumed:
+        ev.record()
+    torch.cuda.synchronize()
     t0 = time.perf_counter()
-    for _ in range(steps):
-        xd = xh.to(dev, non_blocking=True)
-        loss = trainer.step(xd, [ydd, yed])
+    upload(0)
+    for i in range(steps):
+        torch.cuda.current_stream().wait_event(ready[i & 1])
+        loss = trainer.step(slots[i & 1], [ydd, yed])
+        consumed[i & 1].record()
+        if i + 1 < steps:
+            upload(i + 1)
         lv = float(loss)
     barrier()
     e2e = torch.tensor([time.perf_counter() - t0], device=dev)

@@ -59,29 +59,64 @@ def unflatten_like(flat: torch.Tensor, params: Sequence[torch.Tensor]) -> List[t
     return out
 
 
-class DataParallelTrainer:
-    """One training step per call: shard -> forward/backward on the local plan -> one all-reduce -> optimizer."""
+def flatten_parameters_(module) -> torch.nn.Parameter:
+    """Re-home every parameter of `module` into ONE flat fp32 buffer (named_parameters order, the order of the flat
+    gradient) and return that buffer as a Parameter.  The module's parameters become views of it, so the state_dict,
+    the packing kernels and an optimizer stepping the flat tensor all see the same storage; the elementwise optimizers
+    of the reference (Adam with L2 weight decay, utils.py:133-134) then update all 126 tensors in one fused launch
+    instead of a multi-tensor sweep."""
+    params = [p for _, p in module.named_parameters()]
+    if not params:
+        raise ValueError("module has no parameters")
+    flat = torch.cat([p.detach().reshape(-1).float() for p in params]).contiguous()
+    off = 0
+    for p in params:
+        n = p.numel()
+        p.data = flat[off:off + n].view(p.shape)
+        off += n
+    return torch.nn.Parameter(flat, requires_grad=True)
 
-    def __init__(self, module, optimizer, group=None):
+
+class DataParallelTrainer:
+    """One training step per call: shard -> forward/backward on the local plan -> one all-reduce -> optimizer.
+
+    optimizer: a torch optimizer over module.parameters() (the reference's construction), or None together with
+    `flat_adam=dict(lr=..., weight_decay=...)` to flatten the parameters and step one fused Adam over the flat buffer."""
+
+    def __init__(self, module, optimizer=None, group=None, flat_adam=None):
         self.module, self.optimizer, self.group = module, optimizer, group
+        self._flat_param = None
+        if optimizer is None:
+            if flat_adam is None:
+                raise ValueError("give an optimizer or flat_adam=dict(lr=..., weight_decay=...)")
+            self._flat_param = flatten_parameters_(module)
+            kw = dict(flat_adam)
+            if self._flat_param.is_cuda:
+                kw.setdefault("fused", True)
+            self.optimizer = torch.optim.Adam([self._flat_param], **kw)
         self.params = [p for _, p in module.named_parameters()]
         self._flat = None
         self._loss_bufs = None
+        self._state = None
 
     def step(self, x_local: torch.Tensor, labels_local: Sequence[torch.Tensor]):
         """x_local / labels_local: this rank's shard. Returns the local loss (python float is NOT taken here)."""
         from .engine import nll_loss
         m = self.module
         plan = m._train_plan(x_local.device, x_local.shape[0])
-        state = [v.detach() for v in m.state_dict(keep_vars=True).values()]
-        outs = plan.forward(state, x_local)
+        if self._state is None:   # parameter / buffer tensors are updated in place, their identities are stable
+            self._state = [v.detach() for v in m.state_dict(keep_vars=True).values()]
+        outs = plan.forward(self._state, x_local)
         # NLLLoss (mean) per task, summed, and its gradient: one fused launch (utils.py:139,361,367)
         self._loss_bufs = nll_loss(list(outs), [y.long().contiguous() for y in labels_local], out=self._loss_bufs)
         loss, douts = self._loss_bufs
         if self._flat is None or self._flat.device != x_local.device:
             self._flat = torch.empty(plan.n_params, dtype=torch.float32, device=x_local.device)
-            for p, g in zip(self.params, unflatten_like(self._flat, self.params)):
-                p.grad = g                         # views of the flat buffer: bound once, refilled every step
+            if self._flat_param is not None:
+                self._flat_param.grad = self._flat  # one tensor, one fused optimizer launch
+            else:
+                for p, g in zip(self.params, unflatten_like(self._flat, self.params)):
+                    p.grad = g                     # views of the flat buffer: bound once, refilled every step
         plan.backward(douts, self._flat)
         allreduce_mean_(self._flat, self.group)
         self.optimizer.step()

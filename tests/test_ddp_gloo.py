@@ -68,3 +68,34 @@ def test_flat_gradient_allreduce_equals_mean_of_shard_gradients(tmp_path):
     for r in range(world):
         res = torch.load(os.path.join(str(tmp_path), f"r{r}.pt"))
         assert res["ok"], res
+
+
+def test_flat_parameter_adam_equals_per_tensor_adam():
+    """flatten_parameters_ re-homes the parameters into one buffer (named_parameters order = flat-gradient order);
+    Adam with L2 weight decay (utils.py:133-134) is elementwise, so stepping the flat tensor must give bit-identical
+    parameters to stepping the separate tensors, and the module must keep seeing the updated values."""
+    import torch
+    from mtldas_b200.ddp import flatten_parameters_, unflatten_like
+    torch.manual_seed(0)
+
+    def make():
+        torch.manual_seed(1)
+        return torch.nn.Sequential(torch.nn.Conv2d(1, 4, 3, bias=False), torch.nn.BatchNorm2d(4), torch.nn.Conv2d(4, 2, 1))
+    a, b = make(), make()
+    opt_a = torch.optim.Adam(a.parameters(), lr=1e-3 / 1.5, weight_decay=1e-5)
+    flat = flatten_parameters_(b)
+    opt_b = torch.optim.Adam([flat], lr=1e-3 / 1.5, weight_decay=1e-5)
+    names_a = [n for n, _ in a.named_parameters()]
+    assert [n for n, _ in b.named_parameters()] == names_a
+    assert flat.numel() == sum(p.numel() for p in a.parameters())
+    x = torch.randn(3, 1, 8, 8)
+    for step in range(3):
+        grads = [torch.randn_like(p) for p in a.parameters()]
+        for p, g in zip(a.parameters(), grads):
+            p.grad = g.clone()
+        flat.grad = torch.cat([g.reshape(-1) for g in grads])
+        opt_a.step(); opt_b.step()
+        for pa, pb, view in zip(a.parameters(), b.parameters(), unflatten_like(flat.data, list(b.parameters()))):
+            assert torch.equal(pa.data, pb.data) and pb.data.data_ptr() == view.data_ptr()
+        assert torch.equal(a(x), b(x))
+    assert set(b.state_dict().keys()) == set(a.state_dict().keys())
