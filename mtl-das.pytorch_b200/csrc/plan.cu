@@ -412,8 +412,14 @@ Plan* build_plan(int kind, int mb, int precision) {
   p.stem_w_off = take(49 * 16 * 4);
   p.stem_b_off = take(16 * 4);
   p.stem_wu_off = take(2048);
-  // host entry point: chunks of at most 1024 patches through two staging slots (H2D of chunk i+1 overlaps chunk i)
-  p.host_chunk = std::min(mb, 1024);
+  // host entry point: chunks of at most 512 patches through two staging slots (H2D of chunk i+1 overlaps chunk i;
+  // the copy is the bottleneck, so the un-overlapped tail is the compute of the LAST chunk: keep it short)
+  {
+    const char* e = getenv("MTLDAS_HOST_CHUNK");
+    int hc = e ? atoi(e) : 512;  // measured end to end at batch 4096: 1024 -> 460 k, 512 -> 495 k, 256 -> 426 k samples/s
+    if (hc < 64) hc = 64;
+    p.host_chunk = std::min(mb, hc);
+  }
   p.x_stage_off = take((size_t)2 * p.host_chunk * kPatchH * kPatchW * 4);
   p.out_stage_off = take((size_t)2 * p.host_chunk * 18 * 4);
   p.ws_bytes = off;
