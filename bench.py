@@ -44,6 +44,7 @@ def parse():
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--cpu-sample", type=int, default=256, help="patches per CPU-baseline step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the model B / streaming side measurements")
     ap.add_argument("--train-batch", type=int, default=256, help="training patches per GPU per step")
     return ap.parse_args()
 
@@ -175,6 +176,57 @@ def conv_algorithmic_elems_per_sample(desc):
                 e += L["cin"] * hi * wi + L["cout"] * ho * wo
         per_op.append(e)
     return per_op
+
+
+def measure_extras(args, dev, world, rank, barrier):
+    """BASELINE.json configs[3] and configs[4], reported next to the headline (same timing rules, fewer steps):
+    model B (single_distance / single_event) inference on the same kernels, and streaming inference over a synthetic
+    DAS array sharded by fibre-channel windows (no collective)."""
+    import torch
+    import torch.distributed as dist
+    from mtldas_b200 import EvalPlan, synth as O
+    from mtldas_b200.stream_infer import StreamingInference
+    steps = max(3, min(args.steps, 10))
+
+    def timed(fn):
+        for _ in range(3):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()) / steps
+
+    out = {}
+    B = args.batch
+    base, _, _ = O.synth_patches(64, seed=99 + rank)
+    x = base.repeat((B + 63) // 64, 1, 1, 1)[:B].contiguous().to(dev)
+    for kind in ("single_distance", "single_event"):
+        plan = EvalPlan(kind, min(B, args.micro_batch), args.precision, dev)
+        plan.pack({k: v.to(dev) for k, v in O.synth_state_dict(kind, seed=0).items()})
+        outs = [torch.empty(B, c, device=dev) for c in plan.classes]
+        ms = timed(lambda: plan.forward(x, outs))
+        out["model_b_" + kind] = {"value": world * B / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "batch_per_gpu": B,
+                                  "workload": "Single_Task_Net inference, inputs resident"}
+        del plan, outs
+    # streaming: [n_channels, n_time] fp32 per rank, window 100 channels x 250 samples, channel stride 10
+    n_ch, n_time, stride = 2140, 250 * 20, 10
+    si = StreamingInference(O.synth_state_dict("MTL", seed=0), "MTL", args.precision, min(B, args.micro_batch), stride, dev)
+    g = torch.Generator(device="cpu").manual_seed(7 + rank)
+    slab = torch.randn(n_ch, n_time, generator=g).to(dev)
+    nwin = (n_ch - 100) // stride + 1
+    ms = timed(lambda: si.run(slab))
+    out["streaming"] = {"value": world * nwin * (n_time // 250) / (ms * 1e-3), "unit": "windows/s", "ms_per_step": ms,
+                        "workload": "array [%d channels x %d samples] per GPU -> %d windows x %d blocks, stride %d, "
+                                    "window gather + MTL forward, windows sharded across ranks, no collective"
+                                    % (n_ch, n_time, nwin, n_time // 250, stride)}
+    return out
 
 
 def measure_train(args, dev, world, rank, barrier):
@@ -346,6 +398,7 @@ def run_ours(args):
                               for i, (m, op) in enumerate(zip(per_op_ms, desc["program"]))}}
 
     train = measure_train(args, dev, world, rank, barrier)
+    extras = measure_extras(args, dev, world, rank, barrier) if not args.no_extras else None
 
     if rank == 0:
         value = world * B * args.steps / (ms_total * 1e-3)
@@ -367,6 +420,7 @@ def run_ours(args):
             "clocks": clocks,
             "roofline": roof,
             "train": train,
+            "extras": extras,
         }
         if world == 1 and not args.no_cpu_baseline:
             steps = 16
