@@ -191,3 +191,36 @@ def test_streaming_inference_windows_match_oracle():
         r = r.view(len(starts_all), 3, -1)
         assert got.shape == r.shape
         assert float((got.double() - r).abs().max() / r.abs().max()) <= 1e-4
+
+
+def test_tensor_core_stem_matches_oracle_and_cuda_core_stem(monkeypatch):
+    """The tcgen05 stem (one banded GEMM per output row, stem_umma.cu) against the fp64 oracle's stem feature map and
+    against the CUDA-core stem on the same inputs; also the unaligned-patch fallback (bulk copies need 16-byte
+    aligned patches: a tensor view at a 4-byte offset must take the CUDA-core kernel and give the same numbers)."""
+    from mtldas_b200 import EvalPlan
+    n = 7                                   # 7 images x 3 units: partial last unit (10 rows) and a ragged grid
+    sd = O.synth_state_dict("MTL", seed=0)
+    x, _, _ = O.synth_patches(n, seed=11)
+    _, feats = O.forward(sd, x, "MTL", training=False, dtype=torch.float64, return_feats=True)
+    ref = feats["stem"]
+    got = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("MTLDAS_UMMA_STEM", flag)
+        plan = EvalPlan("MTL", 8, "bf16", "cuda:0")
+        plan.pack({k: v.cuda() for k, v in sd.items()})
+        plan.forward(x.cuda())
+        got[flag] = plan.read_tensor("stem", n).cpu().double()
+        err = float((got[flag] - ref).abs().max() / ref.abs().max())
+        assert err < 1e-2, (flag, err)       # bf16 operands (flag 1) / bf16 store (both): north_star bf16 tolerance
+    # the two kernels differ only by the bf16 rounding of the patch and the weights
+    assert float((got["1"] - got["0"]).abs().max() / ref.abs().max()) < 1e-2
+    monkeypatch.setenv("MTLDAS_UMMA_STEM", "1")
+    plan = EvalPlan("MTL", 8, "bf16", "cuda:0")
+    plan.pack({k: v.cuda() for k, v in sd.items()})
+    big = torch.empty(n * 25000 + 1, device="cuda")
+    xu = big[1:].view(n, 1, 100, 250)        # 4-byte offset: not 16-byte aligned
+    xu.copy_(x)
+    assert xu.data_ptr() % 16 != 0
+    plan.forward(xu)
+    fallback = plan.read_tensor("stem", n).cpu().double()
+    assert torch.equal(fallback, got["0"])

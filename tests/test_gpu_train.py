@@ -201,3 +201,30 @@ def test_nll_loss_matches_torch():
     bad = torch.zeros(1, dtype=torch.int32, device="cuda")
     nll_loss([lp0.detach()], [torch.full((n,), 16, device="cuda")], status=bad)
     assert int(bad) == 1      # torch raises on an out-of-range label; the kernel reports it
+
+
+def test_tensor_core_weight_gradients_match_cuda_core_weight_gradients(monkeypatch):
+    """The tcgen05 weight gradients (wide-N kernel for the narrow 3x3 layers, per-tap kernel for the rest) against the
+    CUDA-core weight gradient on identical bf16 activations: same sums, different association -> fp32 noise only."""
+    from mtldas_b200 import TrainPlan
+    n = 6                                    # 6 x 2975 positions: not a multiple of 16 (zero-filled K tail)
+    sd = O.synth_state_dict("MTL", seed=0)
+    x, yd, ye = O.synth_patches(n, seed=5)
+    state = [v.cuda().contiguous() for v in sd.values()]
+    flats = {}
+    for mode in ("umma", "cuda"):
+        if mode == "cuda":
+            monkeypatch.setenv("MTLDAS_WGRAD_CUDA_CORES", "1")
+        plan = TrainPlan("MTL", 8, "bf16", "cuda:0")
+        outs = plan.forward(state, x.cuda())
+        flats[mode] = plan.backward([torch.full_like(o, -1.0 / n) for o in outs]).cpu().double()
+    a, b = flats["umma"], flats["cuda"]
+    assert float((a - b).norm() / b.norm()) < 1e-5
+    off = 0
+    for k, shp, _ in O.state_dict_keys("MTL"):
+        if k.endswith(("running_mean", "running_var", "num_batches_tracked")):
+            continue
+        m = int(torch.tensor(shp).prod()) if len(shp) else 1
+        da, db = a[off:off + m], b[off:off + m]
+        off += m
+        assert float((da - db).norm()) <= 1e-4 * float(db.norm()) + 1e-9, k
