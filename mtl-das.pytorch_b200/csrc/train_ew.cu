@@ -414,6 +414,73 @@ __device__ __forceinline__ void act_grad(const float* y, const float* dzv, const
   }
 }
 
+// One pass of the ReLU + max-pool backward over the pooled positions of chunk c.  thread = pooled position; the 2x2
+// window's four full-resolution positions belong to this thread alone.  Two pooled positions (ten 16-byte loads)
+// are in flight per thread.  PASS 0 accumulates sum(g), sum(g*y_hat); PASS 1 writes dy.
+template <typename T, int PASS>
+__device__ __forceinline__ void pool_bwd_pass(const EwParams& p, int c, const BwdConst& k, int first, int stride,
+                                              const char* ybase, char* dybase, float* rg, float* rgy) {
+  constexpr int G = Gran<T>::bytes;
+  constexpr int U = Batch<T>::n / 2;  // bf16: two pooled positions per iteration, fp32: one (registers)
+  const int body = (int)p.body;
+  for (int f0 = first; f0 < body; f0 += U * stride) {
+    Raw<T> rdz[U], ry[U][4];
+    long long pos0[U];
+    bool ok[U], inb[U][4];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int f = f0 + u * stride;
+      const Pos3 o = decode3(f < body ? f : 0, p.Pimgo, p.Wpo, p.magic_pimgo, p.magic_wpo);
+      ok[u] = f < body && o.h < p.Ho && o.w < p.Wo;
+      const int h0 = 2 * o.h, w0 = 2 * o.w;
+      pos0[u] = (long long)o.n * p.Pimg + h0 * p.Wp + w0;
+      inb[u][0] = ok[u], inb[u][1] = ok[u] && w0 + 1 < p.W, inb[u][2] = ok[u] && h0 + 1 < p.H;
+      inb[u][3] = inb[u][1] && inb[u][2];
+      if (ok[u]) load_raw(view_addr<T>(p.dz, c, f, o.n, o.h, o.w), rdz[u]);
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        if (inb[u][q]) load_raw(ybase + (pos0[u] + (q >> 1) * p.Wp + (q & 1)) * G, ry[u][q]);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (!ok[u]) continue;
+      float dzv[8], yv[4][8];
+      unpack(rdz[u], dzv);
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        if (inb[u][q]) unpack(ry[u][q], yv[q]);
+      int arg[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float best = -INFINITY;
+        arg[j] = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          if (!inb[u][q]) continue;
+          const float r = fmaxf(fmaf(yv[q][j], k.sc[j], k.shf[j]), 0.f);
+          if (r > best) best = r, arg[j] = q;   // strict '>' : first maximum wins (scan order h, w)
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (!inb[u][q]) continue;
+        float dyv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float v = fmaf(yv[q][j], k.sc[j], k.shf[j]);
+          const float g = (arg[j] == q && v > 0.f) ? dzv[j] : 0.f;
+          if (PASS == 0) {
+            rg[j] += g, rgy[j] = fmaf(g, (yv[q][j] - k.a[j]) * k.b[j], rgy[j]);
+          } else {
+            dyv[j] = fmaf(k.sc[j], g, fmaf(k.b[j], yv[q][j], k.a[j]));
+          }
+        }
+        if (PASS == 1) store8<T>(dybase + (pos0[u] + (q >> 1) * p.Wp + (q & 1)) * G, dyv);
+      }
+    }
+  }
+}
+
 template <typename T, int MODE>
 __global__ void __launch_bounds__(kEwThreads, 2) ew_bwd_kernel(const __grid_constant__ EwParams p) {
   __shared__ float sh[kEwThreads / 32][8];
@@ -426,7 +493,6 @@ __global__ void __launch_bounds__(kEwThreads, 2) ew_bwd_kernel(const __grid_cons
   const int first = blockIdx.x * kEwThreads + threadIdx.x;
 
   if (MODE == EW_RELU_POOL) {
-    // thread = pooled position; the 2x2 window's four full-resolution positions belong to this thread alone
     BwdConst k;
     load_fwd_const(p.bn, c, k);
     const char* ybase = p.y.base + ((long long)c * p.y.plane + p.y.g_lo) * G;
@@ -434,57 +500,12 @@ __global__ void __launch_bounds__(kEwThreads, 2) ew_bwd_kernel(const __grid_cons
     float rg[8], rgy[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) rg[j] = rgy[j] = 0.f;
-#pragma unroll 1
-    for (int pass = 0; pass < 2; ++pass) {
-      for (int f = first; f < body; f += stride) {
-        const Pos3 o = decode3(f, p.Pimgo, p.Wpo, p.magic_pimgo, p.magic_wpo);
-        if (!(o.h < p.Ho && o.w < p.Wo)) continue;
-        float dzv[8];
-        load8<T>(view_addr<T>(p.dz, c, f, o.n, o.h, o.w), dzv);
-        const int h0 = 2 * o.h, w0 = 2 * o.w;
-        const long long pos0 = (long long)o.n * p.Pimg + h0 * p.Wp + w0;
-        bool inb[4];
-        inb[0] = true, inb[1] = w0 + 1 < p.W, inb[2] = h0 + 1 < p.H, inb[3] = inb[1] && inb[2];
-        float yv[4][8];
-#pragma unroll
-        for (int q = 0; q < 4; ++q)
-          if (inb[q]) load8<T>(ybase + (pos0 + (q >> 1) * p.Wp + (q & 1)) * G, yv[q]);
-        int arg[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          float best = -INFINITY;
-          arg[j] = 0;
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            if (!inb[q]) continue;
-            const float r = fmaxf(fmaf(yv[q][j], k.sc[j], k.shf[j]), 0.f);
-            if (r > best) best = r, arg[j] = q;   // strict '>' : first maximum wins (scan order h, w)
-          }
-        }
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          if (!inb[q]) continue;
-          float dyv[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float v = fmaf(yv[q][j], k.sc[j], k.shf[j]);
-            const float g = (arg[j] == q && v > 0.f) ? dzv[j] : 0.f;
-            if (pass == 0) {
-              rg[j] += g, rgy[j] = fmaf(g, (yv[q][j] - k.a[j]) * k.b[j], rgy[j]);
-            } else {
-              dyv[j] = fmaf(k.sc[j], g, fmaf(k.b[j], yv[q][j], k.a[j]));
-            }
-          }
-          if (pass == 1) store8<T>(dybase + (pos0 + (q >> 1) * p.Wp + (q & 1)) * G, dyv);
-        }
-      }
-      if (pass == 0) {
-        block_reduce8(rg, p.bn.red_g + c * 8, sh);
-        block_reduce8(rgy, p.bn.red_gy + c * 8, sh);
-        chunk_barrier(p.sync + c, gridDim.x);
-        to_grad_const(p.bn, c, p.inv_n, k);
-      }
-    }
+    pool_bwd_pass<T, 0>(p, c, k, first, stride, ybase, dybase, rg, rgy);
+    block_reduce8(rg, p.bn.red_g + c * 8, sh);
+    block_reduce8(rgy, p.bn.red_gy + c * 8, sh);
+    chunk_barrier(p.sync + c, gridDim.x);
+    to_grad_const(p.bn, c, p.inv_n, k);
+    pool_bwd_pass<T, 1>(p, c, k, first, stride, ybase, dybase, rg, rgy);
     if (blockIdx.x == 0) {
       if (threadIdx.x == 0) write_bn_grads(p.bn, p.gseg, p.ngseg, p.nchunks, c, 1);
       // the tensor-core weight gradient reduces 16 positions per MMA: keep [body, round_up(body,16)) zero
