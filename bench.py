@@ -385,8 +385,8 @@ def run_ours(args):
             pass
         ach = conv_bytes / (conv_ms * 1e-3) / 1e9
         # DRAM read+write bytes per conv launch from the ncu --set full pass over this workload
-        # (profiles/r1_conv_ncu_full_batch4096.txt: 15 342 MB over the 30 launches); other workloads: not captured
-        traffic = 15342e6 / 30 if (B == 4096 and args.precision == "bf16" and passes == 1) else None
+        # (profiles/r1_conv_ncu_full_batch4096.txt: 15 330 MB over the 30 launches); other workloads: not captured
+        traffic = 15330e6 / 30 if (B == 4096 and args.precision == "bf16" and passes == 1) else None
         roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
                 "traffic_source": "profiles/r1_conv_ncu_full_batch4096.txt" if traffic else None,
                 "algorithmic_bytes_per_launch": conv_bytes / n_conv,
