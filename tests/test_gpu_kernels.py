@@ -224,3 +224,24 @@ def test_tensor_core_stem_matches_oracle_and_cuda_core_stem(monkeypatch):
     plan.forward(xu)
     fallback = plan.read_tensor("stem", n).cpu().double()
     assert torch.equal(fallback, got["0"])
+
+
+def test_eval_is_batching_invariant_at_full_size():
+    """Size-independent property at BASELINE.json's full inference size: eval-mode results do not depend on how the
+    patches are batched (4100 > the 4096-patch plan, so the module runs two passes; the same patches as three ragged
+    calls must give bit-identical log-probs on the bf16 path)."""
+    from model.modelA_MTL import MTL_Net
+    m = MTL_Net()
+    m.load_state_dict(O.synth_state_dict("MTL", seed=0), strict=True)
+    m = m.cuda().eval()
+    base, _, _ = O.synth_patches(64, seed=3)
+    g = torch.Generator().manual_seed(5)
+    x = (base.repeat(65, 1, 1, 1)[:4100] + 0.1 * torch.randn(4100, 1, 100, 250, generator=g)).cuda()
+    with torch.no_grad():
+        whole = [o.clone() for o in m(x)]
+        parts = [[o.clone() for o in m(x[a:b])] for a, b in ((0, 1), (1, 1000), (1000, 4100))]
+    for t in range(2):
+        cat = torch.cat([p[t] for p in parts])
+        assert not bool(torch.isnan(whole[t]).any())
+        assert torch.equal(whole[t], cat)
+        assert float((whole[t].exp().sum(1) - 1).abs().max()) < 1e-3    # rows are log-probabilities
