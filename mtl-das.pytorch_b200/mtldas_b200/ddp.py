@@ -42,8 +42,11 @@ def shard_windows(n_channels: int, rank: int, world: int, window: int = 100, str
 def allreduce_mean_(flat: torch.Tensor, group=None) -> torch.Tensor:
     """In-place mean over ranks of the flat gradient buffer: one collective per step."""
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
-        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
-        flat.div_(dist.get_world_size(group))
+        if flat.is_cuda and dist.get_backend(group) == "nccl":
+            dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=group)   # the division happens inside the collective
+        else:
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)   # gloo has no AVG
+            flat.div_(dist.get_world_size(group))
     return flat
 
 
