@@ -65,7 +65,27 @@ def _load():
     return L
 
 
-lib = _load()
+class _LazyLib:
+    """The shared library is mapped on first use, not at package import: importing `mtldas_b200` (or its synthetic-data
+    helpers) from a CPU-only process -- the oracle, the reference arm of bench.py -- must not load any native code."""
+
+    _real = None
+
+    def _get(self):
+        if _LazyLib._real is None:
+            _LazyLib._real = _load()
+        return _LazyLib._real
+
+    def __getattr__(self, name):
+        return getattr(self._get(), name)
+
+
+lib = _LazyLib()
+
+
+def loaded():
+    """True once libmtldas_b200.so has been mapped into this process."""
+    return _LazyLib._real is not None
 
 
 def check(rc, what):

@@ -96,5 +96,40 @@ def main():
             print(path, os.path.getsize(path) // 1024, "KiB", "loss", [float(res[k]) for k in res if k.startswith("loss")])
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and "--trained" not in sys.argv:
     main()
+
+
+def make_trained_state(steps=40, batch=32):
+    """the weight state "after 40 reference Adam steps" -- torch.manual_seed(0), the
+    reference constructor's default init, Adam(lr 1e-3 / 1.5, weight_decay 1e-5) as utils.py:133-134,247, batches of 32
+    synthetic patches (seed 1000 + step), NLLLoss + NLLLoss (utils.py:139,361,367).  Stored as fp32 arrays in
+    state_dict order (MTL_trained40.npz) with the per-step loss curve; tests/test_oracle_golden.py re-runs the same 40
+    steps on the oracle restatement and must land on the same curve."""
+    torch.manual_seed(0)
+    torch.set_num_threads(8)
+    m = MTL_Net()
+    opt = torch.optim.Adam(m.parameters(), lr=1e-3 / 1.5, weight_decay=1e-5)
+    crit = torch.nn.NLLLoss()
+    init = {k: v.clone().numpy() for k, v in m.state_dict().items()}
+    m.train()
+    curve = []
+    for step in range(steps):
+        x, yd, ye = O.synth_patches(batch, seed=1000 + step)
+        out1, out2 = m(x)
+        loss = crit(out1, yd) + crit(out2, ye)
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        curve.append(float(loss.detach()))
+    out = {"key:" + k: v.numpy() for k, v in m.state_dict().items()}
+    out["loss_curve"] = np.array(curve)
+    # the initial state is kept in half precision only as a cross-check of the constructor's seeded init
+    out["init_checksum"] = np.array([float(np.abs(v).sum()) for v in init.values()], dtype=np.float64)
+    path = os.path.join(HERE, "MTL_trained40.npz")
+    np.savez_compressed(path, **out)
+    print(path, os.path.getsize(path) // 1024, "KiB", "loss", curve[0], "->", curve[-1])
+
+
+if __name__ == "__main__" and "--trained" in sys.argv:
+    make_trained_state()

@@ -58,7 +58,7 @@ def test_train_forward_and_running_stats_fp32(kind):
         assert torch.equal(new_state[k], sd[k])
 
 
-@pytest.mark.parametrize("kind", ["MTL", "single_event"])
+@pytest.mark.parametrize("kind", ["MTL", "single_event", "single_distance"])
 def test_train_gradients_fp32(kind):
     """north_star: fp32 path within 1e-4 on gradients.  The network is piecewise linear (ReLU, max-pool): when one
     pre-activation lies within fp32 rounding of 0 its mask flips and the whole gradient moves by ~1e-4 (a different,
