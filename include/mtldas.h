@@ -131,7 +131,8 @@ MTLDAS_API int mtldas_conv2d_nchw(const float* dev_x, const float* dev_x2, const
  * Its temporaries live in a fixed 32 MiB array inside the library image (held by every GPU that loads the
  * library, until exit); a call that needs more returns MTLDAS_ERR_UNSUPPORTED with the required size in
  * mtldas_last_error() and allocates nothing.  The first call on a device looks the array's device address up
- * (cudaGetSymbolAddress) -- make that first call before any stream capture.  All calls share the array: the part a
+ * (cudaGetSymbolAddress) -- make that first call before any stream capture; the address is cached per device ordinal
+ * for the life of the process, so after cudaDeviceReset the entry point must not be used again.  All calls share the array: the part a
  * call uses is cleared first, and calls whose GPU work overlaps (other streams / threads) race and must be serialised. */
 MTLDAS_API int mtldas_conv2d_nchw_static(const float* dev_x, const float* dev_x2, const float* dev_weight,
                                          const float* dev_bias, const float* dev_aux, float* dev_out, int n, int cin,
@@ -144,7 +145,12 @@ MTLDAS_API int mtldas_conv2d_nchw_static(const float* dev_x, const float* dev_x2
  * i.e. MTL_Net.forward in train mode (modelA_MTL.py:127-174, nn.BatchNorm2d batch statistics, running-stat update
  * with momentum 0.1) and the autograd backward of it.  The loss (NLLLoss per task, utils.py:139,361,367) stays
  * outside: backward takes d(loss)/d(log-probs).
- * `batch` is the largest batch the plan accepts (BatchNorm couples the batch, so one pass holds it all). */
+ * `batch` is the largest batch the plan accepts (BatchNorm couples the batch, so one pass holds it all).
+ * EXCLUSIVITY: the fused BatchNorm kernels synchronise the thread blocks of one channel chunk through a device-side
+ * counter and size their grids so that every block is resident on an otherwise idle GPU (the plan's own side stream is
+ * accounted for).  Keep at most ONE training plan with work in flight per device -- two training steps overlapping on
+ * one GPU (other streams / host threads, or another process under MPS) can starve each other's blocks; the kernels
+ * then trap after a bounded wait instead of hanging.  Inference plans have no such restriction. */
 typedef struct mtldas_train mtldas_train;
 MTLDAS_API mtldas_train* mtldas_train_create(int model_kind, int batch, int precision);
 MTLDAS_API void mtldas_train_destroy(mtldas_train* t);
@@ -176,6 +182,30 @@ MTLDAS_API size_t mtldas_train_describe(const mtldas_train* t, char* buf, size_t
 MTLDAS_API int mtldas_nll_loss(const float* dev_logp0, const long long* dev_y0, int classes0, float* dev_dlogp0,
                                const float* dev_logp1, const long long* dev_y1, int classes1, float* dev_dlogp1,
                                int n, float* dev_loss, int* dev_status, void* stream);
+
+/* optimizer step over the flat parameter buffer -------------------------------------------------------
+ * Replaces `optimizer.step()` with optimizer = optim.Adam(model.parameters(), lr=1e-3, weight_decay=1e-5)
+ * (utils.py:133-134,374): torch's Adam with L2 weight decay folded into the gradient (not AdamW), bias-corrected,
+ * no amsgrad.  One launch over n contiguous fp32 elements (all four buffers 16-byte aligned); `step` is the 1-based
+ * step count (the bias corrections 1 - beta^step are formed in double on the host).  The learning-rate schedule
+ * (lr /= 1.5 every 5 epochs, utils.py:245-247) stays with the caller: pass the current lr. */
+MTLDAS_API int mtldas_adam_step(float* dev_params, const float* dev_grads, float* dev_exp_avg, float* dev_exp_avg_sq,
+                                size_t n, int step, float lr, float beta1, float beta2, float eps, float weight_decay,
+                                void* stream);
+
+/* validation bookkeeping on the device -----------------------------------------------------------------
+ * Replaces, per validation batch, utils.py:274-291: criterion(out_t, y_t) sums, pred_t = torch.max(out_t, 1)[1]
+ * (first maximum wins), (pred_t == y_t).sum(), and the label / prediction lists that become
+ * sklearn.metrics.confusion_matrix at utils.py:313 -- without the per-sample `int(x)` device syncs of
+ * utils.py:308-311.  ACCUMULATES into caller-zeroed buffers, so one read-back per epoch suffices:
+ *   dev_counts4[0..1] correct predictions per task, [2] samples seen, [3] labels outside [0, classes);
+ *   dev_loss_sums2[t] = sum_i -logp_t[i, y_t[i]]  (NLLLoss(mean) of a batch = its share / n);
+ *   dev_confusion_t[label * classes_t + prediction] (int64).
+ * dev_pred_t (int64 [n]) may be NULL.  The second task may be NULL (single-task nets).  classes <= 16. */
+MTLDAS_API int mtldas_eval_metrics(const float* dev_logp0, const long long* dev_y0, int classes0, long long* dev_pred0,
+                                   const float* dev_logp1, const long long* dev_y1, int classes1, long long* dev_pred1,
+                                   int n, long long* dev_counts4, double* dev_loss_sums2, long long* dev_confusion0,
+                                   long long* dev_confusion1, void* stream);
 
 /* streaming inference over a large DAS array --------------------------------------------------------
  * No counterpart in the reference (its README only motivates it): cuts the [100 x 250] patches the

@@ -833,16 +833,17 @@ static cudaError_t launch_ex(K kernel, dim3 grid, dim3 block, size_t smem, cudaS
 cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream, bool pdl) {
   if (precision == 0 && p.persist_stages > 0) {
     const size_t smem = conv_persist_smem_bytes(p);
-    static size_t configured_p = 0;
-    if (smem > configured_p) {
-      cudaError_t e = cudaSuccess;
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_ADD_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_SIGMOID_MUL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_ACCUM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    static PerDeviceSmem configured_p;
+    {
+      cudaError_t e = configured_p.ensure(smem, [](int bytes) {
+        cudaError_t e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_ADD_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_SIGMOID_MUL>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_ACCUM>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        return e;
+      });
       if (e != cudaSuccess) return e;
-      configured_p = smem;
     }
     const int tile = p.pool_k > 0 ? 2 * p.Wp * p.pool_k : p.MT * kTileM;
     const int ntiles = (int)((p.body + tile - 1) / tile);
@@ -874,16 +875,17 @@ cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream,
     }
   } else if (precision == 0) {
     size_t smem = conv_umma_smem_bytes(p);
-    static size_t configured = 0;
-    if (smem > configured) {
-      cudaError_t e = cudaSuccess;
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_kernel<EPI_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_kernel<EPI_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_kernel<EPI_ADD_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_kernel<EPI_SIGMOID_MUL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_kernel<EPI_ACCUM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    static PerDeviceSmem configured;
+    {
+      cudaError_t e = configured.ensure(smem, [](int bytes) {
+        cudaError_t e = cudaFuncSetAttribute(conv_umma_kernel<EPI_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_kernel<EPI_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_kernel<EPI_ADD_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_kernel<EPI_SIGMOID_MUL>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_kernel<EPI_ACCUM>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        return e;
+      });
       if (e != cudaSuccess) return e;
-      configured = smem;
     }
     int tile = p.MT * kTileM;
     dim3 grid((unsigned)((p.body + tile - 1) / tile), p.ngroups, 1);

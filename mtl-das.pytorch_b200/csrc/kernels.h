@@ -2,9 +2,35 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <mutex>
+
 #include "types.h"
 
 namespace mtldas {
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a property of (kernel, DEVICE): every launcher keeps one of these
+// tables per kernel family and raises the limit on the device that is current at the launch.  Safe under concurrent
+// launches from several host threads (distinct plans may run concurrently, include/mtldas.h).
+class PerDeviceSmem {
+ public:
+  template <class F>
+  cudaError_t ensure(size_t smem, F&& set_attr) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDev) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu_);
+    if (smem <= bytes_[dev]) return cudaSuccess;
+    e = set_attr((int)smem);
+    if (e == cudaSuccess) bytes_[dev] = smem;
+    return e;
+  }
+
+ private:
+  static constexpr int kMaxDev = 64;
+  std::mutex mu_;
+  size_t bytes_[kMaxDev] = {};
+};
 
 // precision: 0 = bf16 (tcgen05), 1 = fp32 (CUDA cores)
 cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream, bool pdl = false);

@@ -37,9 +37,14 @@ std::mutex g_scratch_mutex;
 int scratch_for_current_device(char** out) {
   int dev = -1;
   cudaError_t e = cudaGetDevice(&dev);
-  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
-    set_error("conv2d_nchw_static: cudaGetDevice failed or device ordinal out of range: %s", cudaGetErrorString(e));
+  if (e != cudaSuccess) {
+    set_error("conv2d_nchw_static: cudaGetDevice failed: %s", cudaGetErrorString(e));
     return MTLDAS_ERR_CUDA;
+  }
+  if (dev < 0 || dev >= kMaxDevices) {
+    set_error("conv2d_nchw_static: device ordinal %d is outside the %d ordinals this entry point keeps an address for", dev,
+              kMaxDevices);
+    return MTLDAS_ERR_UNSUPPORTED;
   }
   std::lock_guard<std::mutex> lock(g_scratch_mutex);
   if (!g_scratch_addr[dev]) {
@@ -107,7 +112,7 @@ extern "C" int mtldas_conv2d_nchw_static(const float* dev_x, const float* dev_x2
                                          int cin2, int h, int w, int cout, int ksize, int stride, int epilogue,
                                          int precision, int aux_phase_split, void* stream) {
   const bool has_aux = (epilogue == EPI_ADD_RELU || epilogue == EPI_SIGMOID_MUL);
-  if (!dev_x || !dev_weight || !dev_out || n < 1 || cin < 16 || (cin % 16) || (cin2 % 16) || (cout % 16) ||
+  if (!dev_x || !dev_weight || !dev_out || n < 1 || h < 1 || w < 1 || cin < 16 || (cin % 16) || (cin2 % 16) || (cout % 16) ||
       cout < 16 || cout > 256 || (ksize != 1 && ksize != 3) || (stride != 1 && stride != 2) || epilogue < 0 ||
       epilogue > 3 || precision < 0 || precision > 1 || (dev_x2 && !(ksize == 1 && stride == 1 && cin2 == cin)) ||
       (!dev_x2 && cin2) || (has_aux && !dev_aux)) {
@@ -199,6 +204,7 @@ extern "C" int mtldas_conv2d_nchw_static(const float* dev_x, const float* dev_x2
   q.MT = op.MT, q.SP = op.MT * kTileM + op.halo_lo + op.halo_hi;
   q.tps = op.tps, q.NS = op.NS, q.nstages = op.nstages, q.tap_bytes = op.tap_bytes, q.tmem_cols = op.tmem_cols;
   q.epi = epilogue, q.swap_desc = 0, q.ngroups = 1, q.dbg = nullptr, q.ksplit = op.ksplit;
+  q.persist_stages = persist_stages_for(op, 0);  // the kernel mtldas_conv2d_nchw picks for the same arguments
   q.magic_pimg = (1ull << 40) / (unsigned long long)q.Pimg + 1, q.magic_wp = (1ull << 40) / (unsigned long long)q.Wp + 1;
   for (int t = 0; t < op.ntaps; ++t) q.tap[t] = op.tap[t];
   ConvGroupDev& d = q.g[0];

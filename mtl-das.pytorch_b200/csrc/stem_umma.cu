@@ -215,11 +215,12 @@ cudaError_t launch_stem_umma(const StemParams& p, cudaStream_t stream, bool pdl)
   // bulk copies need 16-byte aligned spans: the patch tensor must start aligned and an image must be a multiple of 16 B
   if (p.Wp > 128 || smem > 225 * 1024 || (reinterpret_cast<uintptr_t>(p.x) & 15) || ((size_t)p.Hin * p.Win * 4) % 16)
     return cudaErrorInvalidValue;
-  static size_t configured = 0;
-  if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(stem_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  static PerDeviceSmem configured;
+  {
+    cudaError_t e = configured.ensure(smem, [](int bytes) {
+      return cudaFuncSetAttribute(stem_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    });
     if (e != cudaSuccess) return e;
-    configured = smem;
   }
   const int nb = (int)(p.body / p.Pimg);
   const int upi = (p.H + kStemRows - 1) / kStemRows, nunits = nb * upi;

@@ -12,6 +12,7 @@
 #include <cstdlib>
 
 #include "gran.cuh"
+#include "kernels.h"
 #include "ptx.cuh"
 #include "train_kernels.h"
 
@@ -428,11 +429,12 @@ static cudaError_t launch_wgrad_umma2(WgradParams p, cudaStream_t st, bool* hand
   const long long want = std::max<long long>(1, (long long)148 * resident / ngroups);
   const long long slice = std::max<long long>(512, (body16 + want - 1) / want);
   p.slice = (int)((slice + kWgStage - 1) / kWgStage * kWgStage);
-  static size_t configured = 0;
-  if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(wgrad_umma2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  static PerDeviceSmem configured;
+  {
+    cudaError_t e = configured.ensure(smem, [](int bytes) {
+      return cudaFuncSetAttribute(wgrad_umma2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    });
     if (e != cudaSuccess) return e;
-    configured = smem;
   }
   dim3 grid((unsigned)((body16 + p.slice - 1) / p.slice), ngroups);
   wgrad_umma2_kernel<<<grid, kWg2Threads, smem, st>>>(p);
@@ -460,11 +462,12 @@ static cudaError_t launch_wgrad_umma(WgradParams p, cudaStream_t st) {
   long long want = std::max<long long>(1, (long long)148 * resident / ngroups);
   long long slice = std::max<long long>(512, (body16 + want - 1) / want);
   p.slice = (int)((slice + kWgStage - 1) / kWgStage * kWgStage);
-  static size_t configured = 0;
-  if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  static PerDeviceSmem configured;
+  {
+    cudaError_t e = configured.ensure(smem, [](int bytes) {
+      return cudaFuncSetAttribute(wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    });
     if (e != cudaSuccess) return e;
-    configured = smem;
   }
   dim3 grid((unsigned)((body16 + p.slice - 1) / p.slice), ngroups);
   wgrad_umma_kernel<<<grid, 128, smem, st>>>(p);

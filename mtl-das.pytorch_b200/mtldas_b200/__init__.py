@@ -7,8 +7,10 @@ modelB_singleTask.py:53-178) while their compute runs in hand-written CUDA kerne
 There is no CPU fallback: without the built library and a B200 the compute calls raise.
 """
 from ._lib import lib, MtldasError, library_path  # noqa: F401
-from .engine import EvalPlan, TrainPlan, conv2d_nchw, conv2d_nchw_static, nll_loss, umma_selftest  # noqa: F401
+from .engine import (EvalPlan, TrainPlan, FlatAdam, EvalMetrics, conv2d_nchw, conv2d_nchw_static, nll_loss,  # noqa: F401
+                     umma_selftest)
 from .nets import MTL_Net, Single_Task_Net  # noqa: F401
 from . import synth  # noqa: F401
 
-__all__ = ["MTL_Net", "Single_Task_Net", "EvalPlan", "conv2d_nchw", "umma_selftest", "lib", "MtldasError"]
+__all__ = ["MTL_Net", "Single_Task_Net", "EvalPlan", "TrainPlan", "FlatAdam", "EvalMetrics", "conv2d_nchw", "umma_selftest",
+           "lib", "MtldasError"]

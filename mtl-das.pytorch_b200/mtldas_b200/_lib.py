@@ -54,6 +54,8 @@ def _load():
         "mtldas_train_describe": (sz, [vp, c.c_char_p, sz]),
         "mtldas_window_gather": (ci, [vp, c.c_longlong, c.c_longlong, ci, ci, ci, vp, vp]),
         "mtldas_nll_loss": (ci, [vp, vp, ci, vp, vp, vp, ci, vp, ci, vp, vp, vp]),
+        "mtldas_adam_step": (ci, [vp, vp, vp, vp, sz, ci, cf, cf, cf, cf, cf, vp]),
+        "mtldas_eval_metrics": (ci, [vp, vp, ci, vp, vp, vp, ci, vp, ci, vp, vp, vp, vp, vp]),
         "mtldas_umma_selftest": (cf, [ci, ci, ci]),
         "mtldas_umma_rate": (ci, [ci, ci, ci, c.POINTER(cf)]),
     }

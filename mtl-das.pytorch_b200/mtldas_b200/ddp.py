@@ -80,23 +80,56 @@ def flatten_parameters_(module) -> torch.nn.Parameter:
     return torch.nn.Parameter(flat, requires_grad=True)
 
 
+def broadcast_module_(module, group=None, src=0):
+    """Make every rank start from rank `src`'s parameters AND buffers (BatchNorm running statistics, counters), as torch
+    DDP does at construction: the reference builds its model with `MTL_Net()` (utils.py:87, per-process random init), so
+    without this the replicas would average gradients of different weights for ever."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) < 2:
+        return
+    with torch.no_grad():
+        for t in list(module.parameters()) + list(module.buffers()):
+            dist.broadcast(t.data, src=src, group=group)
+
+
+def replica_checksum(module, group=None):
+    """(max over ranks) - (min over ranks) of a checksum of all parameters: 0.0 when the replicas are identical.
+    One small all-reduce; used by bench.py and the multi-GPU tests after the timed steps."""
+    with torch.no_grad():
+        ps = [p.detach().double().reshape(-1) for p in module.parameters()]
+        flat = torch.cat(ps)
+        w = torch.arange(1, flat.numel() + 1, dtype=torch.float64, device=flat.device) % 1021.0 + 1.0
+        c = torch.stack(((flat * w).sum(), flat.abs().sum()))
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        hi, lo = c.clone(), c.clone()
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
+        return float((hi - lo).abs().max()), [float(v) for v in c]
+    return 0.0, [float(v) for v in c]
+
+
 class DataParallelTrainer:
     """One training step per call: shard -> forward/backward on the local plan -> one all-reduce -> optimizer.
 
     optimizer: a torch optimizer over module.parameters() (the reference's construction), or None together with
-    `flat_adam=dict(lr=..., weight_decay=...)` to flatten the parameters and step one fused Adam over the flat buffer."""
+    `flat_adam=dict(lr=..., weight_decay=...)` to flatten the parameters and step ONE Adam launch over the flat buffer
+    (mtldas_adam_step on a B200; torch.optim.Adam on the CPU, where only the host logic is exercised).
+    Construction broadcasts rank 0's parameters and buffers to every rank of `group`."""
 
-    def __init__(self, module, optimizer=None, group=None, flat_adam=None):
+    def __init__(self, module, optimizer=None, group=None, flat_adam=None, broadcast=True):
         self.module, self.optimizer, self.group = module, optimizer, group
         self._flat_param = None
+        if broadcast:
+            broadcast_module_(module, group)
         if optimizer is None:
             if flat_adam is None:
                 raise ValueError("give an optimizer or flat_adam=dict(lr=..., weight_decay=...)")
             self._flat_param = flatten_parameters_(module)
             kw = dict(flat_adam)
             if self._flat_param.is_cuda:
-                kw.setdefault("fused", True)
-            self.optimizer = torch.optim.Adam([self._flat_param], **kw)
+                from .engine import FlatAdam
+                self.optimizer = FlatAdam(self._flat_param, **kw)
+            else:
+                self.optimizer = torch.optim.Adam([self._flat_param], **kw)
         self.params = [p for _, p in module.named_parameters()]
         self._flat = None
         self._loss_bufs = None
@@ -116,11 +149,15 @@ class DataParallelTrainer:
         if self._flat is None or self._flat.device != x_local.device:
             self._flat = torch.empty(plan.n_params, dtype=torch.float32, device=x_local.device)
             if self._flat_param is not None:
-                self._flat_param.grad = self._flat  # one tensor, one fused optimizer launch
+                self._flat_param.grad = self._flat  # one tensor, one optimizer launch
             else:
                 for p, g in zip(self.params, unflatten_like(self._flat, self.params)):
                     p.grad = g                     # views of the flat buffer: bound once, refilled every step
         plan.backward(douts, self._flat)
         allreduce_mean_(self._flat, self.group)
         self.optimizer.step()
+        # parameters and BatchNorm buffers changed under the module (in-place kernels do not bump torch's version
+        # counters): the eval-mode weight image packed earlier is stale
+        if hasattr(m, "invalidate_packed"):
+            m.invalidate_packed()
         return loss

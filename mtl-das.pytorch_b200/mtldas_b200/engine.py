@@ -296,5 +296,104 @@ def nll_loss(logps, labels, want_grads=True, status=None, out=None):
     return loss, grads
 
 
+class FlatAdam:
+    """torch.optim.Adam(params, lr, weight_decay) of the reference trainer (utils.py:133-134,374) over ONE flat fp32
+    parameter buffer through mtldas_adam_step: L2 weight decay folded into the gradient, betas (0.9, 0.999), eps 1e-8,
+    bias correction; one launch per step.  `lr` is an attribute (the reference divides it by 1.5 every 5 epochs,
+    utils.py:245-247).  State (exp_avg, exp_avg_sq, step) lives here; state_dict()/load_state_dict() keep torch's names."""
+
+    def __init__(self, flat_param, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0):
+        if not (flat_param.is_cuda and flat_param.dtype == torch.float32 and flat_param.is_contiguous()):
+            raise MtldasError("FlatAdam needs one contiguous fp32 CUDA buffer (see ddp.flatten_parameters_)")
+        _require_b200(flat_param.device)
+        self.param = flat_param
+        self.lr, self.betas, self.eps, self.weight_decay = float(lr), (float(betas[0]), float(betas[1])), float(eps), float(weight_decay)
+        self.exp_avg = torch.zeros_like(flat_param.detach())
+        self.exp_avg_sq = torch.zeros_like(flat_param.detach())
+        self.step_count = 0
+
+    def zero_grad(self, set_to_none=False):
+        if self.param.grad is not None and not set_to_none:
+            self.param.grad.zero_()
+        elif set_to_none:
+            self.param.grad = None
+
+    def step(self, grad=None):
+        g = self.param.grad if grad is None else grad
+        if g is None:
+            raise MtldasError("FlatAdam.step: no gradient")
+        if not (g.is_cuda and g.dtype == torch.float32 and g.is_contiguous() and g.numel() == self.param.numel()):
+            raise MtldasError("FlatAdam.step: the gradient must be a contiguous fp32 CUDA buffer of the parameters' size")
+        self.step_count += 1
+        dev = self.param.device
+        with torch.cuda.device(dev):
+            check(lib.mtldas_adam_step(ctypes.c_void_p(self.param.data_ptr()), ctypes.c_void_p(g.data_ptr()),
+                                       ctypes.c_void_p(self.exp_avg.data_ptr()), ctypes.c_void_p(self.exp_avg_sq.data_ptr()),
+                                       self.param.numel(), self.step_count, self.lr, self.betas[0], self.betas[1], self.eps,
+                                       self.weight_decay, _stream_ptr(dev)), "adam_step")
+
+    def state_dict(self):
+        return {"step": self.step_count, "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq, "lr": self.lr}
+
+    def load_state_dict(self, sd):
+        self.step_count = int(sd["step"])
+        self.exp_avg.copy_(sd["exp_avg"])
+        self.exp_avg_sq.copy_(sd["exp_avg_sq"])
+        self.lr = float(sd.get("lr", self.lr))
+
+
+class EvalMetrics:
+    """Validation bookkeeping of utils.py:274-291,313 kept on the device (mtldas_eval_metrics): per-task NLL sums,
+    argmax predictions (first maximum wins, like torch.max), correct counts and confusion matrices accumulate over the
+    batches of an epoch; result() is the ONE device-to-host read (the reference syncs once per sample)."""
+
+    def __init__(self, classes=(16, 2), device=None):
+        self.classes = tuple(int(c) for c in classes)
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        _require_b200(self.device)
+        self.counts = torch.zeros(4, dtype=torch.int64, device=self.device)
+        self.loss_sums = torch.zeros(2, dtype=torch.float64, device=self.device)
+        self.confusion = [torch.zeros(c * c, dtype=torch.int64, device=self.device) for c in self.classes]
+        self.batches = 0
+        self.loss_mean_sums = torch.zeros(2, dtype=torch.float64, device=self.device)
+
+    def reset(self):
+        for t in (self.counts, self.loss_sums, self.loss_mean_sums, *self.confusion):
+            t.zero_()
+        self.batches = 0
+
+    def update(self, logps, labels, want_pred=False):
+        """logps: the module's outputs for one batch (fp32 [n, classes_t]); labels: int64 [n] per task."""
+        n = logps[0].shape[0]
+        for lp, y, c in zip(logps, labels, self.classes):
+            if not (lp.is_cuda and lp.dtype == torch.float32 and lp.is_contiguous() and lp.shape == (n, c)
+                    and y.dtype == torch.int64 and y.is_contiguous() and y.shape[0] == n and y.device == lp.device):
+                raise MtldasError("EvalMetrics.update needs contiguous fp32 [n, classes] log-probs and int64 [n] labels")
+        preds = [torch.empty(n, dtype=torch.int64, device=self.device) for _ in logps] if want_pred else [None] * len(logps)
+        p = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None  # noqa: E731
+        two = len(logps) > 1
+        before = self.loss_sums.clone()
+        with torch.cuda.device(self.device):
+            check(lib.mtldas_eval_metrics(p(logps[0]), p(labels[0]), self.classes[0], p(preds[0]),
+                                          p(logps[1]) if two else None, p(labels[1]) if two else None,
+                                          self.classes[1] if two else 0, p(preds[1]) if two else None, n,
+                                          p(self.counts), p(self.loss_sums), p(self.confusion[0]),
+                                          p(self.confusion[1]) if two else None, _stream_ptr(self.device)), "eval_metrics")
+        # the reference adds criterion(out, y) = the batch MEAN to testloss (utils.py:274-278): keep that sum as well
+        self.loss_mean_sums += (self.loss_sums - before) / max(n, 1)
+        self.batches += 1
+        return preds if want_pred else None
+
+    def result(self):
+        counts = self.counts.cpu().tolist()
+        seen = max(counts[2], 1)
+        out = {"seen": counts[2], "bad_labels": counts[3],
+               "accuracy": [counts[t] / seen for t in range(len(self.classes))],
+               "nll_mean": [float(v) / seen for v in self.loss_sums.cpu().tolist()][:len(self.classes)],
+               "sum_of_batch_means": self.loss_mean_sums.cpu().tolist()[:len(self.classes)],
+               "confusion": [m.view(c, c).cpu() for m, c in zip(self.confusion, self.classes)]}
+        return out
+
+
 def umma_selftest(n_cols=16, row_shift=0, swap=0):
     return float(lib.mtldas_umma_selftest(n_cols, row_shift, swap))

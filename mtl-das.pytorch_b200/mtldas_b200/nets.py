@@ -75,6 +75,18 @@ class _DasNet(nn.Module):
         self.micro_batch = int(os.environ.get("MTLDAS_MICRO_BATCH", "4096"))
 
     # ---- engine plumbing -------------------------------------------------------------------
+    def invalidate_packed(self):
+        """Forget the eval-mode weight images: the next eval forward folds BatchNorm and packs again.  Called whenever
+        state may have changed behind torch's version counters -- a training forward (the kernels update running_mean /
+        running_var / num_batches_tracked in place), an optimizer step over a flattened parameter buffer, and every
+        train -> eval switch (utils.py:249-250 follows utils.py:344 each epoch)."""
+        getattr(self, "_packed_sig", {}).clear()
+
+    def train(self, mode=True):
+        if bool(mode) != self.training:
+            self.invalidate_packed()
+        return super().train(mode)
+
     def _kind(self):
         return "MTL" if len(self.tasks) == 2 else "single_" + self.tasks[0]
 
@@ -123,12 +135,19 @@ class _TrainStep(torch.autograd.Function):
         plan = module._train_plan(x.device, x.shape[0])
         state = [v.detach() for v in module.state_dict(keep_vars=True).values()]
         outs = plan.forward(state, x)
-        ctx.plan, ctx.shapes = plan, [p.shape for p in params]
+        module.invalidate_packed()          # running statistics were updated in place
+        plan.forward_serial = getattr(plan, "forward_serial", 0) + 1
+        ctx.plan, ctx.shapes, ctx.serial = plan, [p.shape for p in params], plan.forward_serial
         ctx.mark_non_differentiable()
         return outs
 
     @staticmethod
     def backward(ctx, *douts):
+        if ctx.serial != ctx.plan.forward_serial:
+            # the plan keeps the activations of ONE forward; a later train-mode forward has overwritten them
+            raise MtldasError("backward of a stale forward: another train-mode forward of this module ran in between "
+                              "(the training plan holds the activations of the most recent forward only); call "
+                              "loss.backward() before the next model(x), as utils.py:359-373 does")
         flat = ctx.plan.backward(douts)
         grads, off = [], 0
         for shp in ctx.shapes:

@@ -70,6 +70,38 @@ def test_flat_gradient_allreduce_equals_mean_of_shard_gradients(tmp_path):
         assert res["ok"], res
 
 
+def _bcast_worker(rank, world, port, tmp):
+    sys.path[:0] = [ROOT, os.path.join(ROOT, "mtl-das.pytorch_b200")]
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from mtldas_b200.ddp import DataParallelTrainer, replica_checksum
+    torch.manual_seed(100 + rank)                      # the reference constructs MTL_Net() unseeded: ranks differ
+    m = torch.nn.Sequential(torch.nn.Conv2d(1, 4, 3), torch.nn.BatchNorm2d(4), torch.nn.Conv2d(4, 2, 1))
+    m[1].running_mean.add_(rank + 1.0)                 # buffers differ too
+    before, _ = replica_checksum(m)
+    tr = DataParallelTrainer(m, flat_adam=dict(lr=1e-3, weight_decay=1e-5))     # broadcasts rank 0's state
+    after, sums = replica_checksum(m)
+    rm = m[1].running_mean.clone()
+    dist.all_reduce(rm, op=dist.ReduceOp.MAX)
+    same_buffers = bool(torch.equal(rm, m[1].running_mean))
+    # one identical "gradient" step on every rank keeps the replicas identical
+    tr._flat_param.grad = torch.ones_like(tr._flat_param)
+    tr.optimizer.step()
+    final, _ = replica_checksum(m)
+    torch.save({"before": before, "after": after, "final": final, "same_buffers": same_buffers},
+               os.path.join(tmp, f"b{rank}.pt"))
+    dist.destroy_process_group()
+
+
+def test_trainer_construction_broadcasts_rank0_state(tmp_path):
+    """ranks built from different seeds must hold rank 0's parameters and buffers after construction."""
+    world, port = 2, 29300 + os.getpid() % 300
+    mp.spawn(_bcast_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    for r in range(world):
+        res = torch.load(os.path.join(str(tmp_path), f"b{r}.pt"))
+        assert res["before"] > 0 and res["after"] == 0.0 and res["final"] == 0.0 and res["same_buffers"], res
+
+
 def test_flat_parameter_adam_equals_per_tensor_adam():
     """flatten_parameters_ re-homes the parameters into one buffer (named_parameters order = flat-gradient order);
     Adam with L2 weight decay (utils.py:133-134) is elementwise, so stepping the flat tensor must give bit-identical
