@@ -52,21 +52,60 @@ def parse():
 # ------------------------------------------------------------------------------------------------
 # CPU arm: the oracle port on the host cores
 # ------------------------------------------------------------------------------------------------
+def find_reference():
+    """The unmodified reference tree, when this machine has it ($MTLDAS_REF, /root/reference, baseline/_ref).  It exists
+    in the build container only (a Python reference cannot travel to the GPU box), so on the box the CPU arm is the
+    oracle port: the same ATen CPU ops called from oracle/mtl_oracle.py."""
+    for cand in (os.environ.get("MTLDAS_REF"), "/root/reference", os.path.join(ROOT, "baseline", "_ref")):
+        if cand and os.path.isfile(os.path.join(cand, "model", "modelA_MTL.py")):
+            return cand
+    return None
+
+
+def cpu_model():
+    """(kind, eval_forward(x), train_step(x, yd, ye)) on the host cores; kind = "reference" | "port"."""
+    import torch
+    from oracle import mtl_oracle as O
+    sd = O.synth_state_dict("MTL", seed=0)
+    ref = find_reference()
+    if ref:
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("_reference_modelA_MTL", os.path.join(ref, "model", "modelA_MTL.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        net = mod.MTL_Net()
+        net.load_state_dict(sd, strict=True)
+        crit = torch.nn.NLLLoss()
+
+        def fwd(x):
+            net.eval()
+            return net(x)
+
+        def train(x, yd, ye):       # utils.py:344,359-373 without the optimizer
+            net.train()
+            net.zero_grad()
+            o1, o2 = net(x)
+            (crit(o1, yd.long()) + crit(o2, ye.long())).backward()
+        return "reference", fwd, train
+    return ("port", lambda x: O.forward(sd, x, "MTL", training=False),
+            lambda x, yd, ye: O.loss_and_grads(sd, x, yd, ye, "MTL"))
+
+
 def cpu_samples_per_s(sample, steps, warmup):
     import torch
     from oracle import mtl_oracle as O
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    sd = O.synth_state_dict("MTL", seed=0)
+    kind, fwd, _ = cpu_model()
     x, _, _ = O.synth_patches(sample, seed=1234)
     with torch.no_grad():
         for _ in range(warmup):
-            O.forward(sd, x, "MTL", training=False)
+            fwd(x)
         t0 = time.perf_counter()
         for _ in range(steps):
-            O.forward(sd, x, "MTL", training=False)
+            fwd(x)
         dt = time.perf_counter() - t0
-    return sample * steps / dt, dt / steps * 1e3, cores
+    return sample * steps / dt, dt / steps * 1e3, cores, kind
 
 
 def cpu_train_samples_per_s(batch, steps, warmup):
@@ -75,36 +114,37 @@ def cpu_train_samples_per_s(batch, steps, warmup):
     from oracle import mtl_oracle as O
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    sd = O.synth_state_dict("MTL", seed=0)
+    kind, _, train = cpu_model()
     x, yd, ye = O.synth_patches(batch, seed=1234)
     for _ in range(warmup):
-        O.loss_and_grads(sd, x, yd, ye, "MTL")
+        train(x, yd, ye)
     t0 = time.perf_counter()
     for _ in range(steps):
-        O.loss_and_grads(sd, x, yd, ye, "MTL")
+        train(x, yd, ye)
     dt = time.perf_counter() - t0
-    return batch * steps / dt, dt / steps * 1e3, cores
+    return batch * steps / dt, dt / steps * 1e3, cores, kind
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    val, ms, cores = cpu_samples_per_s(args.cpu_sample, args.steps, args.warmup)
-    sample = f"{args.cpu_sample} patches/step x {args.steps} steps, eval forward, torch CPU fp32, {cores} threads"
+    val, ms, cores, kind = cpu_samples_per_s(args.cpu_sample, args.steps, args.warmup)
+    what = "the reference's own MTL_Net (unmodified modules)" if kind == "reference" else "oracle port (same ATen CPU ops)"
+    sample = f"{args.cpu_sample} patches/step x {args.steps} steps, eval forward, torch CPU fp32, {cores} threads, {what}"
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": "MTL (model A) inference, synthetic DAS patches [1,100,250] (bounded CPU sample)",
                    "batch_per_step": args.cpu_sample},
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    tval, tms, _ = cpu_train_samples_per_s(32, max(2, min(args.steps, 5)), 1)
+    tval, tms, _, _ = cpu_train_samples_per_s(32, max(2, min(args.steps, 5)), 1)
     line["train"] = {"value": tval, "unit": UNIT, "ms_per_step": tms, "batch": 32,
-                     "what": "reference CPU training step fwd+bwd (BASELINE.json configs[0]), oracle port"}
+                     "what": "reference CPU training step fwd+bwd (BASELINE.json configs[0]), " + what}
     print(json.dumps(line), flush=True)
 
 
@@ -176,6 +216,26 @@ def conv_algorithmic_elems_per_sample(desc):
                 e += L["cin"] * hi * wi + L["cout"] * ho * wo
         per_op.append(e)
     return per_op
+
+
+def hbm_peak():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def profiled_traffic(version, batch, precision, passes):
+    """DRAM read+write bytes per conv launch from the committed `ncu --set full` summary (profiles/r2_traffic.json,
+    written by tools/ncu_traffic_summary.py).  Only trusted when it was captured on THIS build of the kernels and this
+    workload; otherwise null (the bench never prints a stale number)."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json")))
+    except Exception:
+        return None, None
+    if t.get("mtldas_version") != version or t.get("batch") != batch or t.get("precision") != precision or passes != 1:
+        return None, "profiles/r2_traffic.json is from build %r, batch %r: not this run" % (t.get("mtldas_version"), t.get("batch"))
+    return float(t["conv_dram_bytes_per_step"]) / float(t["conv_launches_per_step"]), t.get("source")
 
 
 def measure_extras(args, dev, world, rank, barrier):
@@ -292,7 +352,24 @@ def measure_train(args, dev, world, rank, barrier):
     if world > 1:
         dist.all_reduce(e2e, op=dist.ReduceOp.MAX)
     plan = m._train_plan(dev, nb)
+    # every rank must hold the same parameters after the timed steps (one all-reduced gradient, one optimizer rule)
+    from mtldas_b200.ddp import replica_checksum
+    spread, sums = replica_checksum(m)
+    if world > 1 and spread != 0.0:
+        raise SystemExit("bench: replicas diverged after %d training steps (checksum spread %g)" % (steps, spread))
+    step_s = float(ms.item()) * 1e-3 / steps
+    peak, peak_src = hbm_peak()
+    # BASELINE.md section 2 / SURVEY 8d, layer-fused byte model of one training step in bf16: 15.91 MB and
+    # 1299.56 MFLOP per sample -> bound 393 k samples/s per GPU at the measured peaks (HBM-bound at layer granularity)
+    tbytes = 15.91e6 * (2.0 if args.precision == "fp32" else 1.0) * nb
+    train_roof = {"bound": "hbm", "achieved": tbytes / step_s / 1e9, "peak": peak, "unit": "GB/s",
+                  "frac": tbytes / step_s / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                  "algorithmic_bytes_per_step": tbytes, "algorithmic_flop_per_step": 1299.56e6 * nb,
+                  "what": "whole training step (all launches) against the layer-fused byte model; at 256 patches per GPU "
+                          "every tensor is L2-resident, so this fraction measures launch-chain latency, not DRAM"}
     return {"value": world * nb * steps / (float(ms.item()) * 1e-3), "unit": UNIT, "ms_per_step": float(ms.item()) / steps,
+            "roofline": train_roof, "replica_checksum_spread": spread, "replica_checksum": sums,
+            "optimizer": "mtldas_adam_step (one launch over the flat parameter buffer)",
             "steps": steps, "batch_per_gpu": nb, "scaling": "weak",
             "step": "pack weights + forward (batch-stat BN) + backward + all-reduce + Adam",
             "allreduce_bytes_per_step": plan.n_params * 4 if world > 1 else 0,
@@ -393,6 +470,37 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_val = world * B * e2e_steps / float(e2e_s.item())
+    # the same with the patches already bf16 on the host (half the PCIe bytes; bit-identical log-probs)
+    e2e_bf16 = None
+    if args.precision == "bf16":
+        xh_host = x_host.to(torch.bfloat16).pin_memory()
+        for _ in range(2):
+            plan.forward_host(xh_host, outs_host)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            plan.forward_host(xh_host, outs_host)
+        barrier()
+        tb = torch.tensor([time.perf_counter() - t0], device=dev)
+        if world > 1:
+            dist.all_reduce(tb, op=dist.ReduceOp.MAX)
+        e2e_bf16 = {"value": world * B * e2e_steps / float(tb.item()), "unit": UNIT, "h2d_bytes_per_step": B * PATCH_BYTES // 2,
+                    "d2h_bytes_per_step": B * sum(plan.classes) * 4,
+                    "what": "mtldas_plan_forward_eval_host_bf16: host patches stored as bf16"}
+        del xh_host
+    # host-side bound: pinned host -> device copy rate of this rank while all ranks copy (max over ranks of the time)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        x.copy_(x_host, non_blocking=True)
+    barrier()
+    tc = torch.tensor([time.perf_counter() - t0], device=dev)
+    if world > 1:
+        dist.all_reduce(tc, op=dist.ReduceOp.MAX)
+    h2d_gbs = 3 * B * PATCH_BYTES / float(tc.item()) / 1e9
+    e2e_bound = {"h2d_gbs_per_rank": h2d_gbs, "samples_per_s_fp32_upload": world * h2d_gbs * 1e9 / PATCH_BYTES,
+                 "samples_per_s_bf16_upload": world * h2d_gbs * 1e9 / (PATCH_BYTES / 2),
+                 "what": "pinned host-to-device copy rate with all %d ranks copying at once: the ceiling of e2e" % world}
 
     # ---- live per-kernel durations for the roofline (CUDA events around every launch) --------------
     roof = None
@@ -404,21 +512,14 @@ def run_ours(args):
         conv_bytes = sum(elems) * B * (2 if args.precision == "bf16" else 4)
         passes = (B + args.micro_batch - 1) // args.micro_batch
         n_conv = sum(1 for op in desc["program"] if op["op"] == "conv") * passes
-        peak = 6650.0
-        peak_src = "fallback"
-        try:
-            peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
-            peak_src = "measured"
-        except Exception:
-            pass
+        peak, peak_src = hbm_peak()
         ach = conv_bytes / (conv_ms * 1e-3) / 1e9
-        # DRAM read+write bytes per conv launch from the ncu --set full pass over this workload
-        # (profiles/r1_conv_ncu_full_batch4096.txt: 15 330 MB over the 30 launches); other workloads: not captured
-        traffic = 15330e6 / 30 if (B == 4096 and args.precision == "bf16" and passes == 1) else None
+        from mtldas_b200 import lib
+        traffic, traffic_src = profiled_traffic(lib.mtldas_version().decode(), B, args.precision, passes)
         roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
-                "traffic_source": "profiles/r1_conv_ncu_full_batch4096.txt" if traffic else None,
+                "traffic_source": traffic_src,
                 "algorithmic_bytes_per_launch": conv_bytes / n_conv,
-                "kernel": "conv_umma_persist_kernel (+ conv_umma_kernel on the deep layers)" if args.precision == "bf16" else "conv_fp32_kernel",
+                "kernel": "conv_umma_persist_kernel (tcgen05 implicit GEMM; + conv_umma_kernel where weights stream)" if args.precision == "bf16" else "conv_fp32_kernel",
                 "launches_per_step": n_conv, "avg_launch_ms": conv_ms / n_conv,
                 "algorithmic_bytes_per_step": conv_bytes, "peak_source": peak_src,
                 "share_of_step": conv_ms / sum(per_op_ms),
@@ -442,7 +543,10 @@ def run_ours(args):
                        "parallelism": "batch-sharded x%d, no collective" % world,
                        "host_cpus_bound_per_rank": numa},
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": B * PATCH_BYTES,
-                    "d2h_bytes_per_step": B * sum(plan.classes) * 4},
+                    "d2h_bytes_per_step": B * sum(plan.classes) * 4,
+                    "what": "mtldas_plan_forward_eval_host: fp32 host patches (what the reference's DataLoader holds)"},
+            "e2e_bf16_upload": e2e_bf16,
+            "e2e_bound": e2e_bound,
             "gpu_launches": launches,
             "host_enqueue_ms_per_step": host_ms,
             "cuda_graph": os.environ.get("MTLDAS_NO_GRAPH", "0") != "1",
@@ -453,10 +557,15 @@ def run_ours(args):
         }
         if world == 1 and not args.no_cpu_baseline:
             steps = 16
-            val, cms, cores = cpu_samples_per_s(args.cpu_sample, steps, 2)
-            line["cpu_baseline"] = {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
-                                    "sample": f"{args.cpu_sample} patches/step x {steps} steps, eval forward, "
-                                              f"torch CPU fp32 oracle port, {cores} threads"}
+            val, cms, cores, kind = cpu_samples_per_s(args.cpu_sample, steps, 2)
+            line["cpu_baseline"] = {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
+                                    "sample": f"{args.cpu_sample} patches/step x {steps} steps, eval forward, torch CPU "
+                                              f"fp32 ({'reference modules' if kind == 'reference' else 'oracle port'}), "
+                                              f"{cores} threads"}
+            tval, tms, _, _ = cpu_train_samples_per_s(32, 4, 1)
+            line["train"]["cpu_baseline"] = {"value": tval, "unit": UNIT, "cores": cores, "kind": kind,
+                                             "sample": "32 patches/step x 4 steps, train-mode forward + NLL+NLL + backward "
+                                                       "(BASELINE.json configs[0]), torch CPU fp32, %d threads" % cores}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -100,6 +100,11 @@ MTLDAS_API int mtldas_plan_forward_eval(mtldas_plan* plan, const float* dev_x, i
  * utils.py:264-277.  Uses staging space inside the bound workspace; allocates nothing. */
 MTLDAS_API int mtldas_plan_forward_eval_host(mtldas_plan* plan, const float* host_x, int n, float* host_out0,
                                   float* host_out1, void* stream);
+/* The same with the host patches already in bfloat16 (raw 16-bit words, [n,1,100,250]): HALF the bytes over PCIe.
+ * The bf16 path rounds the patches to bf16 before its first MMA anyway, so for patches that are bf16-representable the
+ * results are bit-identical to mtldas_plan_forward_eval_host on the same values.  bf16 plans only. */
+MTLDAS_API int mtldas_plan_forward_eval_host_bf16(mtldas_plan* plan, const void* host_x_bf16, int n, float* host_out0,
+                                                  float* host_out1, void* stream);
 /* Instrumented forward for bench.py: same work as forward_eval with a CUDA-event pair around every launch;
  * host_ms_per_op[i] receives the device time of program op i (order of describe()'s "program") summed over
  * the micro-batch passes. Synchronises the stream. No reference counterpart (measurement only). */

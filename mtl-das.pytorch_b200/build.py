@@ -16,19 +16,35 @@ def needs_build():
         return True
     t = os.path.getmtime(OUT)
     for f in os.listdir(CSRC):
+        if not os.path.isfile(os.path.join(CSRC, f)):
+            continue
         if os.path.getmtime(os.path.join(CSRC, f)) > t:
             return True
     return os.path.getmtime(os.path.join(HERE, "..", "include", "mtldas.h")) > t
+
+
+def build_id():
+    """Short digest of every kernel source: mtldas_version() carries it, and profiles/r2_traffic.json is only trusted by
+    bench.py when it was captured on the same digest."""
+    import hashlib
+    h = hashlib.sha1()
+    for f in sorted(os.listdir(CSRC)) + [os.path.join("..", "..", "include", "mtldas.h")]:
+        if not os.path.isfile(os.path.join(CSRC, f)):
+            continue
+        with open(os.path.join(CSRC, f), "rb") as fh:
+            h.update(f.encode() + b"\0" + fh.read())
+    return h.hexdigest()[:10]
 
 
 def build(force=False, verbose=False):
     if not force and not needs_build():
         return OUT
     objs = []
+    bid = build_id()
     os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
     for s in SOURCES:
         o = os.path.join(HERE, "build", s + ".o")
-        cmd = ["nvcc", *FLAGS, "-c", os.path.join(CSRC, s), "-o", o]
+        cmd = ["nvcc", *FLAGS, f'-DMTLDAS_BUILD_ID="{bid}"', "-c", os.path.join(CSRC, s), "-o", o]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if verbose or r.returncode:
             sys.stderr.write(r.stdout + r.stderr)

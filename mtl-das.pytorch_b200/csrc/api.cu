@@ -16,7 +16,10 @@ struct mtldas_plan {
 
 extern "C" {
 
-const char* mtldas_version(void) { return "mtldas-b200 0.1 (sm_100a)"; }
+#ifndef MTLDAS_BUILD_ID
+#define MTLDAS_BUILD_ID "dev"
+#endif
+const char* mtldas_version(void) { return "mtldas-b200 0.2 (sm_100a) build " MTLDAS_BUILD_ID; }
 const char* mtldas_last_error(void) { return last_error_text(); }
 
 int mtldas_device_ok(void) {
@@ -128,13 +131,19 @@ int mtldas_plan_forward_eval(mtldas_plan* plan, const float* dev_x, int n, float
   return plan_forward_eval(*plan->p, dev_x, n, dev_out0, dev_out1, (cudaStream_t)stream);
 }
 
-int mtldas_plan_forward_eval_host(mtldas_plan* plan, const float* host_x, int n, float* host_out0, float* host_out1,
-                                  void* stream) {
-  if (!plan || !host_x || !host_out0 || n < 0) {
+static int forward_eval_host_impl(mtldas_plan* plan, const void* host_x_any, bool x_is_bf16, int n, float* host_out0,
+                                  float* host_out1, void* stream) {
+  if (!plan || !host_x_any || !host_out0 || n < 0) {
     set_error("forward_eval_host: bad arguments");
     return MTLDAS_ERR_ARG;
   }
+  const float* host_x = static_cast<const float*>(host_x_any);
+  const uint16_t* host_xh = static_cast<const uint16_t*>(host_x_any);
   Plan& p = *plan->p;
+  if (x_is_bf16 && p.precision != 0) {
+    set_error("forward_eval_host_bf16: bf16 patches are accepted by the bf16 plan only (the fp32 path keeps fp32 inputs)");
+    return MTLDAS_ERR_UNSUPPORTED;
+  }
   if (!p.ws || !p.packed) {
     set_error("forward_eval_host: bind a workspace and pack weights first");
     return MTLDAS_ERR_STATE;
@@ -147,6 +156,7 @@ int mtldas_plan_forward_eval_host(mtldas_plan* plan, const float* host_x, int n,
   float* o0[2] = {reinterpret_cast<float*>(p.ws + p.out_stage_off),
                   reinterpret_cast<float*>(p.ws + p.out_stage_off) + (size_t)chunk * 18};
   float* o1[2] = {o0[0] + (size_t)chunk * 16, o0[1] + (size_t)chunk * 16};
+  uint16_t* xh[2] = {reinterpret_cast<uint16_t*>(p.ws + p.xh_stage_off), reinterpret_cast<uint16_t*>(p.ws + p.xh_stage_off) + xslot};
 #define CKH(call)                                                        \
   do {                                                                   \
     cudaError_t e_ = (call);                                             \
@@ -163,10 +173,15 @@ int mtldas_plan_forward_eval_host(mtldas_plan* plan, const float* host_x, int n,
     const int nb = n - s < chunk ? n - s : chunk;
     const int slot = i & 1;
     if (i >= 2) CKH(cudaStreamWaitEvent(p.copy_stream, p.ev_comp[slot], 0));  // slot free again
-    CKH(cudaMemcpyAsync(xs[slot], host_x + (size_t)s * kPatchH * kPatchW, (size_t)nb * kPatchH * kPatchW * 4,
-                        cudaMemcpyHostToDevice, p.copy_stream));
+    if (x_is_bf16)   // half the bytes over PCIe; widened on the device (exact), the stem rounds to the same bf16 values
+      CKH(cudaMemcpyAsync(xh[slot], host_xh + (size_t)s * kPatchH * kPatchW, (size_t)nb * kPatchH * kPatchW * 2,
+                          cudaMemcpyHostToDevice, p.copy_stream));
+    else
+      CKH(cudaMemcpyAsync(xs[slot], host_x + (size_t)s * kPatchH * kPatchW, (size_t)nb * kPatchH * kPatchW * 4,
+                          cudaMemcpyHostToDevice, p.copy_stream));
     CKH(cudaEventRecord(p.ev_h2d[slot], p.copy_stream));
     CKH(cudaStreamWaitEvent(st, p.ev_h2d[slot], 0));
+    if (x_is_bf16) CKH(launch_widen_bf16(xh[slot], xs[slot], (long long)nb * kPatchH * kPatchW, st));
     int rc = plan_forward_eval(p, xs[slot], nb, o0[slot], c1 ? o1[slot] : nullptr, st);
     if (rc) return rc;
     launches += p.last_launches;
@@ -179,6 +194,16 @@ int mtldas_plan_forward_eval_host(mtldas_plan* plan, const float* host_x, int n,
   CKH(cudaStreamSynchronize(st));
 #undef CKH
   return 0;
+}
+
+int mtldas_plan_forward_eval_host(mtldas_plan* plan, const float* host_x, int n, float* host_out0, float* host_out1,
+                                  void* stream) {
+  return forward_eval_host_impl(plan, host_x, false, n, host_out0, host_out1, stream);
+}
+
+int mtldas_plan_forward_eval_host_bf16(mtldas_plan* plan, const void* host_x_bf16, int n, float* host_out0,
+                                       float* host_out1, void* stream) {
+  return forward_eval_host_impl(plan, host_x_bf16, true, n, host_out0, host_out1, stream);
 }
 
 int mtldas_plan_profile_eval(mtldas_plan* plan, const float* dev_x, int n, float* dev_out0, float* dev_out1,

@@ -351,4 +351,32 @@ cudaError_t launch_view_to_nchw(ActView v, float* nchw, int nb, int C, int H, in
   return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------------------
+// bf16 -> fp32 widening of host patches that came over PCIe as bf16 (mtldas_plan_forward_eval_host_bf16)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) widen_bf16_kernel(const uint4* __restrict__ in, float4* __restrict__ out, long long n8,
+                                                         const uint16_t* in_tail, float* out_tail, int tail) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    const uint4 q = in[i];
+    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) f[2 * j] = __uint_as_float(w[j] << 16), f[2 * j + 1] = __uint_as_float(w[j] & 0xffff0000u);
+    out[2 * i] = make_float4(f[0], f[1], f[2], f[3]);
+    out[2 * i + 1] = make_float4(f[4], f[5], f[6], f[7]);
+  }
+  if (blockIdx.x == 0 && (int)threadIdx.x < tail) out_tail[threadIdx.x] = __uint_as_float((uint32_t)in_tail[threadIdx.x] << 16);
+}
+
+cudaError_t launch_widen_bf16(const uint16_t* in, float* out, long long n, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  const long long n8 = n / 8;
+  const int tail = (int)(n - n8 * 8);
+  const int blocks = (int)std::min<long long>(148 * 8, std::max<long long>(1, (n8 + 255) / 256));
+  widen_bf16_kernel<<<blocks, 256, 0, stream>>>(reinterpret_cast<const uint4*>(in), reinterpret_cast<float4*>(out), n8,
+                                                in + n8 * 8, out + n8 * 8, tail);
+  return cudaGetLastError();
+}
+
 }  // namespace mtldas

@@ -47,6 +47,9 @@ cudaError_t launch_pack_batch(const PackParams* packs, int n, cudaStream_t strea
 cudaError_t launch_window_gather(const float* arr, long long n_time, int start0, int stride, int n_windows,
                                  int n_tblocks, float* out, cudaStream_t stream);
 
+// bf16 -> fp32 (exact) for host patches uploaded in half the bytes
+cudaError_t launch_widen_bf16(const uint16_t* in, float* out, long long n, cudaStream_t stream);
+
 // layout conversion (tests, debugging, and the autograd boundary): fp32 NCHW <-> P8 / P8S2 views
 cudaError_t launch_nchw_to_view(const float* nchw, ActView v, int nb, int C, int H, int W, int precision,
                                 cudaStream_t stream);

@@ -422,6 +422,7 @@ Plan* build_plan(int kind, int mb, int precision) {
   }
   p.x_stage_off = take((size_t)2 * p.host_chunk * kPatchH * kPatchW * 4);
   p.out_stage_off = take((size_t)2 * p.host_chunk * 18 * 4);
+  p.xh_stage_off = precision == 0 ? take((size_t)2 * p.host_chunk * kPatchH * kPatchW * 2) : 0;  // bf16 host patches
   p.ws_bytes = off;
   return pp;
 }

@@ -81,7 +81,7 @@ struct Plan {
   int stem_layer, stem_out;
   size_t stem_w_off, stem_b_off, stem_wu_off = 0;
   int use_umma_stem = 0;
-  size_t x_stage_off, out_stage_off;
+  size_t x_stage_off, out_stage_off, xh_stage_off = 0;
   int host_chunk = 0;
   size_t ws_bytes;
   char* ws = nullptr;

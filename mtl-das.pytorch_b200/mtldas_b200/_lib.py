@@ -36,6 +36,7 @@ def _load():
         "mtldas_plan_pack_eval": (ci, [vp, c.POINTER(vp), ci, vp]),
         "mtldas_plan_forward_eval": (ci, [vp, vp, ci, vp, vp, vp]),
         "mtldas_plan_forward_eval_host": (ci, [vp, vp, ci, vp, vp, vp]),
+        "mtldas_plan_forward_eval_host_bf16": (ci, [vp, vp, ci, vp, vp, vp]),
         "mtldas_plan_profile_eval": (ci, [vp, vp, ci, vp, vp, vp, c.POINTER(cf), ci]),
         "mtldas_plan_last_launch_count": (ci, [vp]),
         "mtldas_plan_read_tensor": (ci, [vp, c.c_char_p, ci, vp, vp]),

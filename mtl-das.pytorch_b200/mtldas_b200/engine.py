@@ -101,10 +101,13 @@ class EvalPlan:
     def forward_host(self, x_host, outs_host=None):
         """Host buffers in, host buffers out (H2D + forward + D2H + sync inside the call)."""
         n = x_host.shape[0]
+        if x_host.is_cuda or not x_host.is_contiguous() or x_host.dtype not in (torch.float32, torch.bfloat16):
+            raise MtldasError("forward_host takes a contiguous fp32 or bf16 HOST tensor [n,1,100,250]")
         if outs_host is None:
             outs_host = [torch.empty((n, c), dtype=torch.float32).pin_memory() for c in self.classes]
+        fn = lib.mtldas_plan_forward_eval_host_bf16 if x_host.dtype == torch.bfloat16 else lib.mtldas_plan_forward_eval_host
         with torch.cuda.device(self.device):
-            check(lib.mtldas_plan_forward_eval_host(self._h, ctypes.c_void_p(x_host.data_ptr()), n,
+            check(fn(self._h, ctypes.c_void_p(x_host.data_ptr()), n,
                                                     ctypes.c_void_p(outs_host[0].data_ptr()),
                                                     ctypes.c_void_p(outs_host[1].data_ptr()) if len(outs_host) > 1 else None,
                                                     _stream_ptr(self.device)), "forward_eval_host")
