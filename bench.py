@@ -208,8 +208,12 @@ def conv_algorithmic_elems_per_sample(desc):
             per_op.append(0)
             continue
         e = 0
+        seen = set()
         for g in op["groups"]:
             for s in g["segs"]:
+                if s["layer"] in seen:     # N-split groups of one reference conv: its input / output count once
+                    continue
+                seen.add(s["layer"])
                 L = layers[s["layer"]]
                 ho, wo = op["H"], op["W"]
                 hi, wi = (ho, wo) if L["stride"] == 1 else {17: (33, 83), 9: (17, 42), 5: (9, 21)}[ho]

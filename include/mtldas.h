@@ -54,6 +54,8 @@ extern "C" {
 #define MTLDAS_EPI_RELU 1        /* relu(y)                 modelA_MTL.py:16,47,102   */
 #define MTLDAS_EPI_ADD_RELU 2    /* relu(y + aux)           modelA_MTL.py:29-30       */
 #define MTLDAS_EPI_SIGMOID_MUL 3 /* sigmoid(y) * aux        modelA_MTL.py:50,144      */
+#define MTLDAS_EPI_RELU_POOL 5   /* maxpool2x2_ceil(relu(y)) modelA_MTL.py:102,116,145 (bf16 3x3/s1 only; out is
+                                    [n, cout, ceil(h/2), ceil(w/2)]; the full-resolution tensor is never written)     */
 
 typedef struct mtldas_plan mtldas_plan; /* opaque; not thread safe; distinct plans may run concurrently */
 

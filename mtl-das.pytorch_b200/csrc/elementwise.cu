@@ -216,11 +216,16 @@ __device__ __forceinline__ void pack_element(const PackParams& p, int i) {
   const int r1 = i - co * (s.cin * kk);
   const int ci = r1 / kk;
   const int rs = r1 - ci * kk;
+  int col = co;            // column inside this block's slice of the layer's output channels
+  if (s.co_n > 0 && !s.transpose && !s.k_from_tap) {
+    if (co < s.co_lo || co >= s.co_lo + s.co_n) return;
+    col = co - s.co_lo;
+  }
   float scale = 1.f;
   if (p.fold) scale = s.gamma[co] * rsqrtf(s.rvar[co] + p.eps);
   if (p.fold && r1 == 0) {
     float b = s.conv_bias ? s.conv_bias[co] : 0.f;
-    p.bias_dst[s.cout_off + co] = s.beta[co] + (b - s.rmean[co]) * scale;
+    p.bias_dst[s.cout_off + col] = s.beta[co] + (b - s.rmean[co]) * scale;
   }
   const float v = s.w[i] * scale;
   int tap = rs, k = ci, cop;
@@ -238,7 +243,7 @@ __device__ __forceinline__ void pack_element(const PackParams& p, int i) {
       k -= s.split;
     }
     k += s.k_off;
-    cop = s.cout_off + co;
+    cop = s.cout_off + col;
   }
   if (p.fp32) {
     reinterpret_cast<float*>(p.dst)[((size_t)tap * p.K_tap + k) * p.Cout_p + cop] = v;

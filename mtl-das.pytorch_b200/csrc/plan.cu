@@ -124,6 +124,9 @@ ActView Plan::view(int tensor, int chunk0) const {
 // conv op construction
 // ---------------------------------------------------------------------------------------------
 // shared-memory stages of the persistent kernel for this op (0 = not eligible); `extra` = bytes of other buffers
+// dynamic shared memory one CTA may own on sm_100 (227 KB) minus the kernel's header and alignment slack
+constexpr size_t kSmemOneCta = 232448 - 1280 - 384;
+
 int persist_stages_for(const ConvOpHost& op, size_t extra) {
   if (op.nstages != 1) return 0;
   const size_t SP = (size_t)op.MT * kTileM + op.halo_lo + op.halo_hi;
@@ -134,11 +137,11 @@ int persist_stages_for(const ConvOpHost& op, size_t extra) {
     env_stages = e ? atoi(e) : 3;
   }
   if (wb + (size_t)env_stages * slab + extra <= 108 * 1024) return env_stages;
-  if (wb + 2 * slab + extra <= 200 * 1024) return 2;
+  if (wb + 2 * ((slab + 127) & ~(size_t)127) + extra <= kSmemOneCta) return 2;
   return 0;
 }
 
-void choose_tiling(ConvOpHost& op, long long positions) {
+void choose_tiling(ConvOpHost& op, long long positions, bool small_resident) {
   op.tap_bytes = op.nchunks * 8 * op.Cout * 2;
   const int total_w = op.ntaps * op.tap_bytes;
   int MT = 4;
@@ -165,10 +168,12 @@ void choose_tiling(ConvOpHost& op, long long positions) {
     big_resident = (e && e[0] == '0') ? 0 : 1;
   }
   if (big_resident && slab + total_w > 96 * 1024) {
-    for (int m = 2; m >= 2; m >>= 1) {  // MT = 1 (64 -> 128 layers) measured slower than the ring kernel
+    // MT = 1 with full-width (128-column) weights measured slower than the ring kernel; the N-split halves
+    // (small_resident) are where one tile per iteration pays: their weights only fit next to single-tile slabs
+    for (int m = 2; m >= (small_resident ? 1 : 2); m >>= 1) {
       if (m > MT) continue;
-      const size_t sl = (size_t)op.nsrc * op.nchunks * (m * kTileM + op.halo_lo + op.halo_hi) * 16;
-      if ((size_t)total_w + 2 * sl <= 196 * 1024 && 2 * m * op.Cout <= 512) {
+      const size_t sl = ((size_t)op.nsrc * op.nchunks * (m * kTileM + op.halo_lo + op.halo_hi) * 16 + 127) & ~(size_t)127;
+      if ((size_t)total_w + 2 * sl <= kSmemOneCta && 2 * m * op.Cout <= 512) {
         MT = m, slab = sl;
         op.MT = MT, op.tps = op.ntaps, op.NS = 1, op.nstages = 1, op.ksplit = 0;
         int c = 32;
@@ -195,6 +200,40 @@ void choose_tiling(ConvOpHost& op, long long positions) {
   int cols = 32;
   while (cols < (op.ksplit ? 2 : 1) * MT * op.Cout) cols <<= 1;
   op.tmem_cols = cols;
+}
+
+// Layers whose packed weights cannot stay in shared memory (64->128 / 128->128: 147 / 295 KB) ran one tile per CTA
+// with the weights re-streamed from L2 per tile and load -> MMA -> epilogue back to back (0.13-0.37 of their roofline).
+// Splitting the OUTPUT channels into two groups halves the weight image per CTA, so each half stays resident and runs
+// the persistent pipelined kernel (epilogue of tile i under the MMAs of tile i+1).  The two halves of a tile run on
+// different CTAs at about the same time, so the second read of the input slab hits L2.  Cost: N = 64 instructions
+// are bound by the A-operand read (~45 cycles against 32 ideal), ~1.3x the tensor time of N = 128.
+bool split_output_channels(ConvOpHost& op, long long positions, bool even_if_resident) {
+  if ((op.nstages == 1 && !even_if_resident) || op.Cout < 128 || (op.Cout % 32) || op.ngroups * 2 > kMaxGroups) return false;
+  const int Cs = op.Cout / 2;
+  ConvOpHost s = op;
+  s.Cout = Cs, s.ngroups = op.ngroups * 2;
+  for (int g = 0; g < op.ngroups; ++g) {
+    if (op.g[g].aux_tensor >= 0 && op.g[g].aux_nchunks != op.Cout / 8) return false;
+    for (int half = 0; half < 2; ++half) {
+      ConvGroupHost ng = op.g[g];
+      ng.out_chunk0 += half * (Cs / 8);
+      if (ng.aux_tensor >= 0) ng.aux_chunk0 += half * (Cs / 8), ng.aux_nchunks = Cs / 8;
+      ng.segs.clear();
+      for (const PackSegHost& sg : op.g[g].segs) {
+        if (sg.layer < 0) continue;
+        // the caller's segs place whole layers; single-layer groups only (all candidates are)
+        PackSegHost h = sg;
+        h.co_lo = sg.co_lo + half * Cs, h.co_n = Cs;
+        ng.segs.push_back(h);
+      }
+      s.g[g * 2 + half] = ng;
+    }
+  }
+  choose_tiling(s, positions, /*small_resident=*/true);
+  if (s.nstages != 1 || persist_stages_for(s, 0) == 0) return false;
+  op = s;
+  return true;
 }
 
 namespace {
@@ -238,8 +277,12 @@ struct Builder {
     for (int s = 0; s < nsrc; ++s) op.tap[s] = ConvTapDev{s, 0};
     op.halo_lo = op.halo_hi = 0;
   }
-  void finish(ConvOpHost& op) {
-    choose_tiling(op, (long long)p.mb * (op.H + 1) * (op.W + 1));
+  void finish(ConvOpHost& op, bool tiled = false) {
+    const long long positions = (long long)p.mb * (op.H + 1) * (op.W + 1);
+    if (!tiled) {
+      choose_tiling(op, positions);
+      if (p.precision == 0 && !p.training && p.use_nsplit) split_output_channels(op, positions);
+    }
     p.convs.push_back(op);
     p.program.push_back(Op{1, (int)p.convs.size() - 1});
   }
@@ -250,10 +293,14 @@ struct Builder {
 };
 }  // namespace
 
-Plan* build_plan(int kind, int mb, int precision) {
+Plan* build_plan(int kind, int mb, int precision, bool training) {
   Plan* pp = new Plan();
   Plan& p = *pp;
-  p.kind = kind, p.mb = mb, p.precision = precision;
+  p.kind = kind, p.mb = mb, p.precision = precision, p.training = training;
+  {
+    const char* e = getenv("MTLDAS_NO_NSPLIT");
+    p.use_nsplit = !(e && e[0] == '1');
+  }
   p.ntasks = kind == 0 ? 2 : 1;
   p.gran = precision == 0 ? 16 : 32;
   build_layers(p);
@@ -380,14 +427,25 @@ Plan* build_plan(int kind, int mb, int precision) {
     }
     choose_tiling(op3);
     // bf16 inference: ReLU + 2x2 max-pool are fused into the conv epilogue (shared-memory staging tile) when the layer
-    // qualifies for the persistent kernel; the full-resolution tensor `o` is then never written
+    // qualifies for the persistent kernel; the full-resolution tensor `o` is then never written.  output_layer3 (64->128,
+    // 147 KB of weights per task) qualifies once its output channels are split into two groups (split_output_channels).
     const char* nofuse = getenv("MTLDAS_NO_POOL_FUSE");
-    const size_t staging = (size_t)(oc / 8) * op3.MT * kTileM * 16;
-    const bool fuse = precision == 0 && !(nofuse && nofuse[0] == '1') && persist_stages_for(op3, staging) > 0 &&
-                      (op3.MT * kTileM) / (2 * (W[l] + 1)) >= 1;
+    auto fusable = [&](const ConvOpHost& o) {
+      const size_t staging = (size_t)(o.Cout / 8) * o.MT * kTileM * 16;
+      return precision == 0 && !(nofuse && nofuse[0] == '1') && persist_stages_for(o, staging) > 0 &&
+             (o.MT * kTileM) / (2 * (W[l] + 1)) >= 1;
+    };
+    bool fuse = fusable(op3);
+    if (!fuse && precision == 0 && !training && p.use_nsplit) {
+      ConvOpHost sp = op3;
+      if (split_output_channels(sp, 0, /*even_if_resident=*/true) && fusable(sp)) op3 = sp, fuse = true;
+    }
     if (fuse)
-      for (int t = 0; t < T; ++t) op3.g[t].pool_tensor = pooled;
-    b.finish(op3);
+      for (int g = 0; g < op3.ngroups; ++g) op3.g[g].pool_tensor = pooled;
+    b.finish(op3, /*tiled=*/fuse);
+    if (!fuse) {
+      // (finish() tiles batch-aware and may still split the layer for the persistent kernel without the pool)
+    }
     if (!fuse) {
       p.pools.push_back(PoolOpHost{"pool" + std::to_string(l + 1), o, pooled});
       p.program.push_back(Op{2, (int)p.pools.size() - 1});
@@ -497,6 +555,7 @@ PackSeg make_seg(const Plan& p, const PackSegHost& h, const void* const* state) 
   s.rvar = (const float*)state[L.i_rv];
   s.cout = L.cout, s.cin = L.cin, s.ksize = L.ksize;
   s.split = h.split, s.k_off = h.k_off, s.cout_off = h.cout_off;
+  s.co_lo = h.co_lo, s.co_n = h.co_n;
   return s;
 }
 
@@ -761,10 +820,13 @@ int single_conv(const float* x, const float* x2, const float* weight, const floa
                 int precision, int aux_phase_split, int swap_desc) {
   if (n < 1 || (cin % 16) || (cin2 % 16) || (cout % 16) || cout > 256 || cin < 16 || (ksize != 1 && ksize != 3) ||
       (stride != 1 && stride != 2) || (x2 && !(ksize == 1 && stride == 1 && cin2 == cin)) || (!x2 && cin2) ||
-      ((epi == EPI_ADD_RELU || epi == EPI_SIGMOID_MUL) && !aux)) {
+      ((epi == EPI_ADD_RELU || epi == EPI_SIGMOID_MUL) && !aux) || epi < 0 || epi > 5 || epi == 4 ||
+      (epi == 5 && (precision != 0 || ksize != 3 || stride != 1))) {
     set_error("conv2d_nchw: unsupported arguments");
     return -1;
   }
+  const bool want_pool = epi == 5;   // MTLDAS_EPI_RELU_POOL: ReLU + MaxPool2d(2,2,ceil) fused into the epilogue
+  if (want_pool) epi = EPI_RELU;
   Plan p;
   p.kind = -1, p.mb = n, p.precision = precision, p.ntasks = 1, p.gran = precision == 0 ? 16 : 32;
   p.swap_desc = swap_desc;
@@ -774,6 +836,8 @@ int single_conv(const float* x, const float* x2, const float* weight, const floa
   int tin2 = x2 ? add_tensor(p, "x2", cin2, h, w, LAY_P8) : -1;
   int tout = add_tensor(p, "y", cout, Ho, Wo, LAY_P8);
   int taux = aux ? add_tensor(p, "aux", cout, Ho, Wo, aux_phase_split ? LAY_P8S2 : LAY_P8) : -1;
+  const int Hq = (Ho + 1) / 2, Wq = (Wo + 1) / 2;
+  int tpool = want_pool ? add_tensor(p, "yp", cout, Hq, Wq, LAY_P8) : -1;
   ConvOpHost op = b.base("conv", Ho, Wo, cout, cin / 8, epi, 1);
   if (ksize == 3 && stride == 1) {
     b.taps_3x3_s1(op);
@@ -792,6 +856,17 @@ int single_conv(const float* x, const float* x2, const float* weight, const floa
   op.g[0].out_tensor = tout;
   op.g[0].aux_tensor = taux;
   choose_tiling(op);
+  // the same re-grouping the inference plan applies (layers whose weights would not stay resident: N-split halves)
+  const char* nosplit = getenv("MTLDAS_NO_NSPLIT");
+  if (precision == 0 && !(nosplit && nosplit[0] == '1')) split_output_channels(op, 0, /*even_if_resident=*/want_pool && cout >= 128);
+  if (want_pool) {   // same eligibility rule as build_plan's output layers
+    const size_t staging = (size_t)(op.Cout / 8) * op.MT * kTileM * 16;
+    if (persist_stages_for(op, staging) == 0 || (op.MT * kTileM) / (2 * (Wo + 1)) < 1) {
+      set_error("conv2d_nchw: this shape does not qualify for the fused ReLU + max-pool epilogue");
+      return -4;
+    }
+    for (int gi = 0; gi < op.ngroups; ++gi) op.g[gi].pool_tensor = tpool;
+  }
   size_t off = 0;
   auto take = [&](size_t bytes) {
     size_t o = off;
@@ -799,9 +874,11 @@ int single_conv(const float* x, const float* x2, const float* weight, const floa
     return o;
   };
   for (auto& t : p.tensors) t.offset = take(t.bytes);
-  const size_t wbytes = (size_t)op.ntaps * op.nchunks * 8 * cout * (precision == 0 ? 2 : 4);
-  op.g[0].w_off = take(wbytes);
-  op.g[0].bias_off = take((size_t)cout * 4);
+  const size_t wbytes = (size_t)op.ntaps * op.nchunks * 8 * op.Cout * (precision == 0 ? 2 : 4);
+  for (int gi = 0; gi < op.ngroups; ++gi) {
+    op.g[gi].w_off = take(wbytes);
+    op.g[gi].bias_off = take((size_t)op.Cout * 4);
+  }
   CK(cudaMalloc(&p.ws, off));
   int rc = 0;
   do {
@@ -816,15 +893,20 @@ int single_conv(const float* x, const float* x2, const float* weight, const floa
     CKB(launch_nchw_to_view(x, p.view(tin, 0), n, cin, h, w, precision, 0));
     if (x2) CKB(launch_nchw_to_view(x2, p.view(tin2, 0), n, cin2, h, w, precision, 0));
     if (aux) CKB(launch_nchw_to_view(aux, p.view(taux, 0), n, cout, Ho, Wo, precision, 0));
-    PackParams q{};
-    q.seg.w = weight;
-    q.seg.cout = cout, q.seg.cin = cin + cin2, q.seg.ksize = ksize;
-    q.seg.split = x2 ? cin : INT_MAX;
-    q.dst = p.ws + op.g[0].w_off;
-    q.bias_dst = reinterpret_cast<float*>(p.ws + op.g[0].bias_off);
-    q.Cout_p = cout, q.K_tap = op.nchunks * 8, q.fp32 = precision == 0 ? 0 : 1, q.fold = 0, q.eps = 0.f;
-    CKB(launch_pack(q, 0));
-    if (bias) CKB(cudaMemcpy(p.ws + op.g[0].bias_off, bias, (size_t)cout * 4, cudaMemcpyDeviceToDevice));
+    for (int gi = 0; gi < op.ngroups && !rc; ++gi) {
+      PackParams q{};
+      q.seg.w = weight;
+      q.seg.cout = cout, q.seg.cin = cin + cin2, q.seg.ksize = ksize;
+      q.seg.split = x2 ? cin : INT_MAX;
+      if (op.ngroups > 1) q.seg.co_lo = gi * op.Cout, q.seg.co_n = op.Cout;
+      q.dst = p.ws + op.g[gi].w_off;
+      q.bias_dst = reinterpret_cast<float*>(p.ws + op.g[gi].bias_off);
+      q.Cout_p = op.Cout, q.K_tap = op.nchunks * 8, q.fp32 = precision == 0 ? 0 : 1, q.fold = 0, q.eps = 0.f;
+      CKB(launch_pack(q, 0));
+      if (bias)
+        CKB(cudaMemcpy(p.ws + op.g[gi].bias_off, bias + (size_t)gi * op.Cout, (size_t)op.Cout * 4, cudaMemcpyDeviceToDevice));
+    }
+    if (rc) break;
     ConvParams cp = p.conv_params(op, n);
     const char* dbg_env = getenv("MTLDAS_CONV_DEBUG");
     if (dbg_env && precision == 0) {
@@ -870,7 +952,11 @@ int single_conv(const float* x, const float* x2, const float* weight, const floa
       cp.dbg = nullptr;
     }
     CKB(launch_conv(cp, precision, 0));
-    CKB(launch_view_to_nchw(p.view(tout, 0), out, n, cout, Ho, Wo, precision, 0));
+    if (want_pool) {
+      CKB(launch_view_to_nchw(p.view(tpool, 0), out, n, cout, Hq, Wq, precision, 0));
+    } else {
+      CKB(launch_view_to_nchw(p.view(tout, 0), out, n, cout, Ho, Wo, precision, 0));
+    }
     CKB(cudaDeviceSynchronize());
 #undef CKB
   } while (0);
@@ -933,7 +1019,7 @@ std::string Plan::describe() const {
           const PackSegHost& s = g.segs[si];
           o << (si ? "," : "") << "{\"layer\":\"" << layers[s.layer].conv << "\",\"split\":"
             << (s.split == INT_MAX ? -1 : s.split) << ",\"k_off\":" << s.k_off << ",\"cout_off\":" << s.cout_off
-            << "}";
+            << ",\"co_lo\":" << s.co_lo << ",\"co_n\":" << s.co_n << "}";
         }
         o << "]}";
       }

@@ -38,6 +38,7 @@ struct SrcRef {
 struct PackSegHost {
   int layer;                  // index into layers
   int split, k_off, cout_off;
+  int co_lo = 0, co_n = 0;    // co_n > 0: only output channels [co_lo, co_lo+co_n) of the layer (N-split group)
 };
 struct ConvGroupHost {
   SrcRef src[kMaxSrc];
@@ -70,6 +71,8 @@ struct Op {
 
 struct Plan {
   int kind, mb, precision, ntasks;
+  bool training = false;   // plan built for the training program (no inference-only re-groupings)
+  bool use_nsplit = true;
   int gran;  // bytes per granule (16 bf16 / 32 fp32)
   std::vector<std::string> state_keys;
   std::vector<LayerSpec> layers;
@@ -114,10 +117,11 @@ struct Plan {
   std::string describe() const;
 };
 
-Plan* build_plan(int kind, int mb, int precision);
+Plan* build_plan(int kind, int mb, int precision, bool training = false);
 int add_tensor(Plan& p, const std::string& name, int C, int H, int W, int layout);
 PackSeg make_seg(const Plan& p, const PackSegHost& h, const void* const* state);
-void choose_tiling(ConvOpHost& op, long long positions = 0);  // positions > 0: batch-aware tile count
+void choose_tiling(ConvOpHost& op, long long positions = 0, bool small_resident = false);  // positions > 0: batch-aware tile count
+bool split_output_channels(ConvOpHost& op, long long positions, bool even_if_resident = false);  // N-split into two groups when that makes the weights resident
 int persist_stages_for(const ConvOpHost& op, size_t extra);
 int plan_pack_eval(Plan& p, const void* const* state, cudaStream_t stream);
 int plan_forward_eval(Plan& p, const float* x, int n, float* out0, float* out1, cudaStream_t stream);

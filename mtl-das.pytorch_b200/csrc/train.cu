@@ -111,7 +111,7 @@ static bool claim(TrainPlan& tp, int tensor, int chunk0, int nch, int phase) {
 TrainPlan* build_train_plan(int kind, int batch, int precision) {
   TrainPlan* tpp = new TrainPlan();
   TrainPlan& tp = *tpp;
-  tp.p = build_plan(kind, batch, precision);
+  tp.p = build_plan(kind, batch, precision, /*training=*/true);
   Plan& p = *tp.p;
   const int T = p.ntasks;
   const std::vector<Op> inf_prog = p.program;

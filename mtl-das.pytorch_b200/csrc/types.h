@@ -21,7 +21,7 @@ namespace mtldas {
 
 constexpr int kMaxSrc = 4;
 constexpr int kMaxTaps = 9;
-constexpr int kMaxGroups = 2;
+constexpr int kMaxGroups = 4;  // tasks x output-channel halves (N-split of layers whose weights would not stay resident)
 constexpr int kTileM = 128;
 constexpr int kMaxRing = 9;
 
@@ -124,6 +124,7 @@ struct PackSeg {           // one source layer scattered into a packed weight bl
   int transpose, ci_lo, ci_n;
   int tap_map[9];
   int k_from_tap;          // stem: the filter taps ARE the K dimension (k = r*ksize+s, single packed tap)
+  int co_lo, co_n;         // co_n > 0: only output channels [co_lo, co_lo+co_n) of the layer go into this block (N-split)
 };
 struct PackParams {
   PackSeg seg;

@@ -234,6 +234,8 @@ def conv2d_nchw(x, weight, bias=None, aux=None, x2=None, stride=1, epilogue=0, p
     cin2 = x2.shape[1] if x2 is not None else 0
     assert cin_tot == cin + cin2
     ho, wo = (h, w) if stride == 1 else ((h + 1) // 2, (w + 1) // 2)
+    if epilogue == 5:      # fused ReLU + MaxPool2d(2, 2, ceil_mode=True)
+        ho, wo = (ho + 1) // 2, (wo + 1) // 2
     out = torch.empty((n, cout, ho, wo), dtype=torch.float32, device=x.device)
     p = lambda t: ctypes.c_void_p(t.contiguous().data_ptr()) if t is not None else None  # noqa: E731
     keep = [t.contiguous().float() if t is not None else None for t in (x, x2, weight, bias, aux)]

@@ -35,6 +35,8 @@ class Emu:
         bias = torch.zeros(Cout, dtype=torch.float64)
         for s in g["segs"]:
             w, b = self.folded(s["layer"])
+            if s.get("co_n", 0) > 0:        # N-split group: a slice of the layer's output channels
+                w, b = w[s["co_lo"]:s["co_lo"] + s["co_n"]], b[s["co_lo"]:s["co_lo"] + s["co_n"]]
             co, ci, k, _ = w.shape
             for c in range(ci):
                 shift = 1 if (s["split"] >= 0 and c >= s["split"]) else 0

@@ -42,6 +42,30 @@ def _ref_conv(x, w, b, aux, x2, stride, epi, k):
     return y
 
 
+# fused ReLU + MaxPool2d(2,2,ceil) epilogue (output_layer1/2/3): odd H and W give the clipped last row / column windows
+POOL_CASES = [(16, 32, 33, 83), (32, 64, 17, 42), (64, 128, 9, 21)]
+
+
+@pytest.mark.parametrize("case", POOL_CASES, ids=lambda c: "c%d-%d_%dx%d" % c)
+def test_fused_relu_maxpool_epilogue_matches_torch(case):
+    """maxpool2x2_ceil(relu(conv3x3 + bias)) in ONE kernel (modelA_MTL.py:102,116,145) against torch on bf16-rounded
+    operands; 5 and 13 images (ragged last tiles: a tile is a whole number of image-row pairs)."""
+    from mtldas_b200 import conv2d_nchw
+    cin, cout, H, W = case
+    for n in (5, 13):
+        g = torch.Generator().manual_seed(cin * 7 + n)
+        x = torch.randn(n, cin, H, W, generator=g)
+        w = torch.randn(cout, cin, 3, 3, generator=g) / (3.0 * cin ** 0.5)
+        b = torch.randn(cout, generator=g) * 0.3
+        xr, wr = x.bfloat16().float(), w.bfloat16().float()
+        y = torch.relu(F.conv2d(xr.double(), wr.double(), b.double(), padding=1))
+        ref = F.max_pool2d(y, kernel_size=2, stride=2, ceil_mode=True)
+        out = conv2d_nchw(x.cuda(), w.cuda(), b.cuda(), epilogue=5, precision="bf16").cpu().double()
+        assert out.shape == ref.shape == (n, cout, (H + 1) // 2, (W + 1) // 2)
+        err = float((out - ref).abs().max() / ref.abs().max())
+        assert err <= 6e-3, (case, n, err)      # one bf16 rounding of the stored result
+
+
 def test_umma_descriptor_selftest():
     from mtldas_b200 import umma_selftest
     table = {}
