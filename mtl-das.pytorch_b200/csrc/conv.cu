@@ -134,6 +134,13 @@ __device__ __forceinline__ void epilogue_cols(const float* bias_s, int c0, bool 
   store8<T>(out_addr0 + (ch + 1) * out_plane_bytes, v + 8);
 }
 
+// relu + round-to-nearest bf16 of two floats in one instruction; lo lands in the low half (lower channel)
+__device__ __forceinline__ uint32_t relu_pack_bf16x2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+
 // ---- epilogues with a second operand (residual / feature map): the aux granules are fetched kAuxDepth blocks of
 // 16 channels ahead of the accumulator read, across accumulator-tile boundaries, and the first fetches are issued
 // BEFORE the wait for the accumulator -- otherwise every block pays a full L2 round trip between tcgen05.ld and the
@@ -514,6 +521,30 @@ __device__ __forceinline__ int fast_div(int f, unsigned long long magic) {
   return (int)(((unsigned long long)(unsigned)f * magic) >> 40);
 }
 
+// 32 accumulator columns of this thread's row, summed over the KS K-split partials
+__device__ __forceinline__ void load_acc32(uint32_t taddr, int KS, uint32_t part_cols, uint32_t* r) {
+  ptx::tmem_ld32_issue(taddr, r);
+  ptx::tmem_wait32(r);
+  for (int h = 1; h < KS; ++h) {
+    uint32_t r2[32];
+    ptx::tmem_ld32_issue(taddr + (uint32_t)h * part_cols, r2);
+    ptx::tmem_wait32(r2);
+#pragma unroll
+    for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
+  }
+}
+__device__ __forceinline__ void load_acc16(uint32_t taddr, int KS, uint32_t part_cols, uint32_t* r) {
+  ptx::tmem_ld16_issue(taddr, r);
+  ptx::tmem_wait16(r);
+  for (int h = 1; h < KS; ++h) {
+    uint32_t r2[16];
+    ptx::tmem_ld16_issue(taddr + (uint32_t)h * part_cols, r2);
+    ptx::tmem_wait16(r2);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
+  }
+}
+
 template <int EPI>
 __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(const __grid_constant__ ConvParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -533,7 +564,12 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
   const int tile_pos = p.pool_k > 0 ? 2 * p.Wp * p.pool_k : tile_rows;   // rows a tile advances by
   const int ntiles = (int)((p.body + tile_pos - 1) / tile_pos);
   uint8_t* staging = slabs + (size_t)p.persist_stages * slab_stride;     // fused max-pool: [chunk][tile_rows][16 B]
-  const uint32_t acc_cols = (uint32_t)(p.MT * p.Cout);
+  // K-split: the K steps of a tile rotate over KS accumulator partials (summed in the epilogue).  Back-to-back MMAs
+  // into ONE accumulator serialise on the accumulate latency (~135 cycles against ~45 per N <= 64 instruction), so a
+  // CTA wants MT * KS >= 4 independent chains.
+  const int KS = p.ksplit > 1 ? p.ksplit : 1;
+  const uint32_t part_cols = (uint32_t)(p.MT * p.Cout);            // one partial of all MT tiles
+  const uint32_t acc_cols = part_cols * (uint32_t)KS;              // one accumulator set
   const int nsets = p.acc_sets;                       // 1 or 2 TMEM accumulator sets
   const int nepi = (int)(blockDim.x >> 5) - 2;        // 4 or 8 epilogue warps
   uint32_t cols = 32;
@@ -610,15 +646,20 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
         // consecutive MMAs go to DIFFERENT accumulator tiles (mt innermost): back-to-back accumulation into the same
         // TMEM tile serialises on the accumulate latency, interleaving the MT tiles keeps the tensor pipe busy
         const uint32_t d_base = tmem_base + (uint32_t)a * acc_cols;
-        uint32_t acc = 0u, b_lo = w16;
+        uint32_t started = 0u, b_lo = w16;   // bit h of `started`: partial h already holds a product
+        int step = 0;
 #pragma unroll
         for (int t = 0; t < kMaxTaps; ++t) {
           if (t < ntaps) {
             uint32_t a_lo = slab16 + tap_off[t];
             for (int k = 0; k < KC2; ++k) {
+              const int h = step & (KS - 1);
+              const uint32_t d_part = d_base + (uint32_t)h * part_cols;
+              const uint32_t acc = (started >> h) & 1u;
               for (int mt = 0; mt < MT; ++mt)
-                ptx::umma_bf16(d_base + (uint32_t)(mt * Cout), a_hi | (a_lo + (uint32_t)(mt * kTileM)), b_hi | b_lo, idesc, acc);
-              acc = 1u;
+                ptx::umma_bf16(d_part + (uint32_t)(mt * Cout), a_hi | (a_lo + (uint32_t)(mt * kTileM)), b_hi | b_lo, idesc, acc);
+              started |= 1u << h;
+              ++step;
               a_lo += a_kstep;
               b_lo += b_kstep;
             }
@@ -644,6 +685,29 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
       m_per_chunk = (1ull << 40) / (unsigned long long)(p.pool_k * (Wp >> 1)) + 1;
       m_wph = (1ull << 40) / (unsigned long long)(Wp >> 1) + 1;
       m_hph = (1ull << 40) / (unsigned long long)((H + 1) >> 1) + 1;
+    }
+    // fused pool: the pooled items of this thread (chunk, row pair, column) are the same for every tile: their
+    // staging rows and output offsets are formed once, here
+    constexpr int kPoolItems = 4;
+    int pi_r0[kPoolItems], pi_rp[kPoolItems];
+    long long pi_base[kPoolItems];
+    int pi_n = 0;
+    const int pool_nthr = nepi * 32, pool_e = (warp - 2) * 32 + lane;
+    if (EPI == EPI_RELU && p.pool_k > 0) {
+      const int Wph = Wp >> 1, per_chunk = p.pool_k * Wph, total = per_chunk * (Cout >> 3);
+#pragma unroll
+      for (int k = 0; k < kPoolItems; ++k) {
+        const int o = pool_e + k * pool_nthr;
+        pi_r0[k] = -1, pi_rp[k] = 0, pi_base[k] = 0;
+        if (o < total) {
+          const int c = fast_div(o, m_per_chunk), q = o - c * per_chunk;
+          const int rp = fast_div(q, m_wph), cp = q - rp * Wph;
+          pi_r0[k] = c * tile_rows + 2 * rp * Wp + 2 * cp;    // granule index inside the staging tile
+          pi_rp[k] = rp | ((2 * rp * Wp + 2 * cp) << 8);       // row pair | row inside the tile (body check)
+          pi_base[k] = (long long)c * g.pool_out.plane + g.pool_out.g_lo + cp;
+          pi_n = k + 1;
+        }
+      }
     }
     int it = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
@@ -671,26 +735,42 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
         if (EPI == EPI_RELU && p.pool_k > 0) {
           // fused max-pool: relu(acc + bias) of this row goes to the shared-memory staging tile (zero at pads)
           const int row = mt * kTileM + quarter * 32 + lane;
-          for (int c0 = 0; c0 < Cout; c0 += 32) {  // Cout is a multiple of 32 on the pooled layers (32 / 64 / 128)
+          uint4* srow = reinterpret_cast<uint4*>(staging) + row;
+          for (int c0 = 0; c0 < Cout; c0 += 32) {  // Cout is a multiple of 32 on the pooled layers (32 / 64)
             uint32_t r[32];
             ptx::tmem_ld32_issue(trow + (uint32_t)c0, r);
+            if (mt == half && c0 == 0 && it > 0) {
+              // the staging tile is free once every epilogue thread has finished pooling the previous tile; waiting
+              // HERE (after the accumulator wait and under the TMEM load) hides the skew between the warps
+              asm volatile("bar.sync 2, %0;" ::"r"(pool_nthr) : "memory");
+            }
             ptx::tmem_wait32(r);
+            for (int h = 1; h < KS; ++h) {
+              uint32_t r2[32];
+              ptx::tmem_ld32_issue(trow + (uint32_t)h * part_cols + (uint32_t)c0, r2);
+              ptx::tmem_wait32(r2);
 #pragma unroll
-            for (int hlf = 0; hlf < 2; ++hlf) {
-              float v[16];
+              for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
+            }
 #pragma unroll
-              for (int j = 0; j < 16; ++j)
-                v[j] = valid ? fmaxf(__uint_as_float(r[hlf * 16 + j]) + bias_s[c0 + hlf * 16 + j], 0.f) : 0.f;
-              const int ch = (c0 >> 3) + 2 * hlf;
-              store8<__nv_bfloat16>(reinterpret_cast<char*>(staging) + ((size_t)ch * tile_rows + row) * 16, v);
-              store8<__nv_bfloat16>(reinterpret_cast<char*>(staging) + ((size_t)(ch + 1) * tile_rows + row) * 16, v + 8);
+            for (int gq = 0; gq < 4; ++gq) {     // four granules of 8 channels
+              uint4 q = make_uint4(0u, 0u, 0u, 0u);
+              if (valid) {
+                const float4 b0 = *reinterpret_cast<const float4*>(bias_s + c0 + gq * 8);
+                const float4 b1 = *reinterpret_cast<const float4*>(bias_s + c0 + gq * 8 + 4);
+                const uint32_t* rr = r + gq * 8;
+                q.x = relu_pack_bf16x2(__uint_as_float(rr[0]) + b0.x, __uint_as_float(rr[1]) + b0.y);
+                q.y = relu_pack_bf16x2(__uint_as_float(rr[2]) + b0.z, __uint_as_float(rr[3]) + b0.w);
+                q.z = relu_pack_bf16x2(__uint_as_float(rr[4]) + b1.x, __uint_as_float(rr[5]) + b1.y);
+                q.w = relu_pack_bf16x2(__uint_as_float(rr[6]) + b1.z, __uint_as_float(rr[7]) + b1.w);
+              }
+              srow[(size_t)((c0 >> 3) + gq) * tile_rows] = q;
             }
           }
         } else if (Cout >= 32) {
           for (int c0 = 0; c0 < Cout; c0 += 32) {
             uint32_t r[32];
-            ptx::tmem_ld32_issue(trow + (uint32_t)c0, r);
-            ptx::tmem_wait32(r);
+            load_acc32(trow + (uint32_t)c0, KS, part_cols, r);
             if (do_store) {
 #pragma unroll
               for (int hlf = 0; hlf < 2; ++hlf) {
@@ -704,8 +784,7 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
           }
         } else {
           uint32_t r[16];
-          ptx::tmem_ld16_issue(trow, r);
-          ptx::tmem_wait16(r);
+          load_acc16(trow, KS, part_cols, r);
           if (do_store) {
             float v[16];
 #pragma unroll
@@ -722,31 +801,33 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
       if (EPI == EPI_RELU && p.pool_k > 0) {
         // ---- fused MaxPool2d(2,2,ceil): the tile is pool_k image-row pairs; every pooled granule is the max of four
         // staged granules (pads were staged as zero, and post-ReLU values are >= 0, so clipped windows are correct)
-        const int nthr = nepi * 32, e = (warp - 2) * 32 + lane;
-        asm volatile("bar.sync 1, %0;" ::"r"(nthr) : "memory");
-        const int Wph = Wp >> 1, nch = Cout >> 3, per_chunk = p.pool_k * Wph;
+        asm volatile("bar.sync 1, %0;" ::"r"(pool_nthr) : "memory");      // staging complete
         const int hp_half = (H + 1) >> 1;                      // row pairs per image (Hp is even)
-        const ActView pv = g.pool_out;
-        for (int o = e; o < per_chunk * nch; o += nthr) {
-          const int c = fast_div(o, m_per_chunk), q = o - c * per_chunk;
-          const int rp = fast_div(q, m_wph), cp = q - rp * Wph;
-          const int r0 = 2 * rp * Wp + 2 * cp;                 // row in the staging tile
-          if ((long long)tile * tile_pos + r0 >= p.body) continue;
-          const uint4* sp = reinterpret_cast<const uint4*>(staging + ((size_t)c * tile_rows + r0) * 16);
-          uint4 m = sp[0];
-          const uint4 b1 = sp[1], b2 = sp[Wp], b3 = sp[Wp + 1];
-          __nv_bfloat162* mm = reinterpret_cast<__nv_bfloat162*>(&m);
-          const __nv_bfloat162* x1 = reinterpret_cast<const __nv_bfloat162*>(&b1);
-          const __nv_bfloat162* x2 = reinterpret_cast<const __nv_bfloat162*>(&b2);
-          const __nv_bfloat162* x3 = reinterpret_cast<const __nv_bfloat162*>(&b3);
+        const uint4* stg = reinterpret_cast<const uint4*>(staging);
+        const long long tile_first = (long long)tile * tile_pos;
+        uint4 v0[kPoolItems], v1[kPoolItems], v2[kPoolItems], v3[kPoolItems];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) mm[j] = __hmax2(__hmax2(mm[j], x1[j]), __hmax2(x2[j], x3[j]));
-          const int R = tile * p.pool_k + rp;                  // global row-pair index
-          const int n = fast_div(R, m_hph), ho = R - n * hp_half;
-          const long long pos = (long long)c * pv.plane + pv.g_lo + (long long)n * p.pool_Pimgo + ho * p.pool_Wpo + cp;
-          *reinterpret_cast<uint4*>(pv.base + pos * 16) = m;
+        for (int k = 0; k < kPoolItems; ++k) {
+          if (k < pi_n) {
+            const uint4* sp = stg + pi_r0[k];
+            v0[k] = sp[0], v1[k] = sp[1], v2[k] = sp[Wp], v3[k] = sp[Wp + 1];
+          }
         }
-        asm volatile("bar.sync 1, %0;" ::"r"(nthr) : "memory");  // staging is reused by the next tile
+#pragma unroll
+        for (int k = 0; k < kPoolItems; ++k) {
+          if (k < pi_n && tile_first + (pi_rp[k] >> 8) < p.body) {
+            uint4 m = v0[k];
+            __nv_bfloat162* mm = reinterpret_cast<__nv_bfloat162*>(&m);
+            const __nv_bfloat162* x1 = reinterpret_cast<const __nv_bfloat162*>(&v1[k]);
+            const __nv_bfloat162* x2 = reinterpret_cast<const __nv_bfloat162*>(&v2[k]);
+            const __nv_bfloat162* x3 = reinterpret_cast<const __nv_bfloat162*>(&v3[k]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) mm[j] = __hmax2(__hmax2(mm[j], x1[j]), __hmax2(x2[j], x3[j]));
+            const int R = tile * p.pool_k + (pi_rp[k] & 255);    // global row-pair index
+            const int n = fast_div(R, m_hph), ho = R - n * hp_half;
+            *reinterpret_cast<uint4*>(g.pool_out.base + (pi_base[k] + (long long)n * p.pool_Pimgo + ho * p.pool_Wpo) * 16) = m;
+          }
+        }
         if (dbg_on) p.dbg[it * 8 + 7] = clock64();
       }
     }
@@ -860,8 +941,21 @@ cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream,
     per_sm = std::max(per_sm, 1);
     ConvParams q = p;
     q.acc_sets = (per_sm * 2 * p.MT * p.Cout <= 512) ? 2 : 1;
+    // K-split partials: N <= 64 instructions issue every ~45 cycles but accumulate with ~135 cycles of latency, so a
+    // CTA wants four independent accumulator chains (two for N = 128); never more partials than K steps per tile
+    static int env_ks = -1;
+    if (env_ks < 0) {
+      const char* e = getenv("MTLDAS_PERSIST_KSPLIT");
+      env_ks = e ? atoi(e) : 4;
+    }
+    int KS = 1;
+    const int want = p.Cout <= 64 ? 4 : 2, ksteps = p.ntaps * (p.nchunks >> 1);
+    while (p.MT * KS < want && KS * 2 <= env_ks && KS * 2 <= ksteps &&
+           per_sm * q.acc_sets * p.MT * p.Cout * KS * 2 <= 512)
+      KS *= 2;
+    q.ksplit = KS;
     uint32_t cols = 32;
-    while (cols < (uint32_t)(q.acc_sets * p.MT * p.Cout)) cols <<= 1;
+    while (cols < (uint32_t)(q.acc_sets * p.MT * p.Cout * KS)) cols <<= 1;
     per_sm = std::max(1, std::min(per_sm, (int)(512 / cols)));
     int ctas = std::min(ntiles, 148 * per_sm / std::max(1, p.ngroups));
     ctas = std::max(ctas, 1);
