@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=256, help="patches per CPU-baseline step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the model B / streaming side measurements")
+    ap.add_argument("--no-train", action="store_true", help="skip the training-step measurement (kernel tuning runs)")
     ap.add_argument("--train-batch", type=int, default=256, help="training patches per GPU per step")
     return ap.parse_args()
 
@@ -530,7 +531,7 @@ def run_ours(args):
                 "per_op_ms": {(op.get("name") or op["op"]) + f"#{i}": round(m, 4)
                               for i, (m, op) in enumerate(zip(per_op_ms, desc["program"]))}}
 
-    train = measure_train(args, dev, world, rank, barrier)
+    train = measure_train(args, dev, world, rank, barrier) if not args.no_train else None
     extras = measure_extras(args, dev, world, rank, barrier) if not args.no_extras else None
 
     if rank == 0:
@@ -567,9 +568,11 @@ def run_ours(args):
                                               f"fp32 ({'reference modules' if kind == 'reference' else 'oracle port'}), "
                                               f"{cores} threads"}
             tval, tms, _, _ = cpu_train_samples_per_s(32, 4, 1)
-            line["train"]["cpu_baseline"] = {"value": tval, "unit": UNIT, "cores": cores, "kind": kind,
-                                             "sample": "32 patches/step x 4 steps, train-mode forward + NLL+NLL + backward "
-                                                       "(BASELINE.json configs[0]), torch CPU fp32, %d threads" % cores}
+            if line["train"] is not None:
+                line["train"]["cpu_baseline"] = {
+                    "value": tval, "unit": UNIT, "cores": cores, "kind": kind,
+                    "sample": "32 patches/step x 4 steps, train-mode forward + NLL+NLL + backward "
+                              "(BASELINE.json configs[0]), torch CPU fp32, %d threads" % cores}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -134,13 +134,6 @@ __device__ __forceinline__ void epilogue_cols(const float* bias_s, int c0, bool 
   store8<T>(out_addr0 + (ch + 1) * out_plane_bytes, v + 8);
 }
 
-// relu + round-to-nearest bf16 of two floats in one instruction; lo lands in the low half (lower channel)
-__device__ __forceinline__ uint32_t relu_pack_bf16x2(float lo, float hi) {
-  uint32_t r;
-  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
-  return r;
-}
-
 // ---- epilogues with a second operand (residual / feature map): the aux granules are fetched kAuxDepth blocks of
 // 16 channels ahead of the accumulator read, across accumulator-tile boundaries, and the first fetches are issued
 // BEFORE the wait for the accumulator -- otherwise every block pays a full L2 round trip between tcgen05.ld and the
@@ -353,13 +346,13 @@ __global__ void __launch_bounds__(256) conv_umma_kernel(const __grid_constant__ 
         for (int mt = 0; mt < MT; ++mt) {
           const uint32_t d_tmem = tmem_base + (uint32_t)(mt * Cout);
           uint32_t acc = 0u;
-          uint32_t b_lo = wring16;
+          uint32_t b_lo = wring16 | (uint32_t)b_hi;
 #pragma unroll
           for (int t = 0; t < kMaxTaps; ++t) {
             if (t < ntaps) {
-              uint32_t a_lo = slab16 + tap_off[t] + (uint32_t)(mt * kTileM);
+              uint32_t a_lo = (slab16 + tap_off[t] + (uint32_t)(mt * kTileM)) | (uint32_t)a_hi;
               for (int k = 0; k < KC2; ++k) {
-                ptx::umma_bf16(d_tmem, a_hi | a_lo, b_hi | b_lo, idesc, acc);
+                ptx::umma_bf16_lean(d_tmem, a_lo, (uint32_t)(a_hi >> 32), b_lo, (uint32_t)(b_hi >> 32), idesc, acc);
                 acc = 1u;
                 a_lo += a_kstep;
                 b_lo += b_kstep;
@@ -374,6 +367,8 @@ __global__ void __launch_bounds__(256) conv_umma_kernel(const __grid_constant__ 
         // (back-to-back accumulation into one tile serialises on the accumulate latency).
         uint32_t acc0 = 0u, acc1 = 0u;
         const uint32_t set1 = p.ksplit ? (uint32_t)(MT * Cout) : 0u;
+        const int nchunks_r = p.nchunks, halo_lo_r = p.halo_lo;
+        const bool ksplit_r = p.ksplit != 0;
         for (int st = 0; st < p.nstages; ++st) {
           const int slot = st % p.NS;
           ptx::mbar_wait(bars + kBarWFull + slot, (st / p.NS) & 1);
@@ -382,14 +377,21 @@ __global__ void __launch_bounds__(256) conv_umma_kernel(const __grid_constant__ 
           const int ntap = min(p.tps, ntaps - st * p.tps);
           for (int ti = 0; ti < ntap; ++ti) {
             const ConvTapDev tp = p.tap[st * p.tps + ti];
-            uint32_t a_lo = slab16 + (uint32_t)(tp.src * p.nchunks) * chunk16 + (uint32_t)(p.halo_lo + tp.off);
-            uint32_t b_lo = wring16 + (uint32_t)slot * stage16 + (uint32_t)ti * tap16;
+            uint32_t a_lo = (slab16 + (uint32_t)(tp.src * nchunks_r) * chunk16 + (uint32_t)(halo_lo_r + tp.off)) | (uint32_t)a_hi;
+            uint32_t b_lo = (wring16 + (uint32_t)slot * stage16 + (uint32_t)ti * tap16) | (uint32_t)b_hi;
+            const uint32_t a_hh = (uint32_t)(a_hi >> 32), b_hh = (uint32_t)(b_hi >> 32);
             for (int k = 0; k < KC2; ++k) {
-              const bool odd = p.ksplit && (k & 1);
+              const bool odd = ksplit_r && (k & 1);
               const uint32_t d0 = tmem_base + (odd ? set1 : 0u);
               const uint32_t acc = odd ? acc1 : acc0;
-              for (int mt = 0; mt < MT; ++mt)
-                ptx::umma_bf16(d0 + (uint32_t)(mt * Cout), a_hi | (a_lo + (uint32_t)(mt * kTileM)), b_hi | b_lo, idesc, acc);
+              if (MT == 4) {
+#pragma unroll
+                for (int mt = 0; mt < 4; ++mt)
+                  ptx::umma_bf16_lean(d0 + (uint32_t)(mt * Cout), a_lo + (uint32_t)(mt * kTileM), a_hh, b_lo, b_hh, idesc, acc);
+              } else {
+                for (int mt = 0; mt < MT; ++mt)
+                  ptx::umma_bf16_lean(d0 + (uint32_t)(mt * Cout), a_lo + (uint32_t)(mt * kTileM), a_hh, b_lo, b_hh, idesc, acc);
+              }
               if (odd) acc1 = 1u; else acc0 = 1u;
               a_lo += a_kstep;
               b_lo += b_kstep;
@@ -521,7 +523,41 @@ __device__ __forceinline__ int fast_div(int f, unsigned long long magic) {
   return (int)(((unsigned long long)(unsigned)f * magic) >> 40);
 }
 
-// 32 accumulator columns of this thread's row, summed over the KS K-split partials
+// All MMAs of one tile set (MT accumulator tiles x taps x K steps), issued by ONE thread.  The issue loop used to cost
+// ~100 cycles per MMA (kernel timeline, round 2): about forty uniform-datapath instructions per K step, parameter
+// re-loads after every MMA (the asm's memory clobber) and R2UR moves of loop bounds -- twice the tensor pipe's own
+// 45-64 cycles.  Here MT is a compile-time constant (the mt loop is fully unrolled), the descriptors are 32-bit
+// running sums, and nothing is read from memory inside the loop.
+template <int MT_, int KS_>
+__device__ __forceinline__ void issue_tile_mmas(uint32_t d_base, uint32_t part_cols, uint32_t slab16,
+                                                const uint32_t (&tap_off)[kMaxTaps], int ntaps, int KC2, uint32_t Cout,
+                                                uint32_t a_hi_lo, uint32_t a_hi_hi, uint32_t b_hi_lo, uint32_t b_hi_hi,
+                                                uint32_t w16, uint32_t a_kstep, uint32_t b_kstep, uint32_t idesc) {
+  // KS_ > 1: the K steps rotate over KS_ accumulator partials (summed in the epilogue): back-to-back MMAs into ONE
+  // accumulator serialise on the accumulate latency (~150 cycles measured for M128 N64 against ~45 of issue), so a
+  // CTA wants MT_ * KS_ >= 4 independent chains
+  uint32_t started = 0u, b_lo = w16 | b_hi_lo, step = 0u;
+#pragma unroll
+  for (int t = 0; t < kMaxTaps; ++t) {
+    if (t < ntaps) {
+      uint32_t a_lo = (slab16 + tap_off[t]) | a_hi_lo;   // start address < 2^14: the OR never carries into the LBO field
+      for (int k = 0; k < KC2; ++k) {
+        const uint32_t h = KS_ > 1 ? (step & (uint32_t)(KS_ - 1)) : 0u;
+        const uint32_t acc = (started >> h) & 1u;
+        const uint32_t d = d_base + h * part_cols;
+#pragma unroll
+        for (int mt = 0; mt < MT_; ++mt)
+          ptx::umma_bf16_lean(d + (uint32_t)mt * Cout, a_lo + (uint32_t)(mt * kTileM), a_hi_hi, b_lo, b_hi_hi, idesc, acc);
+        started |= 1u << h;
+        ++step;
+        a_lo += a_kstep;
+        b_lo += b_kstep;
+      }
+    }
+  }
+}
+
+// 32 / 16 accumulator columns of this thread's row, summed over the KS K-split partials
 __device__ __forceinline__ void load_acc32(uint32_t taddr, int KS, uint32_t part_cols, uint32_t* r) {
   ptx::tmem_ld32_issue(taddr, r);
   ptx::tmem_wait32(r);
@@ -564,10 +600,7 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
   const int tile_pos = p.pool_k > 0 ? 2 * p.Wp * p.pool_k : tile_rows;   // rows a tile advances by
   const int ntiles = (int)((p.body + tile_pos - 1) / tile_pos);
   uint8_t* staging = slabs + (size_t)p.persist_stages * slab_stride;     // fused max-pool: [chunk][tile_rows][16 B]
-  // K-split: the K steps of a tile rotate over KS accumulator partials (summed in the epilogue).  Back-to-back MMAs
-  // into ONE accumulator serialise on the accumulate latency (~135 cycles against ~45 per N <= 64 instruction), so a
-  // CTA wants MT * KS >= 4 independent chains.
-  const int KS = p.ksplit > 1 ? p.ksplit : 1;
+  const int KS = p.ksplit > 1 ? p.ksplit : 1;                      // K-split partials per accumulator tile (launcher)
   const uint32_t part_cols = (uint32_t)(p.MT * p.Cout);            // one partial of all MT tiles
   const uint32_t acc_cols = part_cols * (uint32_t)KS;              // one accumulator set
   const int nsets = p.acc_sets;                       // 1 or 2 TMEM accumulator sets
@@ -646,25 +679,17 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
         // consecutive MMAs go to DIFFERENT accumulator tiles (mt innermost): back-to-back accumulation into the same
         // TMEM tile serialises on the accumulate latency, interleaving the MT tiles keeps the tensor pipe busy
         const uint32_t d_base = tmem_base + (uint32_t)a * acc_cols;
-        uint32_t started = 0u, b_lo = w16;   // bit h of `started`: partial h already holds a product
-        int step = 0;
-#pragma unroll
-        for (int t = 0; t < kMaxTaps; ++t) {
-          if (t < ntaps) {
-            uint32_t a_lo = slab16 + tap_off[t];
-            for (int k = 0; k < KC2; ++k) {
-              const int h = step & (KS - 1);
-              const uint32_t d_part = d_base + (uint32_t)h * part_cols;
-              const uint32_t acc = (started >> h) & 1u;
-              for (int mt = 0; mt < MT; ++mt)
-                ptx::umma_bf16(d_part + (uint32_t)(mt * Cout), a_hi | (a_lo + (uint32_t)(mt * kTileM)), b_hi | b_lo, idesc, acc);
-              started |= 1u << h;
-              ++step;
-              a_lo += a_kstep;
-              b_lo += b_kstep;
-            }
-          }
-        }
+        const uint32_t ah_lo = (uint32_t)a_hi, ah_hi = (uint32_t)(a_hi >> 32), bh_lo = (uint32_t)b_hi, bh_hi = (uint32_t)(b_hi >> 32);
+#define MTLDAS_ISSUE(M_, K_)                                                                                           \
+  issue_tile_mmas<M_, K_>(d_base, part_cols, slab16, tap_off, ntaps, KC2, (uint32_t)Cout, ah_lo, ah_hi, bh_lo, bh_hi, w16, \
+                          a_kstep, b_kstep, idesc)
+        if (MT == 4) MTLDAS_ISSUE(4, 1);
+        else if (MT == 2 && KS == 1) MTLDAS_ISSUE(2, 1);
+        else if (MT == 2) MTLDAS_ISSUE(2, 2);
+        else if (KS == 1) MTLDAS_ISSUE(1, 1);
+        else if (KS == 2) MTLDAS_ISSUE(1, 2);
+        else MTLDAS_ISSUE(1, 4);
+#undef MTLDAS_ISSUE
         ptx::umma_commit(bars + kPBarSlabEmpty + s);
         ptx::umma_commit(bars + kPBarAccFull + a);
         if (dbg_on) p.dbg[it * 8 + 3] = clock64();
@@ -685,29 +710,6 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
       m_per_chunk = (1ull << 40) / (unsigned long long)(p.pool_k * (Wp >> 1)) + 1;
       m_wph = (1ull << 40) / (unsigned long long)(Wp >> 1) + 1;
       m_hph = (1ull << 40) / (unsigned long long)((H + 1) >> 1) + 1;
-    }
-    // fused pool: the pooled items of this thread (chunk, row pair, column) are the same for every tile: their
-    // staging rows and output offsets are formed once, here
-    constexpr int kPoolItems = 4;
-    int pi_r0[kPoolItems], pi_rp[kPoolItems];
-    long long pi_base[kPoolItems];
-    int pi_n = 0;
-    const int pool_nthr = nepi * 32, pool_e = (warp - 2) * 32 + lane;
-    if (EPI == EPI_RELU && p.pool_k > 0) {
-      const int Wph = Wp >> 1, per_chunk = p.pool_k * Wph, total = per_chunk * (Cout >> 3);
-#pragma unroll
-      for (int k = 0; k < kPoolItems; ++k) {
-        const int o = pool_e + k * pool_nthr;
-        pi_r0[k] = -1, pi_rp[k] = 0, pi_base[k] = 0;
-        if (o < total) {
-          const int c = fast_div(o, m_per_chunk), q = o - c * per_chunk;
-          const int rp = fast_div(q, m_wph), cp = q - rp * Wph;
-          pi_r0[k] = c * tile_rows + 2 * rp * Wp + 2 * cp;    // granule index inside the staging tile
-          pi_rp[k] = rp | ((2 * rp * Wp + 2 * cp) << 8);       // row pair | row inside the tile (body check)
-          pi_base[k] = (long long)c * g.pool_out.plane + g.pool_out.g_lo + cp;
-          pi_n = k + 1;
-        }
-      }
     }
     int it = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
@@ -735,36 +737,18 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
         if (EPI == EPI_RELU && p.pool_k > 0) {
           // fused max-pool: relu(acc + bias) of this row goes to the shared-memory staging tile (zero at pads)
           const int row = mt * kTileM + quarter * 32 + lane;
-          uint4* srow = reinterpret_cast<uint4*>(staging) + row;
-          for (int c0 = 0; c0 < Cout; c0 += 32) {  // Cout is a multiple of 32 on the pooled layers (32 / 64)
+          for (int c0 = 0; c0 < Cout; c0 += 32) {  // Cout is a multiple of 32 on the pooled layers (32 / 64 / 128)
             uint32_t r[32];
-            ptx::tmem_ld32_issue(trow + (uint32_t)c0, r);
-            if (mt == half && c0 == 0 && it > 0) {
-              // the staging tile is free once every epilogue thread has finished pooling the previous tile; waiting
-              // HERE (after the accumulator wait and under the TMEM load) hides the skew between the warps
-              asm volatile("bar.sync 2, %0;" ::"r"(pool_nthr) : "memory");
-            }
-            ptx::tmem_wait32(r);
-            for (int h = 1; h < KS; ++h) {
-              uint32_t r2[32];
-              ptx::tmem_ld32_issue(trow + (uint32_t)h * part_cols + (uint32_t)c0, r2);
-              ptx::tmem_wait32(r2);
+            load_acc32(trow + (uint32_t)c0, KS, part_cols, r);
 #pragma unroll
-              for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
-            }
+            for (int hlf = 0; hlf < 2; ++hlf) {
+              float v[16];
 #pragma unroll
-            for (int gq = 0; gq < 4; ++gq) {     // four granules of 8 channels
-              uint4 q = make_uint4(0u, 0u, 0u, 0u);
-              if (valid) {
-                const float4 b0 = *reinterpret_cast<const float4*>(bias_s + c0 + gq * 8);
-                const float4 b1 = *reinterpret_cast<const float4*>(bias_s + c0 + gq * 8 + 4);
-                const uint32_t* rr = r + gq * 8;
-                q.x = relu_pack_bf16x2(__uint_as_float(rr[0]) + b0.x, __uint_as_float(rr[1]) + b0.y);
-                q.y = relu_pack_bf16x2(__uint_as_float(rr[2]) + b0.z, __uint_as_float(rr[3]) + b0.w);
-                q.z = relu_pack_bf16x2(__uint_as_float(rr[4]) + b1.x, __uint_as_float(rr[5]) + b1.y);
-                q.w = relu_pack_bf16x2(__uint_as_float(rr[6]) + b1.z, __uint_as_float(rr[7]) + b1.w);
-              }
-              srow[(size_t)((c0 >> 3) + gq) * tile_rows] = q;
+              for (int j = 0; j < 16; ++j)
+                v[j] = valid ? fmaxf(__uint_as_float(r[hlf * 16 + j]) + bias_s[c0 + hlf * 16 + j], 0.f) : 0.f;
+              const int ch = (c0 >> 3) + 2 * hlf;
+              store8<__nv_bfloat16>(reinterpret_cast<char*>(staging) + ((size_t)ch * tile_rows + row) * 16, v);
+              store8<__nv_bfloat16>(reinterpret_cast<char*>(staging) + ((size_t)(ch + 1) * tile_rows + row) * 16, v + 8);
             }
           }
         } else if (Cout >= 32) {
@@ -801,33 +785,31 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
       if (EPI == EPI_RELU && p.pool_k > 0) {
         // ---- fused MaxPool2d(2,2,ceil): the tile is pool_k image-row pairs; every pooled granule is the max of four
         // staged granules (pads were staged as zero, and post-ReLU values are >= 0, so clipped windows are correct)
-        asm volatile("bar.sync 1, %0;" ::"r"(pool_nthr) : "memory");      // staging complete
+        const int nthr = nepi * 32, e = (warp - 2) * 32 + lane;
+        asm volatile("bar.sync 1, %0;" ::"r"(nthr) : "memory");
+        const int Wph = Wp >> 1, nch = Cout >> 3, per_chunk = p.pool_k * Wph;
         const int hp_half = (H + 1) >> 1;                      // row pairs per image (Hp is even)
-        const uint4* stg = reinterpret_cast<const uint4*>(staging);
-        const long long tile_first = (long long)tile * tile_pos;
-        uint4 v0[kPoolItems], v1[kPoolItems], v2[kPoolItems], v3[kPoolItems];
+        const ActView pv = g.pool_out;
+        for (int o = e; o < per_chunk * nch; o += nthr) {
+          const int c = fast_div(o, m_per_chunk), q = o - c * per_chunk;
+          const int rp = fast_div(q, m_wph), cp = q - rp * Wph;
+          const int r0 = 2 * rp * Wp + 2 * cp;                 // row in the staging tile
+          if ((long long)tile * tile_pos + r0 >= p.body) continue;
+          const uint4* sp = reinterpret_cast<const uint4*>(staging + ((size_t)c * tile_rows + r0) * 16);
+          uint4 m = sp[0];
+          const uint4 b1 = sp[1], b2 = sp[Wp], b3 = sp[Wp + 1];
+          __nv_bfloat162* mm = reinterpret_cast<__nv_bfloat162*>(&m);
+          const __nv_bfloat162* x1 = reinterpret_cast<const __nv_bfloat162*>(&b1);
+          const __nv_bfloat162* x2 = reinterpret_cast<const __nv_bfloat162*>(&b2);
+          const __nv_bfloat162* x3 = reinterpret_cast<const __nv_bfloat162*>(&b3);
 #pragma unroll
-        for (int k = 0; k < kPoolItems; ++k) {
-          if (k < pi_n) {
-            const uint4* sp = stg + pi_r0[k];
-            v0[k] = sp[0], v1[k] = sp[1], v2[k] = sp[Wp], v3[k] = sp[Wp + 1];
-          }
+          for (int j = 0; j < 4; ++j) mm[j] = __hmax2(__hmax2(mm[j], x1[j]), __hmax2(x2[j], x3[j]));
+          const int R = tile * p.pool_k + rp;                  // global row-pair index
+          const int n = fast_div(R, m_hph), ho = R - n * hp_half;
+          const long long pos = (long long)c * pv.plane + pv.g_lo + (long long)n * p.pool_Pimgo + ho * p.pool_Wpo + cp;
+          *reinterpret_cast<uint4*>(pv.base + pos * 16) = m;
         }
-#pragma unroll
-        for (int k = 0; k < kPoolItems; ++k) {
-          if (k < pi_n && tile_first + (pi_rp[k] >> 8) < p.body) {
-            uint4 m = v0[k];
-            __nv_bfloat162* mm = reinterpret_cast<__nv_bfloat162*>(&m);
-            const __nv_bfloat162* x1 = reinterpret_cast<const __nv_bfloat162*>(&v1[k]);
-            const __nv_bfloat162* x2 = reinterpret_cast<const __nv_bfloat162*>(&v2[k]);
-            const __nv_bfloat162* x3 = reinterpret_cast<const __nv_bfloat162*>(&v3[k]);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) mm[j] = __hmax2(__hmax2(mm[j], x1[j]), __hmax2(x2[j], x3[j]));
-            const int R = tile * p.pool_k + (pi_rp[k] & 255);    // global row-pair index
-            const int n = fast_div(R, m_hph), ho = R - n * hp_half;
-            *reinterpret_cast<uint4*>(g.pool_out.base + (pi_base[k] + (long long)n * p.pool_Pimgo + ho * p.pool_Wpo) * 16) = m;
-          }
-        }
+        asm volatile("bar.sync 1, %0;" ::"r"(nthr) : "memory");  // staging is reused by the next tile
         if (dbg_on) p.dbg[it * 8 + 7] = clock64();
       }
     }
@@ -941,8 +923,8 @@ cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream,
     per_sm = std::max(per_sm, 1);
     ConvParams q = p;
     q.acc_sets = (per_sm * 2 * p.MT * p.Cout <= 512) ? 2 : 1;
-    // K-split partials: N <= 64 instructions issue every ~45 cycles but accumulate with ~135 cycles of latency, so a
-    // CTA wants four independent accumulator chains (two for N = 128); never more partials than K steps per tile
+    // K-split partials (see issue_tile_mmas): four independent accumulator chains for N <= 64 instructions, two for
+    // N = 128; never more partials than K steps per tile; only where TMEM has the columns
     static int env_ks = -1;
     if (env_ks < 0) {
       const char* e = getenv("MTLDAS_PERSIST_KSPLIT");
@@ -950,9 +932,10 @@ cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream,
     }
     int KS = 1;
     const int want = p.Cout <= 64 ? 4 : 2, ksteps = p.ntaps * (p.nchunks >> 1);
-    while (p.MT * KS < want && KS * 2 <= env_ks && KS * 2 <= ksteps &&
+    while (p.MT < 4 && p.MT * KS < want && KS * 2 <= env_ks && KS * 2 <= ksteps &&
            per_sm * q.acc_sets * p.MT * p.Cout * KS * 2 <= 512)
       KS *= 2;
+    if (p.MT == 2 && KS > 2) KS = 2;
     q.ksplit = KS;
     uint32_t cols = 32;
     while (cols < (uint32_t)(q.acc_sets * p.MT * p.Cout * KS)) cols <<= 1;

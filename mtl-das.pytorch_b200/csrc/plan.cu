@@ -281,7 +281,9 @@ struct Builder {
     const long long positions = (long long)p.mb * (op.H + 1) * (op.W + 1);
     if (!tiled) {
       choose_tiling(op, positions);
-      if (p.precision == 0 && !p.training && p.use_nsplit) split_output_channels(op, positions);
+      // mode 1: only the stride-2 layers (four phase sources); mode 2 (default): every layer whose weights stream
+      if (p.precision == 0 && !p.training && p.use_nsplit && (p.nsplit_mode >= 2 || op.nsrc == 4))
+        split_output_channels(op, positions);
     }
     p.convs.push_back(op);
     p.program.push_back(Op{1, (int)p.convs.size() - 1});
@@ -300,6 +302,10 @@ Plan* build_plan(int kind, int mb, int precision, bool training) {
   {
     const char* e = getenv("MTLDAS_NO_NSPLIT");
     p.use_nsplit = !(e && e[0] == '1');
+    const char* m = getenv("MTLDAS_NSPLIT_MODE");
+    p.nsplit_mode = m ? atoi(m) : 2;
+    const char* o3 = getenv("MTLDAS_POOL_SPLIT");
+    p.pool_split = !(o3 && o3[0] == '0');
   }
   p.ntasks = kind == 0 ? 2 : 1;
   p.gran = precision == 0 ? 16 : 32;
@@ -436,7 +442,7 @@ Plan* build_plan(int kind, int mb, int precision, bool training) {
              (o.MT * kTileM) / (2 * (W[l] + 1)) >= 1;
     };
     bool fuse = fusable(op3);
-    if (!fuse && precision == 0 && !training && p.use_nsplit) {
+    if (!fuse && precision == 0 && !training && p.use_nsplit && p.pool_split) {
       ConvOpHost sp = op3;
       if (split_output_channels(sp, 0, /*even_if_resident=*/true) && fusable(sp)) op3 = sp, fuse = true;
     }

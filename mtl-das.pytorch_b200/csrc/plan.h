@@ -73,6 +73,8 @@ struct Plan {
   int kind, mb, precision, ntasks;
   bool training = false;   // plan built for the training program (no inference-only re-groupings)
   bool use_nsplit = true;
+  int nsplit_mode = 2;
+  bool pool_split = true;
   int gran;  // bytes per granule (16 bf16 / 32 fp32)
   std::vector<std::string> state_keys;
   std::vector<LayerSpec> layers;
