@@ -147,7 +147,7 @@ struct EpiRow {            // one output position (TMEM lane) of one accumulator
   const char* aux_addr0;
   uint32_t trow;
 };
-constexpr int kAuxDepth = 4;
+constexpr int kRingAuxDepth = 4, kPersistAuxDepth = 4;
 
 template <int EPI>
 __device__ __forceinline__ void aux_fetch(AuxPair& r, const EpiRow& row, long long aux_plane_bytes, int aux_nchunks, int c0) {
@@ -195,7 +195,7 @@ __device__ __forceinline__ void epilogue_cols_aux(const float* bias_s, int c0, c
 
 // Drain `ntile` accumulator tiles (this warp's share) of Cout columns each.  row_of(i) gives the row of the i-th tile,
 // ready(i) blocks until its accumulator is complete.
-template <int EPI, class RowFn, class ReadyFn>
+template <int EPI, int kAuxDepth, class RowFn, class ReadyFn>
 __device__ __forceinline__ void drain_with_aux(int ntile, int Cout, const float* bias_s, long long aux_plane_bytes,
                                                int aux_nchunks, long long out_plane_bytes, RowFn row_of, ReadyFn ready) {
   const int bpt = Cout >> 4, nblk = ntile * bpt;  // blocks of 16 channels
@@ -443,7 +443,7 @@ __global__ void __launch_bounds__(256) conv_umma_kernel(const __grid_constant__ 
         ptx::tc_fence_after();
       };
       const int nmine = mt0 < MT ? (MT - mt0 + mt_step - 1) / mt_step : 0;
-      if (nmine > 0) drain_with_aux<EPI>(nmine, Cout, bias_s, aux_plane_bytes, aux_nchunks, out_plane_bytes, row_of, ready);
+      if (nmine > 0) drain_with_aux<EPI, kRingAuxDepth>(nmine, Cout, bias_s, aux_plane_bytes, aux_nchunks, out_plane_bytes, row_of, ready);
     } else
     for (int mt = mt0; mt < MT; mt += mt_step) {
       const int f = tile_start + mt * kTileM + quarter * 32 + lane;
@@ -683,7 +683,25 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
 #define MTLDAS_ISSUE(M_, K_)                                                                                           \
   issue_tile_mmas<M_, K_>(d_base, part_cols, slab16, tap_off, ntaps, KC2, (uint32_t)Cout, ah_lo, ah_hi, bh_lo, bh_hi, w16, \
                           a_kstep, b_kstep, idesc)
-        if (MT == 4) MTLDAS_ISSUE(4, 1);
+        if (EPI == EPI_RELU && p.pool_k > 0) {
+          // fused-pool layers are bound by their epilogue's shared-memory traffic (staging tile); MMAs issued back to
+          // back take the whole shared-memory bandwidth in bursts and delay exactly that critical path (measured:
+          // 0.56 -> 0.62 ms on output_layer1).  The plain loop below paces itself at ~90 cycles per MMA.
+          uint32_t acc = 0u, b_lo = w16;
+#pragma unroll
+          for (int t = 0; t < kMaxTaps; ++t) {
+            if (t < ntaps) {
+              uint32_t a_lo = slab16 + tap_off[t];
+              for (int k = 0; k < KC2; ++k) {
+                for (int mt = 0; mt < MT; ++mt)
+                  ptx::umma_bf16(d_base + (uint32_t)(mt * Cout), a_hi | (a_lo + (uint32_t)(mt * kTileM)), b_hi | b_lo, idesc, acc);
+                acc = 1u;
+                a_lo += a_kstep;
+                b_lo += b_kstep;
+              }
+            }
+          }
+        } else if (MT == 4) MTLDAS_ISSUE(4, 1);
         else if (MT == 2 && KS == 1) MTLDAS_ISSUE(2, 1);
         else if (MT == 2) MTLDAS_ISSUE(2, 2);
         else if (KS == 1) MTLDAS_ISSUE(1, 1);
@@ -698,6 +716,8 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
     __syncwarp();
   } else {
     // ---- epilogue warps: TMEM lane quarter = warp % 4; the two warps of a quarter take alternate accumulator tiles
+    // (second-operand epilogues fetch ahead of every barrier of this kernel: order them after the previous grid here)
+    if (EPI == EPI_ADD_RELU || EPI == EPI_SIGMOID_MUL) ptx::pdl_grid_wait();
     const int quarter = warp & 3, half = (warp - 2) >> 2, mt_step = nepi >> 2;
     const ActView outv = g.out, auxv = g.aux;
     const long long out_plane_bytes = outv.plane * 16, aux_plane_bytes = auxv.plane * 16;
@@ -716,6 +736,45 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
       const int a = nsets == 2 ? (it & 1) : 0;
       const bool dbg_on = p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && it < 12 && warp == 2 && lane == 0;
       if (dbg_on) p.dbg[it * 8 + 4] = clock64();
+      if (EPI == EPI_ADD_RELU || EPI == EPI_SIGMOID_MUL) {   // (the launcher never K-splits these)
+        // second-operand epilogues: the residual / feature granules of this warp's rows are fetched a few 16-channel
+        // blocks ahead of the accumulator reads, the first ones BEFORE the wait for the accumulator -- one exposed L2
+        // round trip per tile instead of one per block (these layers were epilogue-bound on exactly that)
+        auto row_of = [&](int i) {
+          const int mt = half + i * mt_step;
+          const int f = tile * tile_pos + mt * kTileM + quarter * 32 + lane;
+          const bool in_body = f < body;
+          int n = 0, h = 0, w = 0;
+          if (in_body) {
+            n = fast_div(f, m_pimg);
+            const int rem = f - n * Pimg;
+            h = fast_div(rem, m_wp);
+            w = rem - h * Wp;
+          }
+          EpiRow r;
+          r.valid = in_body && (h < H) && (w < W);
+          r.do_store = in_body && (r.valid || outv.layout == LAY_P8);
+          r.out_addr0 = view_addr<__nv_bfloat16>(outv, 0, f, n, h, w);
+          r.aux_addr0 = view_addr<__nv_bfloat16>(auxv, 0, f, n, h, w);
+          r.trow = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)a * acc_cols + (uint32_t)(mt * Cout);
+          return r;
+        };
+        auto ready = [&](int i) {
+          if (i == 0) {
+            ptx::mbar_wait(bars + kPBarAccFull + a, (it / nsets) & 1);
+            ptx::tc_fence_after();
+          }
+        };
+        const int nmine = half < MT ? (MT - half + mt_step - 1) / mt_step : 0;
+        if (nmine > 0)
+          drain_with_aux<EPI, kPersistAuxDepth>(nmine, Cout, bias_s, aux_plane_bytes, aux_nchunks, out_plane_bytes, row_of, ready);
+        else
+          ready(0);
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(bars + kPBarAccEmpty + a);
+        continue;
+      }
       ptx::mbar_wait(bars + kPBarAccFull + a, (it / nsets) & 1);
       if (dbg_on) p.dbg[it * 8 + 5] = clock64();
       ptx::tc_fence_after();
@@ -928,7 +987,7 @@ cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream,
     static int env_ks = -1;
     if (env_ks < 0) {
       const char* e = getenv("MTLDAS_PERSIST_KSPLIT");
-      env_ks = e ? atoi(e) : 4;
+      env_ks = e ? atoi(e) : 1;   // measured: no gain on B200 (the chains are not what binds), kept as an experiment switch
     }
     int KS = 1;
     const int want = p.Cout <= 64 ? 4 : 2, ksteps = p.ntaps * (p.nchunks >> 1);
@@ -936,6 +995,7 @@ cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream,
            per_sm * q.acc_sets * p.MT * p.Cout * KS * 2 <= 512)
       KS *= 2;
     if (p.MT == 2 && KS > 2) KS = 2;
+    if (p.epi == EPI_ADD_RELU || p.epi == EPI_SIGMOID_MUL) KS = 1;
     q.ksplit = KS;
     uint32_t cols = 32;
     while (cols < (uint32_t)(q.acc_sets * p.MT * p.Cout * KS)) cols <<= 1;

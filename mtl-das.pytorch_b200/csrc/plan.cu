@@ -303,9 +303,10 @@ Plan* build_plan(int kind, int mb, int precision, bool training) {
     const char* e = getenv("MTLDAS_NO_NSPLIT");
     p.use_nsplit = !(e && e[0] == '1');
     const char* m = getenv("MTLDAS_NSPLIT_MODE");
-    p.nsplit_mode = m ? atoi(m) : 2;
+    p.nsplit_mode = m ? atoi(m) : 1;   // measured: only the stride-2 64->128 layer gains (0.19 -> 0.07 ms); N = 64 halves cost the
+                                         // same ~60 cycles per MMA as N = 128 (operand reads bind), so splitting 128->128 only adds work
     const char* o3 = getenv("MTLDAS_POOL_SPLIT");
-    p.pool_split = !(o3 && o3[0] == '0');
+    p.pool_split = (o3 && o3[0] == '1');   // measured slower than resident full-width + separate pool (0.33 vs 0.30 ms)
   }
   p.ntasks = kind == 0 ? 2 : 1;
   p.gran = precision == 0 ? 16 : 32;
