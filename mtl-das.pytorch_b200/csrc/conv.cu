@@ -581,8 +581,10 @@ __device__ __forceinline__ void load_acc16(uint32_t taddr, int KS, uint32_t part
   }
 }
 
-template <int EPI>
-__global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(const __grid_constant__ ConvParams p) {
+// WIDE = 1: layers that own the SM alone anyway (>= 64 output channels, large weight image): no 96-register cap, and the
+// second-operand epilogues run the fetch-ahead drain; WIDE = 0: two CTAs per SM (16 / 32 output channels).
+template <int EPI, int WIDE>
+__global__ void __launch_bounds__(kPersistThreads, WIDE ? 1 : 2) conv_umma_persist_kernel(const __grid_constant__ ConvParams p) {
   extern __shared__ __align__(128) uint8_t smem[];
   const ConvGroupDev& g = p.g[blockIdx.y];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
@@ -717,7 +719,7 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
   } else {
     // ---- epilogue warps: TMEM lane quarter = warp % 4; the two warps of a quarter take alternate accumulator tiles
     // (second-operand epilogues fetch ahead of every barrier of this kernel: order them after the previous grid here)
-    if (EPI == EPI_ADD_RELU || EPI == EPI_SIGMOID_MUL) ptx::pdl_grid_wait();
+    if (WIDE && (EPI == EPI_ADD_RELU || EPI == EPI_SIGMOID_MUL)) ptx::pdl_grid_wait();
     const int quarter = warp & 3, half = (warp - 2) >> 2, mt_step = nepi >> 2;
     const ActView outv = g.out, auxv = g.aux;
     const long long out_plane_bytes = outv.plane * 16, aux_plane_bytes = auxv.plane * 16;
@@ -736,10 +738,11 @@ __global__ void __launch_bounds__(kPersistThreads, 2) conv_umma_persist_kernel(c
       const int a = nsets == 2 ? (it & 1) : 0;
       const bool dbg_on = p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && it < 12 && warp == 2 && lane == 0;
       if (dbg_on) p.dbg[it * 8 + 4] = clock64();
-      if (EPI == EPI_ADD_RELU || EPI == EPI_SIGMOID_MUL) {   // (the launcher never K-splits these)
+      if (WIDE && (EPI == EPI_ADD_RELU || EPI == EPI_SIGMOID_MUL)) {   // (the launcher never K-splits these)
         // second-operand epilogues: the residual / feature granules of this warp's rows are fetched a few 16-channel
         // blocks ahead of the accumulator reads, the first ones BEFORE the wait for the accumulator -- one exposed L2
-        // round trip per tile instead of one per block (these layers were epilogue-bound on exactly that)
+        // round trip per tile instead of one per block.  Measured: pays from 64 output channels on (0.13 -> 0.12 ms at
+        // stage 3); with 16 / 32 channels a row is one or two blocks and the plain path is faster (0.25 vs 0.28 ms).
         auto row_of = [&](int i) {
           const int mt = half + i * mt_step;
           const int f = tile * tile_pos + mt * kTileM + quarter * 32 + lane;
@@ -958,11 +961,12 @@ cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream,
     static PerDeviceSmem configured_p;
     {
       cudaError_t e = configured_p.ensure(smem, [](int bytes) {
-        cudaError_t e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_ADD_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_SIGMOID_MUL>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<EPI_ACCUM>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        cudaError_t e = cudaSuccess;
+#define MTLDAS_SET(E_, W_) \
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_umma_persist_kernel<E_, W_>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)
+        MTLDAS_SET(EPI_NONE, 0); MTLDAS_SET(EPI_RELU, 0); MTLDAS_SET(EPI_ADD_RELU, 0); MTLDAS_SET(EPI_SIGMOID_MUL, 0); MTLDAS_SET(EPI_ACCUM, 0);
+        MTLDAS_SET(EPI_NONE, 1); MTLDAS_SET(EPI_RELU, 1); MTLDAS_SET(EPI_ADD_RELU, 1); MTLDAS_SET(EPI_SIGMOID_MUL, 1); MTLDAS_SET(EPI_ACCUM, 1);
+#undef MTLDAS_SET
         return e;
       });
       if (e != cudaSuccess) return e;
@@ -1003,13 +1007,18 @@ cudaError_t launch_conv(const ConvParams& p, int precision, cudaStream_t stream,
     int ctas = std::min(ntiles, 148 * per_sm / std::max(1, p.ngroups));
     ctas = std::max(ctas, 1);
     dim3 grid(ctas, p.ngroups, 1);
+    const bool wide = per_sm == 1 && p.Cout >= 64;
+#define MTLDAS_GO(E_)                                                                                             \
+  return wide ? launch_ex(conv_umma_persist_kernel<E_, 1>, grid, dim3(threads), smem, stream, pdl, q)             \
+              : launch_ex(conv_umma_persist_kernel<E_, 0>, grid, dim3(threads), smem, stream, pdl, q)
     switch (p.epi) {
-      case EPI_NONE: return launch_ex(conv_umma_persist_kernel<EPI_NONE>, grid, dim3(threads), smem, stream, pdl, q);
-      case EPI_RELU: return launch_ex(conv_umma_persist_kernel<EPI_RELU>, grid, dim3(threads), smem, stream, pdl, q);
-      case EPI_ADD_RELU: return launch_ex(conv_umma_persist_kernel<EPI_ADD_RELU>, grid, dim3(threads), smem, stream, pdl, q);
-      case EPI_ACCUM: return launch_ex(conv_umma_persist_kernel<EPI_ACCUM>, grid, dim3(threads), smem, stream, pdl, q);
-      default: return launch_ex(conv_umma_persist_kernel<EPI_SIGMOID_MUL>, grid, dim3(threads), smem, stream, pdl, q);
+      case EPI_NONE: MTLDAS_GO(EPI_NONE);
+      case EPI_RELU: MTLDAS_GO(EPI_RELU);
+      case EPI_ADD_RELU: MTLDAS_GO(EPI_ADD_RELU);
+      case EPI_ACCUM: MTLDAS_GO(EPI_ACCUM);
+      default: MTLDAS_GO(EPI_SIGMOID_MUL);
     }
+#undef MTLDAS_GO
   } else if (precision == 0) {
     size_t smem = conv_umma_smem_bytes(p);
     static PerDeviceSmem configured;
