@@ -685,7 +685,8 @@ __global__ void __launch_bounds__(kPersistThreads, WIDE ? 1 : 2) conv_umma_persi
 #define MTLDAS_ISSUE(M_, K_)                                                                                           \
   issue_tile_mmas<M_, K_>(d_base, part_cols, slab16, tap_off, ntaps, KC2, (uint32_t)Cout, ah_lo, ah_hi, bh_lo, bh_hi, w16, \
                           a_kstep, b_kstep, idesc)
-        if (EPI == EPI_RELU && p.pool_k > 0) {
+        if ((EPI == EPI_RELU && p.pool_k > 0) || (!WIDE && (EPI == EPI_ADD_RELU || EPI == EPI_SIGMOID_MUL))) {
+          // (same for the narrow second-operand layers, whose epilogue is the critical path: 0.238 -> 0.248 ms otherwise)
           // fused-pool layers are bound by their epilogue's shared-memory traffic (staging tile); MMAs issued back to
           // back take the whole shared-memory bandwidth in bursts and delay exactly that critical path (measured:
           // 0.56 -> 0.62 ms on output_layer1).  The plain loop below paces itself at ~90 cycles per MMA.
