@@ -214,6 +214,34 @@ MTLDAS_API int mtldas_eval_metrics(const float* dev_logp0, const long long* dev_
                                    int n, long long* dev_counts4, double* dev_loss_sums2, long long* dev_confusion0,
                                    long long* dev_confusion1, void* stream);
 
+/* model C: Multi_Classifier (Inception-V3, 1-channel stem, 32 classes), eval-mode forward -------------------------
+ * Replaces, op by op, what /root/reference/model/modelC_multiClassifier.py:102-147 executes in eval mode (utils.py:648):
+ * BasicConv2d = Conv2d(bias=False) + BatchNorm2d(eps=1e-3) + ReLU (modelC:10-25 and torchvision's Inception blocks),
+ * the 3x3 pools, the channel concatenations (a channel offset into the destination tensor) and the classifier head.
+ * Activations use the "planar-8" layout: [channels/8][n*H*W][8] bf16; the host side (mtldas_b200/nets_c.py) owns the
+ * tensors and the layer program.  bf16 tensor-core path only.  All calls are asynchronous on `stream`.
+ *
+ * c_pack_conv: folds BatchNorm (running statistics, eps as given) into the conv weight [cout, cin, kh, kw] and writes
+ *   the packed image [kh*kw][cin/8][cout][8] bf16 (cin == 1: [kh*kw][cout] fp32) and the bias [cout] fp32.
+ * c_conv: out[:, out_channel0 : +cout] = relu?(conv(x) + bias); x planar-8 [n, cin, h, w] (cin == 1: the fp32 patches
+ *   [n,1,h,w], 3x3 / stride 2 / no padding only); any kernel size / stride / padding; cin, cout multiples of 16.
+ * c_pool: 3x3 max pool (is_avg 0; F.max_pool2d(x, 3, stride), no padding) or 3x3 average pool that counts the padding
+ *   (is_avg 1; F.avg_pool2d(x, 3, stride, pad)), written at out_channel0 of the destination tensor.
+ * c_head: logits = Linear(mean over the hw positions)  (AdaptiveAvgPool2d(1) + flatten + fc, modelC:137-146).
+ * c_read: debug / tests: planar-8 channels [channel0, +channels) -> fp32 [n, channels, hw]. */
+MTLDAS_API int mtldas_c_pack_conv(const float* dev_w, const float* dev_gamma, const float* dev_beta, const float* dev_rmean,
+                                  const float* dev_rvar, float eps, int cout, int cin, int kh, int kw, void* dev_packed,
+                                  float* dev_bias, void* stream);
+MTLDAS_API int mtldas_c_conv(const void* dev_x, int n, int cin, int h, int w, const void* dev_packed, const float* dev_bias,
+                             void* dev_out, int out_channels_total, int out_channel0, int cout, int kh, int kw, int sh,
+                             int sw, int ph, int pw, int relu, void* stream);
+MTLDAS_API int mtldas_c_pool(const void* dev_x, int n, int channels, int h, int w, void* dev_out, int out_channels_total,
+                             int out_channel0, int stride, int pad, int is_avg, void* stream);
+MTLDAS_API int mtldas_c_head(const void* dev_x, int n, int channels, int hw, const float* dev_fc_w, const float* dev_fc_b,
+                             int classes, float* dev_logits, void* stream);
+MTLDAS_API int mtldas_c_read(const void* dev_x, int n, int channels_total, int channel0, int channels, int hw,
+                             float* dev_out_nchw, void* stream);
+
 /* streaming inference over a large DAS array --------------------------------------------------------
  * No counterpart in the reference (its README only motivates it): cuts the [100 x 250] patches the
  * network expects (utils.py:128) out of dev_array [n_channels, n_time] fp32 row-major: window wi covers fibre

@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "mtldas_b200", "libmtldas_b200.so")
-SOURCES = ["conv.cu", "elementwise.cu", "plan.cu", "api.cu", "static_conv.cu", "train_kernels.cu", "train_ew.cu", "train.cu", "stem_umma.cu", "optim_metrics.cu"]
+SOURCES = ["conv.cu", "elementwise.cu", "plan.cu", "api.cu", "static_conv.cu", "train_kernels.cu", "train_ew.cu", "train.cu", "stem_umma.cu", "optim_metrics.cu", "modelc.cu"]
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--use_fast_math",
          "-Xcompiler", "-fPIC,-O2,-fvisibility=hidden", "-Xptxas", "-v"]
 

@@ -57,6 +57,11 @@ def _load():
         "mtldas_nll_loss": (ci, [vp, vp, ci, vp, vp, vp, ci, vp, ci, vp, vp, vp]),
         "mtldas_adam_step": (ci, [vp, vp, vp, vp, sz, ci, cf, cf, cf, cf, cf, vp]),
         "mtldas_eval_metrics": (ci, [vp, vp, ci, vp, vp, vp, ci, vp, ci, vp, vp, vp, vp, vp]),
+        "mtldas_c_pack_conv": (ci, [vp, vp, vp, vp, vp, cf, ci, ci, ci, ci, vp, vp, vp]),
+        "mtldas_c_conv": (ci, [vp, ci, ci, ci, ci, vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, ci, ci, ci, vp]),
+        "mtldas_c_pool": (ci, [vp, ci, ci, ci, ci, vp, ci, ci, ci, ci, ci, vp]),
+        "mtldas_c_head": (ci, [vp, ci, ci, ci, vp, vp, ci, vp, vp]),
+        "mtldas_c_read": (ci, [vp, ci, ci, ci, ci, ci, vp, vp]),
         "mtldas_umma_selftest": (cf, [ci, ci, ci]),
         "mtldas_umma_rate": (ci, [ci, ci, ci, c.POINTER(cf)]),
     }

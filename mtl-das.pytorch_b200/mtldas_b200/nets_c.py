@@ -1,16 +1,23 @@
-"""Boundary class for the reference's model C (Inception-V3 multi-classifier).
+"""Drop-in for the reference's model C (Inception-V3 multi-classifier) on the B200 kernels.
 
 /root/reference/model/modelC_multiClassifier.py:28-172 builds torchvision's Inception-V3 with a 1-channel stem, 32
 classes and no auxiliary head.  This class keeps that constructor signature, parameter tree and state_dict (566 keys,
-torchvision naming) so that `utils.py` imports, checkpoints load with strict=True and
-`--model multi_classifier` reaches the forward -- where it stops: the Inception kernels (1x7 / 7x1 / 5x5 / valid 3x3
-convolutions, 3x3 average and max pools, the 2048->32 linear layer) are SURVEY.md section 8 row f1 ("next") and are not
-built yet, and this package has no PyTorch fallback by design.
+torchvision naming) so that `utils.py` imports it, checkpoints load with strict=True and
+`--model multi_classifier` evaluates.  forward() in eval mode runs the layer program below through the C ABI
+(mtldas_c_*: tcgen05 implicit-GEMM convolutions with folded BatchNorm + ReLU, 3x3 pools, concat by channel offset,
+GAP + fc) and returns raw logits [N, 32] (the reference's loss is CrossEntropyLoss, utils.py:137).  Training-mode
+forward (batch statistics, Dropout, backward) is not built for this model: it raises -- there is no PyTorch fallback.
 """
+import ctypes
+
 import torch
 import torch.nn as nn
 
-from ._lib import MtldasError
+from ._lib import lib, check, MtldasError
+from .engine import _require_b200, _stream_ptr
+from .synth import _inception_convs
+
+_SPECS = {name: (cin, cout, k, s, p) for name, cin, cout, k, s, p in _inception_convs()}
 
 
 class _ConvBN(nn.Module):
@@ -20,6 +27,122 @@ class _ConvBN(nn.Module):
         super().__init__()
         self.conv = nn.Conv2d(cin, cout, bias=False, **kw)
         self.bn = nn.BatchNorm2d(cout, eps=0.001)
+
+
+def _out_hw(h, w, k, s, p):
+    return (h + 2 * p[0] - k[0]) // s[0] + 1, (w + 2 * p[1] - k[1]) // s[1] + 1
+
+
+class _Program:
+    """Layer program of Multi_Classifier._forward (modelC:102-147) for a batch of n patches: tensors in the planar-8
+    layout [C/8, n*H*W, 8] bf16 and a list of ops; a concat is a channel offset into the block's output tensor."""
+
+    def __init__(self, n, device, hin=100, win=250):
+        self.n, self.device = n, device
+        self.ops, self.shapes, self.buf = [], {}, {}
+        self.shapes["x"] = (1, hin, win)
+        t = self.conv("x", "Conv2d_1a_3x3")
+        t = self.conv(t, "Conv2d_2a_3x3")
+        t = self.conv(t, "Conv2d_2b_3x3")
+        t = self.pool(t, "maxpool1", stride=2, pad=0, avg=False)
+        t = self.conv(t, "Conv2d_3b_1x1")
+        t = self.conv(t, "Conv2d_4a_3x3")
+        t = self.pool(t, "maxpool2", stride=2, pad=0, avg=False)
+        for name in ("Mixed_5b", "Mixed_5c", "Mixed_5d"):
+            t = self.inception_a(t, name)
+        t = self.inception_b(t, "Mixed_6a")
+        for name in ("Mixed_6b", "Mixed_6c", "Mixed_6d", "Mixed_6e"):
+            t = self.inception_c(t, name)
+        t = self.inception_d(t, "Mixed_7a")
+        for name in ("Mixed_7b", "Mixed_7c"):
+            t = self.inception_e(t, name)
+        self.last = t
+        for name, (c, h, w) in self.shapes.items():
+            if name != "x":
+                self.buf[name] = torch.empty((c // 8, n * h * w, 8), dtype=torch.bfloat16, device=device)
+
+    # ---- op builders ---------------------------------------------------------------------------------
+    def tensor(self, name, c, h, w):
+        self.shapes[name] = (c, h, w)
+        return name
+
+    def conv(self, src, name, dst=None, c0=0):
+        cin, cout, k, s, p = _SPECS[name]
+        c, h, w = self.shapes[src]
+        assert c == cin, (name, c, cin)
+        ho, wo = _out_hw(h, w, k, s, p)
+        if dst is None:
+            dst = self.tensor(name, cout, ho, wo)
+        assert self.shapes[dst][1:] == (ho, wo), (name, self.shapes[dst], ho, wo)
+        self.ops.append(("conv", src, dst, c0, name))
+        return dst
+
+    def pool(self, src, name, stride, pad, avg, dst=None, c0=0):
+        c, h, w = self.shapes[src]
+        ho, wo = _out_hw(h, w, (3, 3), (stride, stride), (pad, pad))
+        if dst is None:
+            dst = self.tensor(name, c, ho, wo)
+        self.ops.append(("pool", src, dst, c0, (stride, pad, int(avg))))
+        return dst
+
+    def block(self, name, src, widths, stride=1):
+        c, h, w = self.shapes[src]
+        ho, wo = (h, w) if stride == 1 else _out_hw(h, w, (3, 3), (2, 2), (0, 0))
+        return self.tensor(name, sum(widths), ho, wo)
+
+    def inception_a(self, x, n):        # torchvision InceptionA._forward: [1x1 | 5x5 | 3x3dbl | pool]
+        pf = _SPECS[n + ".branch_pool"][1]
+        out = self.block(n, x, (64, 64, 96, pf))
+        self.conv(x, n + ".branch1x1", out, 0)
+        self.conv(self.conv(x, n + ".branch5x5_1"), n + ".branch5x5_2", out, 64)
+        t = self.conv(self.conv(x, n + ".branch3x3dbl_1"), n + ".branch3x3dbl_2")
+        self.conv(t, n + ".branch3x3dbl_3", out, 128)
+        self.conv(self.pool(x, n + ".avgpool", 1, 1, True), n + ".branch_pool", out, 224)
+        return out
+
+    def inception_b(self, x, n):        # InceptionB: [3x3 s2 | 3x3dbl s2 | maxpool]
+        cin = self.shapes[x][0]
+        out = self.block(n, x, (384, 96, cin), stride=2)
+        self.conv(x, n + ".branch3x3", out, 0)
+        t = self.conv(self.conv(x, n + ".branch3x3dbl_1"), n + ".branch3x3dbl_2")
+        self.conv(t, n + ".branch3x3dbl_3", out, 384)
+        self.pool(x, n + ".maxpool", 2, 0, False, out, 480)
+        return out
+
+    def inception_c(self, x, n):        # InceptionC: [1x1 | 7x7 | 7x7dbl | pool]
+        out = self.block(n, x, (192, 192, 192, 192))
+        self.conv(x, n + ".branch1x1", out, 0)
+        t = self.conv(self.conv(x, n + ".branch7x7_1"), n + ".branch7x7_2")
+        self.conv(t, n + ".branch7x7_3", out, 192)
+        t = x
+        for s in ("_1", "_2", "_3", "_4"):
+            t = self.conv(t, n + ".branch7x7dbl" + s)
+        self.conv(t, n + ".branch7x7dbl_5", out, 384)
+        self.conv(self.pool(x, n + ".avgpool", 1, 1, True), n + ".branch_pool", out, 576)
+        return out
+
+    def inception_d(self, x, n):        # InceptionD: [3x3 s2 | 7x7x3 s2 | maxpool]
+        cin = self.shapes[x][0]
+        out = self.block(n, x, (320, 192, cin), stride=2)
+        self.conv(self.conv(x, n + ".branch3x3_1"), n + ".branch3x3_2", out, 0)
+        t = x
+        for s in ("_1", "_2", "_3"):
+            t = self.conv(t, n + ".branch7x7x3" + s)
+        self.conv(t, n + ".branch7x7x3_4", out, 320)
+        self.pool(x, n + ".maxpool", 2, 0, False, out, 512)
+        return out
+
+    def inception_e(self, x, n):        # InceptionE: [1x1 | 3x3 (2a|2b) | 3x3dbl (3a|3b) | pool]
+        out = self.block(n, x, (320, 768, 768, 192))
+        self.conv(x, n + ".branch1x1", out, 0)
+        t = self.conv(x, n + ".branch3x3_1")
+        self.conv(t, n + ".branch3x3_2a", out, 320)
+        self.conv(t, n + ".branch3x3_2b", out, 704)
+        t = self.conv(self.conv(x, n + ".branch3x3dbl_1"), n + ".branch3x3dbl_2")
+        self.conv(t, n + ".branch3x3dbl_3a", out, 1088)
+        self.conv(t, n + ".branch3x3dbl_3b", out, 1472)
+        self.conv(self.pool(x, n + ".avgpool", 1, 1, True), n + ".branch_pool", out, 1856)
+        return out
 
 
 class Multi_Classifier(nn.Module):
@@ -54,6 +177,8 @@ class Multi_Classifier(nn.Module):
         self.avgpool = nn.AdaptiveAvgPool2d((1, 1))
         self.dropout = nn.Dropout()
         self.fc = nn.Linear(2048, num_classes)
+        self.num_classes = num_classes
+        self._programs, self._packed, self._packed_sig = {}, {}, {}
         if init_weights:
             self._truncnorm_init()
 
@@ -68,6 +193,90 @@ class Multi_Classifier(nn.Module):
                 nn.init.constant_(m.weight, 1)
                 nn.init.constant_(m.bias, 0)
 
+    # ---- engine ---------------------------------------------------------------------------------------
+    def train(self, mode=True):
+        if bool(mode) != self.training:
+            getattr(self, "_packed_sig", {}).clear()
+        return super().train(mode)
+
+    def _pack(self, device):
+        """Fold eval-mode BatchNorm (eps 1e-3) into every conv and pack it for the kernels; redone when a parameter or
+        buffer changed (version counters) or after a train() / eval() switch."""
+        sd = self.state_dict(keep_vars=True)
+        sig = tuple((v.data_ptr(), v._version) for v in sd.values())
+        key = str(device)
+        if self._packed_sig.get(key) == sig:
+            return self._packed[key]
+        packed = {}
+        p = lambda t: ctypes.c_void_p(t.data_ptr())  # noqa: E731
+        with torch.cuda.device(device):
+            for name, (cin, cout, k, s, pad) in _SPECS.items():
+                t = [sd[name + sfx].detach().float().contiguous() for sfx in
+                     (".conv.weight", ".bn.weight", ".bn.bias", ".bn.running_mean", ".bn.running_var")]
+                for u in t:
+                    if u.device != device:
+                        raise MtldasError(f"state entry of {name} is on {u.device}, input on {device}")
+                nbytes = 9 * cout * 4 if cin == 1 else k[0] * k[1] * cin * cout * 2
+                w = torch.empty(nbytes, dtype=torch.uint8, device=device)
+                b = torch.empty(cout, dtype=torch.float32, device=device)
+                check(lib.mtldas_c_pack_conv(p(t[0]), p(t[1]), p(t[2]), p(t[3]), p(t[4]), 1e-3, cout, cin, k[0], k[1], p(w),
+                                             p(b), _stream_ptr(device)), "c_pack_conv " + name)
+                packed[name] = (w, b, t)
+        packed["fc"] = (sd["fc.weight"].detach().float().contiguous(), sd["fc.bias"].detach().float().contiguous())
+        self._packed[key], self._packed_sig[key] = packed, sig
+        return packed
+
     def forward(self, x):
-        raise MtldasError("Multi_Classifier (model C, Inception-V3): the sm_100a kernels for this model are not built "
-                          "yet (SURVEY.md section 8 row f1); there is no PyTorch fallback in this package")
+        if not isinstance(x, torch.Tensor) or not x.is_cuda:
+            raise MtldasError("mtldas_b200 modules run on a B200 through the CUDA extension only; "
+                              "got a non-CUDA input and there is no CPU fallback")
+        if self.training:
+            raise MtldasError("Multi_Classifier: only the eval-mode forward runs on the sm_100a kernels (training-mode "
+                              "BatchNorm / Dropout / backward of Inception-V3 are not built); call model.eval()")
+        if x.dim() != 4 or tuple(x.shape[1:]) != (1, 100, 250):
+            raise ValueError(f"expected [N,1,100,250], got {tuple(x.shape)}")
+        _require_b200(x.device)
+        x = x.contiguous().float()
+        n, dev = x.shape[0], x.device
+        key = (str(dev), n)
+        prog = self._programs.get(key)
+        if prog is None:
+            if len(self._programs) >= 2:          # the activation buffers of a batch size are large: keep two
+                self._programs.pop(next(iter(self._programs)))
+            prog = self._programs[key] = _Program(n, dev)
+        packed = self._pack(dev)
+        logits = torch.empty((n, self.num_classes), dtype=torch.float32, device=dev)
+        st = _stream_ptr(dev)
+        ptr = lambda name: ctypes.c_void_p(x.data_ptr() if name == "x" else prog.buf[name].data_ptr())  # noqa: E731
+        self.last_launch_count = 0
+        with torch.cuda.device(dev):
+            for kind, src, dst, c0, arg in prog.ops:
+                c, h, w = prog.shapes[src]
+                ctot = prog.shapes[dst][0]
+                if kind == "conv":
+                    cin, cout, k, s, pad = _SPECS[arg]
+                    wp, bp, _ = packed[arg]
+                    check(lib.mtldas_c_conv(ptr(src), n, cin, h, w, ctypes.c_void_p(wp.data_ptr()),
+                                            ctypes.c_void_p(bp.data_ptr()), ptr(dst), ctot, c0, cout, k[0], k[1], s[0], s[1],
+                                            pad[0], pad[1], 1, st), "c_conv " + arg)
+                else:
+                    stride, pad, avg = arg
+                    check(lib.mtldas_c_pool(ptr(src), n, c, h, w, ptr(dst), ctot, c0, stride, pad, avg, st), "c_pool")
+                self.last_launch_count += 1
+            c, h, w = prog.shapes[prog.last]
+            fw, fb = packed["fc"]
+            check(lib.mtldas_c_head(ptr(prog.last), n, c, h * w, ctypes.c_void_p(fw.data_ptr()), ctypes.c_void_p(fb.data_ptr()),
+                                    self.num_classes, ctypes.c_void_p(logits.data_ptr()), st), "c_head")
+            self.last_launch_count += 1
+        self._last_program = prog
+        return logits
+
+    def read_tensor(self, name):
+        """Debug / tests: an intermediate tensor of the last forward as fp32 [n, C, H, W] (names = reference module names)."""
+        prog = self._last_program
+        c, h, w = prog.shapes[name]
+        out = torch.empty((prog.n, c, h, w), dtype=torch.float32, device=prog.device)
+        with torch.cuda.device(prog.device):
+            check(lib.mtldas_c_read(ctypes.c_void_p(prog.buf[name].data_ptr()), prog.n, c, 0, c, h * w,
+                                    ctypes.c_void_p(out.data_ptr()), _stream_ptr(prog.device)), "c_read")
+        return out

@@ -110,3 +110,108 @@ def synth_patches(n: int, seed: int = 1234) -> Tuple[torch.Tensor, torch.Tensor,
     return torch.from_numpy(x.astype(np.float32)), torch.from_numpy(yd), torch.from_numpy(ye)
 
 
+# --------------------------------------------------------------------------------------
+# model C (Multi_Classifier, Inception-V3 with a 1-channel stem): layer table, state_dict contract, synthetic weights
+# --------------------------------------------------------------------------------------
+def _inception_convs():
+    """(prefix, cin, cout, (kh, kw), (sh, sw), (ph, pw)) of every BasicConv2d in registration order
+    (modelC_multiClassifier.py:63-83; torchvision/models/inception.py InceptionA..E constructors)."""
+    L = []
+
+    def add(name, cin, cout, k=1, s=1, p=0):
+        k = (k, k) if isinstance(k, int) else k
+        s = (s, s) if isinstance(s, int) else s
+        p = (p, p) if isinstance(p, int) else p
+        L.append((name, cin, cout, k, s, p))
+
+    add("Conv2d_1a_3x3", 1, 32, 3, 2)
+    add("Conv2d_2a_3x3", 32, 32, 3)
+    add("Conv2d_2b_3x3", 32, 64, 3, 1, 1)
+    add("Conv2d_3b_1x1", 64, 80, 1)
+    add("Conv2d_4a_3x3", 80, 192, 3)
+    for name, cin, pf in (("Mixed_5b", 192, 32), ("Mixed_5c", 256, 64), ("Mixed_5d", 288, 64)):      # InceptionA
+        add(name + ".branch1x1", cin, 64)
+        add(name + ".branch5x5_1", cin, 48)
+        add(name + ".branch5x5_2", 48, 64, 5, 1, 2)
+        add(name + ".branch3x3dbl_1", cin, 64)
+        add(name + ".branch3x3dbl_2", 64, 96, 3, 1, 1)
+        add(name + ".branch3x3dbl_3", 96, 96, 3, 1, 1)
+        add(name + ".branch_pool", cin, pf)
+    add("Mixed_6a.branch3x3", 288, 384, 3, 2)                                                          # InceptionB
+    add("Mixed_6a.branch3x3dbl_1", 288, 64)
+    add("Mixed_6a.branch3x3dbl_2", 64, 96, 3, 1, 1)
+    add("Mixed_6a.branch3x3dbl_3", 96, 96, 3, 2)
+    for name, c7 in (("Mixed_6b", 128), ("Mixed_6c", 160), ("Mixed_6d", 160), ("Mixed_6e", 192)):      # InceptionC
+        add(name + ".branch1x1", 768, 192)
+        add(name + ".branch7x7_1", 768, c7)
+        add(name + ".branch7x7_2", c7, c7, (1, 7), 1, (0, 3))
+        add(name + ".branch7x7_3", c7, 192, (7, 1), 1, (3, 0))
+        add(name + ".branch7x7dbl_1", 768, c7)
+        add(name + ".branch7x7dbl_2", c7, c7, (7, 1), 1, (3, 0))
+        add(name + ".branch7x7dbl_3", c7, c7, (1, 7), 1, (0, 3))
+        add(name + ".branch7x7dbl_4", c7, c7, (7, 1), 1, (3, 0))
+        add(name + ".branch7x7dbl_5", c7, 192, (1, 7), 1, (0, 3))
+        add(name + ".branch_pool", 768, 192)
+    add("Mixed_7a.branch3x3_1", 768, 192)                                                              # InceptionD
+    add("Mixed_7a.branch3x3_2", 192, 320, 3, 2)
+    add("Mixed_7a.branch7x7x3_1", 768, 192)
+    add("Mixed_7a.branch7x7x3_2", 192, 192, (1, 7), 1, (0, 3))
+    add("Mixed_7a.branch7x7x3_3", 192, 192, (7, 1), 1, (3, 0))
+    add("Mixed_7a.branch7x7x3_4", 192, 192, 3, 2)
+    for name, cin in (("Mixed_7b", 1280), ("Mixed_7c", 2048)):                                         # InceptionE
+        add(name + ".branch1x1", cin, 320)
+        add(name + ".branch3x3_1", cin, 384)
+        add(name + ".branch3x3_2a", 384, 384, (1, 3), 1, (0, 1))
+        add(name + ".branch3x3_2b", 384, 384, (3, 1), 1, (1, 0))
+        add(name + ".branch3x3dbl_1", cin, 448)
+        add(name + ".branch3x3dbl_2", 448, 384, 3, 1, 1)
+        add(name + ".branch3x3dbl_3a", 384, 384, (1, 3), 1, (0, 1))
+        add(name + ".branch3x3dbl_3b", 384, 384, (3, 1), 1, (1, 0))
+        add(name + ".branch_pool", cin, 192)
+    return L
+
+
+def state_dict_keys_c():
+    """(key, shape, dtype) of the reference Multi_Classifier state_dict in registration order (566 entries)."""
+    keys = []
+    for name, cin, cout, k, s, p in _inception_convs():
+        keys.append((name + ".conv.weight", (cout, cin, k[0], k[1]), "float32"))
+        keys += [(name + ".bn.weight", (cout,), "float32"), (name + ".bn.bias", (cout,), "float32"),
+                 (name + ".bn.running_mean", (cout,), "float32"), (name + ".bn.running_var", (cout,), "float32"),
+                 (name + ".bn.num_batches_tracked", (), "int64")]
+    keys += [("fc.weight", (32, 2048), "float32"), ("fc.bias", (32,), "float32")]
+    return keys
+
+
+def synth_state_dict_c(seed: int = 0):
+    """Deterministic synthetic weights for model C (numpy PCG64 only): He-uniform conv weights so activations keep their
+    scale through 94 ReLU layers, perturbed BatchNorm affine / running statistics (the eval fold must matter)."""
+    rng = np.random.default_rng(seed)
+    sd = {}
+
+    def u(shape, lo, hi):
+        return torch.from_numpy((rng.random(shape, dtype=np.float64) * (hi - lo) + lo).astype(np.float32))
+
+    for key, shape, dtype in state_dict_keys_c():
+        leaf = key.rsplit(".", 1)[1]
+        if dtype == "int64":
+            sd[key] = torch.tensor(3, dtype=torch.int64)
+        elif len(shape) == 4:
+            b = math.sqrt(6.0 / (shape[1] * shape[2] * shape[3]))
+            sd[key] = u(shape, -b, b)
+        elif key == "fc.weight":
+            b = math.sqrt(3.0 / shape[1])
+            sd[key] = u(shape, -b, b)
+        elif key == "fc.bias":
+            sd[key] = u(shape, -0.1, 0.1)
+        elif leaf == "weight":
+            sd[key] = u(shape, 0.7, 1.3)
+        elif leaf == "bias":
+            sd[key] = u(shape, -0.2, 0.2)
+        elif leaf == "running_mean":
+            sd[key] = u(shape, -0.2, 0.2)
+        elif leaf == "running_var":
+            sd[key] = u(shape, 0.6, 1.4)
+        else:
+            raise AssertionError(key)
+    return sd

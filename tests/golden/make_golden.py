@@ -96,7 +96,7 @@ def main():
             print(path, os.path.getsize(path) // 1024, "KiB", "loss", [float(res[k]) for k in res if k.startswith("loss")])
 
 
-if __name__ == "__main__" and "--trained" not in sys.argv:
+if __name__ == "__main__" and "--trained" not in sys.argv and "--model-c" not in sys.argv:
     main()
 
 
@@ -133,3 +133,37 @@ def make_trained_state(steps=40, batch=32):
 
 if __name__ == "__main__" and "--trained" in sys.argv:
     make_trained_state()
+
+
+def make_model_c():
+    """Reference Multi_Classifier (modelC_multiClassifier.py, torchvision Inception blocks), eval mode, on the oracle's
+    synthetic model-C weights (load_state_dict strict=True pins the 566-key contract): logits in fp32 and fp64 plus
+    per-stage feature checksums -> tests/golden/multi_classifier.npz."""
+    from model.modelC_multiClassifier import Multi_Classifier
+    from oracle import modelc_oracle as C
+    torch.set_num_threads(8)
+    sd = C.synth_state_dict_c(seed=0)
+    x, _, _ = O.synth_patches(3, seed=4242)
+    out = {}
+    for dtype, tag in ((torch.float32, "f32"), (torch.float64, "f64")):
+        m = Multi_Classifier(init_weights=False)
+        assert list(m.state_dict().keys()) == [k for k, _, _ in C.state_dict_keys_c()]
+        m.load_state_dict(sd, strict=True)
+        m = m.to(dtype).eval()
+        feats = {}
+        hooks = [getattr(m, n).register_forward_hook(lambda mod, i, o, n=n: feats.__setitem__(n, o.detach()))
+                 for n in ("Conv2d_1a_3x3", "Conv2d_2b_3x3", "Mixed_5d", "Mixed_6a", "Mixed_6e", "Mixed_7a", "Mixed_7c")]
+        with torch.no_grad():
+            y = m(x.to(dtype))
+        for h in hooks:
+            h.remove()
+        out["logits_" + tag] = y.numpy()
+        for n, t in feats.items():
+            out[f"feat_{tag}:{n}"] = np.array([float(t.double().abs().mean()), float(t.double().sum())] + list(t.shape), dtype=np.float64)
+    path = os.path.join(HERE, "multi_classifier.npz")
+    np.savez_compressed(path, **out)
+    print(path, os.path.getsize(path), "bytes", out["logits_f32"][0, :4])
+
+
+if __name__ == "__main__" and "--model-c" in sys.argv:
+    make_model_c()

@@ -1,0 +1,109 @@
+"""Model C (Multi_Classifier, Inception-V3 with a 1-channel stem) on the GPU, through the C ABI, against the oracle
+(oracle/modelc_oracle.py, pinned to the unmodified reference by tests/golden/multi_classifier.npz)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import modelc_oracle as C
+from oracle import mtl_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+# (cin, cout, kh, kw, sh, sw, ph, pw, H, W): every convolution family of the model (modelC:63-83, inception.py)
+CONVC_CASES = [
+    (32, 32, 3, 3, 1, 1, 0, 0, 49, 124),      # Conv2d_2a_3x3 (valid)
+    (32, 64, 3, 3, 1, 1, 1, 1, 47, 122),      # Conv2d_2b_3x3
+    (64, 80, 1, 1, 1, 1, 0, 0, 23, 60),       # Conv2d_3b_1x1 (N = 80)
+    (80, 192, 3, 3, 1, 1, 0, 0, 23, 60),      # Conv2d_4a_3x3 (five K steps: ragged last ring unit)
+    (48, 64, 5, 5, 1, 1, 2, 2, 10, 28),       # InceptionA 5x5
+    (288, 384, 3, 3, 2, 2, 0, 0, 10, 28),     # InceptionB 3x3 stride 2 (two N tiles of 192)
+    (128, 128, 1, 7, 1, 1, 0, 3, 4, 13),      # InceptionC 1x7
+    (160, 192, 7, 1, 1, 1, 3, 0, 4, 13),      # InceptionC 7x1
+    (192, 320, 3, 3, 2, 2, 0, 0, 4, 13),      # InceptionD (N tiles of 160)
+    (384, 384, 1, 3, 1, 1, 0, 1, 1, 6),       # InceptionE 1x3
+    (448, 384, 3, 3, 1, 1, 1, 1, 1, 6),       # InceptionE 3x3 (28 K steps per tap)
+    (2048, 320, 1, 1, 1, 1, 0, 0, 1, 6),      # InceptionE 1x1 over 2048 channels
+]
+
+
+def _planar(x):          # [n, C, H, W] fp32 -> planar-8 bf16 [C/8, n*H*W, 8]
+    n, c, h, w = x.shape
+    return x.permute(1, 0, 2, 3).reshape(c // 8, 8, n * h * w).permute(0, 2, 1).contiguous().to(torch.bfloat16)
+
+
+@pytest.mark.parametrize("case", CONVC_CASES, ids=lambda c: "c%d-%d_k%dx%d_s%d_p%d%d_%dx%d" % (c[0], c[1], c[2], c[3], c[4], c[6], c[7], c[8], c[9]))
+def test_model_c_conv_unit_matches_torch(case):
+    import ctypes
+    from mtldas_b200 import lib
+    from mtldas_b200._lib import check
+    cin, cout, kh, kw, sh, sw, ph, pw, H, W = case
+    n = 5
+    g = torch.Generator().manual_seed(cin + cout + kh)
+    x = torch.randn(n, cin, H, W, generator=g)
+    w = torch.randn(cout, cin, kh, kw, generator=g) / (cin * kh * kw) ** 0.5
+    gamma, beta = torch.rand(cout, generator=g) + 0.5, torch.randn(cout, generator=g) * 0.2
+    rm, rv = torch.randn(cout, generator=g) * 0.1, torch.rand(cout, generator=g) + 0.5
+    xr = x.bfloat16().float()
+    sc = gamma / torch.sqrt(rv + 1e-3)
+    wf = (w * sc.view(-1, 1, 1, 1)).bfloat16().float()                    # the kernel's operands: folded, bf16
+    ref = torch.relu(F.conv2d(xr.double(), wf.double(), (beta - rm * sc).double(), stride=(sh, sw), padding=(ph, pw)))
+    Ho, Wo = ref.shape[2:]
+    dev = torch.device("cuda:0")
+    xp = _planar(xr).to(dev)
+    packed = torch.empty(kh * kw * cin * cout * 2, dtype=torch.uint8, device=dev)
+    bias = torch.empty(cout, device=dev)
+    ctot, c0 = cout + 16, 8                                                # written at a channel offset of a wider tensor
+    out = torch.zeros((ctot // 8, n * Ho * Wo, 8), dtype=torch.bfloat16, device=dev)
+    p = lambda t: ctypes.c_void_p(t.data_ptr())  # noqa: E731
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    keep = [t.to(dev).contiguous() for t in (w, gamma, beta, rm, rv)]
+    check(lib.mtldas_c_pack_conv(p(keep[0]), p(keep[1]), p(keep[2]), p(keep[3]), p(keep[4]), 1e-3, cout, cin, kh, kw, p(packed),
+                                 p(bias), st), "pack")
+    check(lib.mtldas_c_conv(p(xp), n, cin, H, W, p(packed), p(bias), p(out), ctot, c0, cout, kh, kw, sh, sw, ph, pw, 1, st), "conv")
+    got = torch.empty((n, cout, Ho, Wo), device=dev)
+    check(lib.mtldas_c_read(p(out), n, ctot, c0, cout, Ho * Wo, p(got), st), "read")
+    torch.cuda.synchronize()
+    err = float((got.cpu().double() - ref).abs().max() / ref.abs().max())
+    assert err <= 6e-3, (case, err)                                        # one bf16 rounding of the stored result
+    assert float(out[0].abs().max()) == 0.0 and float(out[-1].abs().max()) == 0.0      # neighbours of the slice untouched
+
+
+def test_model_c_forward_matches_oracle():
+    """Multi_Classifier.forward (eval) for 9 patches: logits within 1e-2 of the fp64 oracle (relative to the largest
+    logit; north_star bf16 tolerance), same argmax wherever the top-2 margin is clear, stage features within 2e-2."""
+    from model.modelC_multiClassifier import Multi_Classifier
+    n = 9
+    sd = C.synth_state_dict_c(seed=0)
+    x, _, _ = O.synth_patches(n, seed=4242)
+    with torch.no_grad():
+        ref, feats = C.forward_c(sd, x, torch.float64, return_feats=True)
+    m = Multi_Classifier(init_weights=False)
+    m.load_state_dict(sd, strict=True)
+    m = m.cuda().eval()
+    out = m(x.cuda())
+    torch.cuda.synchronize()
+    assert out.shape == (n, 32) and out.dtype == torch.float32
+    report = {}
+    for name in ("Conv2d_1a_3x3", "Conv2d_2b_3x3", "maxpool2", "Mixed_5b", "Mixed_5d", "Mixed_6a", "Mixed_6e", "Mixed_7a", "Mixed_7c"):
+        got = m.read_tensor(name).cpu().double()
+        r = feats[name]
+        assert got.shape == r.shape, name
+        report[name] = float((got - r).norm() / r.norm())
+    err = float((out.cpu().double() - ref).abs().max() / ref.abs().max())
+    print("model C: stage rel-L2", {k: round(v, 5) for k, v in report.items()}, "logits max-rel", err, "launches", m.last_launch_count)
+    assert all(v <= 2e-2 for v in report.values()), report
+    assert err <= 1e-2, err
+    top2 = ref.topk(2, dim=1).values
+    clear = (top2[:, 0] - top2[:, 1]) > 4 * float((out.cpu().double() - ref).abs().max())
+    assert bool((out.cpu().argmax(1) == ref.argmax(1))[clear].all())
+    # a second call reuses program and packed weights; a parameter change repacks
+    out2 = m(x.cuda())
+    assert torch.equal(out, out2)
+    with torch.no_grad():
+        m.fc.bias.add_(1.0)
+    out3 = m(x.cuda())
+    assert float((out3 - out - 1.0).abs().max()) < 1e-5
+    m.train()
+    from mtldas_b200 import MtldasError
+    with pytest.raises(MtldasError):
+        m(x.cuda())

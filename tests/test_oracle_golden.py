@@ -96,3 +96,29 @@ def test_oracle_process_loads_no_product_code():
             "print('clean')\n") % (root, os.path.join(root, "mtl-das.pytorch_b200"))
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "clean" in r.stdout, r.stderr[-2000:]
+
+
+def test_model_c_oracle_matches_reference():
+    """oracle/modelc_oracle.py::forward_c vs the unmodified Multi_Classifier run in the build container
+    (tests/golden/multi_classifier.npz): logits and per-stage feature statistics, fp32 and fp64; 566-key contract."""
+    from oracle import modelc_oracle as C
+    g = np.load(os.path.join(GOLD, "multi_classifier.npz"))
+    keys = C.state_dict_keys_c()
+    assert len(keys) == 566 and sum(int(np.prod(s)) for k, s, d in keys if d == "float32" and "running" not in k) == 21850560
+    sd = C.synth_state_dict_c(seed=0)
+    x, _, _ = O.synth_patches(3, seed=4242)
+    for dtype, tag, tol in ((torch.float32, "f32", 2e-4), (torch.float64, "f64", 1e-10)):
+        with torch.no_grad():
+            y, feats = C.forward_c(sd, x, dtype, return_feats=True)
+        ref = g["logits_" + tag]
+        assert y.shape == (3, 32)
+        assert float(np.abs(y.numpy() - ref).max()) <= tol * max(1.0, float(np.abs(ref).max())), tag
+        for key in g.files:
+            if key.startswith(f"feat_{tag}:"):
+                t = feats[key.split(":", 1)[1]]
+                want = g[key]
+                assert list(t.shape) == [int(v) for v in want[2:]], key
+                assert abs(float(t.double().abs().mean()) - want[0]) <= 10 * tol * max(1.0, abs(want[0])), key
+    from mtldas_b200 import synth as P
+    pa = P.synth_state_dict_c(0)
+    assert list(pa) == list(sd) and all(torch.equal(pa[k], sd[k]) for k in ("Conv2d_1a_3x3.conv.weight", "Mixed_6c.branch7x7dbl_3.bn.running_var", "fc.weight"))

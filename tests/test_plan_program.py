@@ -67,9 +67,36 @@ def test_modules_keep_reference_contract():
         m(torch.zeros(1, 1, 100, 250))
 
 
+def test_model_c_layer_program_shapes():
+    """Host logic of the model-C layer program (nets_c._Program): 94 convolutions, the pools, concat offsets and the
+    spatial bookkeeping of modelC_multiClassifier.py:102-147 for 100 x 250 patches -- bit-exact integer work."""
+    from mtldas_b200.nets_c import _Program, _SPECS
+    prog = _Program(2, "cpu")
+    convs = [op for op in prog.ops if op[0] == "conv"]
+    pools = [op for op in prog.ops if op[0] == "pool"]
+    assert len(convs) == 94 and sorted(op[4] for op in convs) == sorted(_SPECS)
+    assert len(pools) == 2 + 3 + 1 + 4 + 1 + 2          # maxpool1/2, avg pools of A/C/E blocks, max pools of B/D
+    want = {"Conv2d_1a_3x3": (32, 49, 124), "Conv2d_2b_3x3": (64, 47, 122), "maxpool1": (64, 23, 60),
+            "Conv2d_4a_3x3": (192, 21, 58), "maxpool2": (192, 10, 28), "Mixed_5b": (256, 10, 28), "Mixed_5d": (288, 10, 28),
+            "Mixed_6a": (768, 4, 13), "Mixed_6e": (768, 4, 13), "Mixed_7a": (1280, 1, 6), "Mixed_7c": (2048, 1, 6)}
+    for k, v in want.items():
+        assert prog.shapes[k] == v, (k, prog.shapes[k])
+    assert prog.last == "Mixed_7c"
+    # every channel of every block output is written exactly once
+    for blk in ("Mixed_5b", "Mixed_6a", "Mixed_6c", "Mixed_7a", "Mixed_7c"):
+        cover = []
+        for kind, src, dst, c0, arg in prog.ops:
+            if dst == blk:
+                width = _SPECS[arg][1] if kind == "conv" else prog.shapes[src][0]
+                cover.append((c0, c0 + width))
+        cover.sort()
+        assert cover[0][0] == 0 and cover[-1][1] == prog.shapes[blk][0]
+        assert all(a[1] == b[0] for a, b in zip(cover, cover[1:])), (blk, cover)
+
+
 def test_model_c_boundary_class_and_launcher():
-    """Model C keeps its constructor / state_dict contract (566 keys) and refuses to run (kernels are
-    the next row); the launcher binds an (absent here or present) reference utils.py to the drop-in modules."""
+    """Model C keeps its constructor / state_dict contract (566 keys, SURVEY App. C) and has no CPU fallback;
+    the launcher binds an (absent here or present) reference utils.py to the drop-in modules."""
     from model.modelC_multiClassifier import Multi_Classifier
     from mtldas_b200 import MtldasError
     m = Multi_Classifier(init_weights=False)
