@@ -280,6 +280,31 @@ def measure_extras(args, dev, world, rank, barrier):
         out["model_b_" + kind] = {"value": world * B / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "batch_per_gpu": B,
                                   "workload": "Single_Task_Net inference, inputs resident"}
         del plan, outs
+    # model C (Multi_Classifier = Inception-V3, BASELINE.json configs[4]): eval forward, compute bound -> tensor roofline
+    try:
+        from mtldas_b200.nets_c import Multi_Classifier
+        nc = min(B, 512)
+        mc = Multi_Classifier(init_weights=False)
+        mc.load_state_dict(O.synth_state_dict_c(seed=0), strict=True)
+        mc = mc.to(dev).eval()
+        xc = x[:nc].contiguous()
+        ms = timed(lambda: mc(xc))
+        flop = 2 * 1.109e9 * nc                       # 1.109 GMAC per patch (94 convolutions)
+        try:
+            pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            peak_tf, src = float(pk["bf16_tflops"]), "measured (burst)"
+        except Exception:
+            peak_tf, src = 1650.0, "fallback"
+        ach = flop / (ms * 1e-3) / 1e12
+        out["model_c"] = {"value": world * nc / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "batch_per_gpu": nc,
+                          "workload": "Multi_Classifier (Inception-V3, 1-channel stem, 32 classes) eval forward, inputs resident",
+                          "gpu_launches_per_step": mc.last_launch_count,
+                          "roofline": {"bound": "tensor", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s",
+                                       "frac": ach / peak_tf, "traffic": None, "peak_source": src,
+                                       "algorithmic_flop_per_step": flop}}
+        del mc
+    except Exception as e:      # the headline must not die on a side measurement
+        out["model_c"] = {"error": repr(e)[:300]}
     # streaming: [n_channels, n_time] fp32 per rank, window 100 channels x 250 samples, channel stride 10
     n_ch, n_time, stride = 2140, 250 * 20, 10
     si = StreamingInference(O.synth_state_dict("MTL", seed=0), "MTL", args.precision, min(B, args.micro_batch), stride, dev)
