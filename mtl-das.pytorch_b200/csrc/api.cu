@@ -1,6 +1,8 @@
 // extern "C" surface of libmtldas_b200.so (see include/mtldas.h).
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "../../include/mtldas.h"
 #include "kernels.h"
@@ -131,6 +133,32 @@ int mtldas_plan_forward_eval(mtldas_plan* plan, const float* dev_x, int n, float
   return plan_forward_eval(*plan->p, dev_x, n, dev_out0, dev_out1, (cudaStream_t)stream);
 }
 
+// Chunk sizes of the host entry point.  fp32 patches: the PCIe copy is the bottleneck (55 GB/s = 554 k patches/s against
+// 600-800 k/s of compute), every chunk's compute hides under the next chunk's copy and only the LAST chunk's compute
+// is exposed -> 512-patch chunks with a short tail.  bf16 patches (half the bytes): compute is the bottleneck, only
+// the FIRST copy is exposed and large chunks run faster (launch / tail overheads) -> 256, 512, 1024, 2048, ...
+static std::vector<int> host_chunk_schedule(int n, int max_chunk, bool x_is_bf16) {
+  std::vector<int> out;
+  int rem = n;
+  if (x_is_bf16) {
+    int c = 256;
+    while (rem > 0) {
+      const int take = std::min(std::min(c, max_chunk), rem);
+      out.push_back(take), rem -= take;
+      c *= 2;
+    }
+  } else {
+    const int c = std::min(512, max_chunk);
+    while (rem > c + c / 2) out.push_back(c), rem -= c;
+    if (rem > c / 2 && rem > 64) {       // split the tail: the last compute is the exposed one
+      out.push_back(rem - rem / 2), out.push_back(rem / 2);
+    } else if (rem > 0) {
+      out.push_back(rem);
+    }
+  }
+  return out;
+}
+
 static int forward_eval_host_impl(mtldas_plan* plan, const void* host_x_any, bool x_is_bf16, int n, float* host_out0,
                                   float* host_out1, void* stream) {
   if (!plan || !host_x_any || !host_out0 || n < 0) {
@@ -168,9 +196,10 @@ static int forward_eval_host_impl(mtldas_plan* plan, const void* host_x_any, boo
   // Two staging slots: the copy stream brings pass i+1 in while the caller's stream computes pass i.
   CKH(cudaEventRecord(p.ev_start, st));
   CKH(cudaStreamWaitEvent(p.copy_stream, p.ev_start, 0));
-  int launches = 0, i = 0;
-  for (int s = 0; s < n; s += chunk, ++i) {
-    const int nb = n - s < chunk ? n - s : chunk;
+  int launches = 0, i = 0, s = 0;
+  const std::vector<int> schedule = host_chunk_schedule(n, chunk, x_is_bf16);
+  for (size_t ci = 0; ci < schedule.size(); s += schedule[ci], ++ci, ++i) {
+    const int nb = schedule[ci];
     const int slot = i & 1;
     if (i >= 2) CKH(cudaStreamWaitEvent(p.copy_stream, p.ev_comp[slot], 0));  // slot free again
     if (x_is_bf16)   // half the bytes over PCIe; widened on the device (exact), the stem rounds to the same bf16 values

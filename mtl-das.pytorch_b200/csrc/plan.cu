@@ -477,11 +477,11 @@ Plan* build_plan(int kind, int mb, int precision, bool training) {
   p.stem_w_off = take(49 * 16 * 4);
   p.stem_b_off = take(16 * 4);
   p.stem_wu_off = take(2048);
-  // host entry point: chunks of at most 512 patches through two staging slots (H2D of chunk i+1 overlaps chunk i;
-  // the copy is the bottleneck, so the un-overlapped tail is the compute of the LAST chunk: keep it short)
+  // host entry point: the batch goes through two staging slots in chunks (H2D of chunk i+1 under the compute of chunk
+  // i); the slots hold the largest chunk of the schedule (api.cu::host_chunk_schedule)
   {
     const char* e = getenv("MTLDAS_HOST_CHUNK");
-    int hc = e ? atoi(e) : 512;  // measured end to end at batch 4096: 1024 -> 460 k, 512 -> 495 k, 256 -> 426 k samples/s
+    int hc = e ? atoi(e) : 2048;
     if (hc < 64) hc = 64;
     p.host_chunk = std::min(mb, hc);
   }
@@ -762,7 +762,7 @@ int plan_forward_eval(Plan& p, const float* x, int n, float* out0, float* out1, 
   for (auto& g : p.graphs)
     if (g.x == x && g.n == n && g.o0 == out0 && g.o1 == out1) e = &g;
   if (!e) {
-    if (p.graphs.size() >= 8) {  // evict the least recently used entry
+    if (p.graphs.size() >= 24) {  // evict the least recently used entry (the host schedule uses 2 slots x 5 chunk sizes)
       size_t victim = 0;
       for (size_t i = 1; i < p.graphs.size(); ++i)
         if (p.graphs[i].stamp < p.graphs[victim].stamp) victim = i;
