@@ -133,29 +133,21 @@ int mtldas_plan_forward_eval(mtldas_plan* plan, const float* dev_x, int n, float
   return plan_forward_eval(*plan->p, dev_x, n, dev_out0, dev_out1, (cudaStream_t)stream);
 }
 
-// Chunk sizes of the host entry point.  fp32 patches: the PCIe copy is the bottleneck (55 GB/s = 554 k patches/s against
-// 600-800 k/s of compute), every chunk's compute hides under the next chunk's copy and only the LAST chunk's compute
-// is exposed -> 512-patch chunks with a short tail.  bf16 patches (half the bytes): compute is the bottleneck, only
-// the FIRST copy is exposed and large chunks run faster (launch / tail overheads) -> 256, 512, 1024, 2048, ...
+// Chunk sizes of the host entry point (two staging slots: the copy of chunk i+1 runs under the compute of chunk i).
+// Measured end to end at 4096 patches: fp32 patches are bound by the PCIe copy (55 GB/s = 554 k patches/s) and want
+// short chunks (256 -> 418 k, 512 -> 495 k, 1024 -> 463 k patches/s: the exposed tail is the last chunk's compute);
+// bf16 patches (half the bytes) are bound by compute and want larger ones (512 -> 540 k, 1024 -> 594 k, 2048 -> 561 k).
+// Growing / shrinking schedules measured worse than the constants (more chunks, more per-chunk fixed cost).
 static std::vector<int> host_chunk_schedule(int n, int max_chunk, bool x_is_bf16) {
-  std::vector<int> out;
-  int rem = n;
-  if (x_is_bf16) {
-    int c = 256;
-    while (rem > 0) {
-      const int take = std::min(std::min(c, max_chunk), rem);
-      out.push_back(take), rem -= take;
-      c *= 2;
-    }
-  } else {
-    const int c = std::min(512, max_chunk);
-    while (rem > c + c / 2) out.push_back(c), rem -= c;
-    if (rem > c / 2 && rem > 64) {       // split the tail: the last compute is the exposed one
-      out.push_back(rem - rem / 2), out.push_back(rem / 2);
-    } else if (rem > 0) {
-      out.push_back(rem);
-    }
+  static int env_chunk = -1;
+  if (env_chunk < 0) {
+    const char* e = getenv("MTLDAS_HOST_CHUNK_SIZE");
+    env_chunk = e ? atoi(e) : 0;
   }
+  int c = env_chunk > 0 ? env_chunk : (x_is_bf16 ? 1024 : 512);
+  c = std::max(1, std::min(c, max_chunk));
+  std::vector<int> out;
+  for (int rem = n; rem > 0; rem -= std::min(c, rem)) out.push_back(std::min(c, rem));
   return out;
 }
 
