@@ -47,7 +47,7 @@ def main():
         out.append(" | ".join(cells))
     txt = os.path.join(ROOT, "profiles", f"r2_conv_ncu_full_batch{batch}.txt")
     with open(txt, "w") as f:
-        f.write("MTLDAS_NO_GRAPH=1 ncu --set full --clock-control none --import-source on -k regex:conv_umma --launch-skip 30 -c 30 "
+        f.write("MTLDAS_NO_GRAPH=1 ncu --set full --clock-control none -k regex:conv_umma --launch-skip 30 -c 30 "
                 f"python tools/one_forward.py {batch}\n(the conv launches of ONE eager MTL forward at batch {batch}, {precision}, build {version}; "
                 "per-launch values, cold cache, serialised)\n")
         f.write(f"sum over the {n} conv launches: dram read {tot_r / 1e6:.0f} MB + write {tot_w / 1e6:.0f} MB = {(tot_r + tot_w) / 1e6:.0f} MB; time {tot_t:.0f} us\n")
