@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=256, help="patches per CPU-baseline step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the model B / streaming side measurements")
+    ap.add_argument("--model-c-batch", type=int, default=512, help="patches per GPU per step of the model C side measurement")
     ap.add_argument("--no-train", action="store_true", help="skip the training-step measurement (kernel tuning runs)")
     ap.add_argument("--train-batch", type=int, default=256, help="training patches per GPU per step")
     return ap.parse_args()
@@ -283,7 +284,7 @@ def measure_extras(args, dev, world, rank, barrier):
     # model C (Multi_Classifier = Inception-V3, BASELINE.json configs[4]): eval forward, compute bound -> tensor roofline
     try:
         from mtldas_b200.nets_c import Multi_Classifier
-        nc = min(B, 512)
+        nc = min(B, args.model_c_batch)
         mc = Multi_Classifier(init_weights=False)
         mc.load_state_dict(O.synth_state_dict_c(seed=0), strict=True)
         mc = mc.to(dev).eval()

@@ -89,6 +89,13 @@ __device__ __forceinline__ long long gtime() {
     p.dbg[(size_t)blockIdx.x * 16 + (slot) + 1] = clock64();                             \
   }
 
+// relu + round-to-nearest bf16 of two floats in one instruction; lo lands in the low half (lower channel)
+__device__ __forceinline__ uint32_t relu_pack_bf16x2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+
 // Epilogue of 16 consecutive channels [c0, c0+16) of one output position held in registers.
 // Everything it needs is passed in registers (the asm "memory" clobbers of the pipeline would otherwise make
 // the compiler re-read the kernel parameter block for every use).
@@ -109,6 +116,21 @@ __device__ __forceinline__ void epilogue_cols(const float* bias_s, int c0, bool 
     for (int q = 0; q < 4; ++q) {
       const float4 bb = b4[q];
       v[4 * q + 0] += bb.x, v[4 * q + 1] += bb.y, v[4 * q + 2] += bb.z, v[4 * q + 3] += bb.w;
+    }
+    if ((EPI == EPI_ADD_RELU || EPI == EPI_RELU) && sizeof(T) == 2) {
+      // ReLU folded into the bf16 conversion (cvt.rn.relu.bf16x2): 8 instructions instead of 16 max + 8 cvt
+      if (EPI == EPI_ADD_RELU) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] += a[j];
+      }
+      uint4 q0, q1;
+      q0.x = relu_pack_bf16x2(v[0], v[1]), q0.y = relu_pack_bf16x2(v[2], v[3]);
+      q0.z = relu_pack_bf16x2(v[4], v[5]), q0.w = relu_pack_bf16x2(v[6], v[7]);
+      q1.x = relu_pack_bf16x2(v[8], v[9]), q1.y = relu_pack_bf16x2(v[10], v[11]);
+      q1.z = relu_pack_bf16x2(v[12], v[13]), q1.w = relu_pack_bf16x2(v[14], v[15]);
+      *reinterpret_cast<uint4*>(out_addr0 + ch * out_plane_bytes) = q0;
+      *reinterpret_cast<uint4*>(out_addr0 + (ch + 1) * out_plane_bytes) = q1;
+      return;
     }
     if (EPI == EPI_ADD_RELU) {
 #pragma unroll
