@@ -261,21 +261,29 @@ __global__ void __launch_bounds__(256) convc_first_kernel(const float* __restric
 __global__ void __launch_bounds__(256) poolc_kernel(const char* __restrict__ x, char* __restrict__ out, int n, int chunks,
                                                     int H, int W, int Ho, int Wo, int stride, int pad, int is_avg,
                                                     int out_chunk0) {
-  const long long Mo = (long long)n * Ho * Wo, Mi = (long long)n * H * W, total = Mo * chunks;
-  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
-    const int c = (int)(i / Mo);
-    const long long m = i - (long long)c * Mo;
-    const int img = (int)(m / (Ho * Wo));
-    const int rem = (int)(m - (long long)img * Ho * Wo);
-    const int ho = rem / Wo, wo = rem - ho * Wo;
+  // grid = (position blocks, channel chunks): 32-bit index arithmetic only (64-bit divisions dominated the first version)
+  const unsigned Mo = (unsigned)n * Ho * Wo, hw = (unsigned)Ho * Wo;
+  const long long Mi = (long long)n * H * W;
+  const int c = blockIdx.y;
+  const char* xin = x + (long long)c * Mi * 16;
+  char* dst = out + (long long)(out_chunk0 + c) * Mo * 16;
+  for (unsigned m = blockIdx.x * 256u + threadIdx.x; m < Mo; m += gridDim.x * 256u) {
+    const unsigned img = m / hw, rem = m - img * hw;
+    const int ho = (int)(rem / (unsigned)Wo), wo = (int)(rem - (unsigned)ho * Wo);
+    const int h0 = ho * stride - pad, w0 = wo * stride - pad;
     float acc[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = is_avg ? 0.f : -INFINITY;
-    for (int r = 0; r < 3; ++r)
+    const char* base = xin + ((long long)img * H * W) * 16;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int hi = h0 + r;
+      if (hi < 0 || hi >= H) continue;
+#pragma unroll
       for (int q = 0; q < 3; ++q) {
-        const int hi = ho * stride + r - pad, wi = wo * stride + q - pad;
-        if (hi < 0 || hi >= H || wi < 0 || wi >= W) continue;
-        const uint4 g = *reinterpret_cast<const uint4*>(x + ((long long)c * Mi + ((long long)img * H + hi) * W + wi) * 16);
+        const int wi = w0 + q;
+        if (wi < 0 || wi >= W) continue;
+        const uint4 g = *reinterpret_cast<const uint4*>(base + (hi * W + wi) * 16);
         const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&g);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -284,12 +292,13 @@ __global__ void __launch_bounds__(256) poolc_kernel(const char* __restrict__ x, 
           else acc[2 * j] = fmaxf(acc[2 * j], f.x), acc[2 * j + 1] = fmaxf(acc[2 * j + 1], f.y);
         }
       }
+    }
     uint4 o;
     __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
     const float sc = is_avg ? (1.f / 9.f) : 1.f;
 #pragma unroll
     for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(acc[2 * j] * sc, acc[2 * j + 1] * sc);
-    *reinterpret_cast<uint4*>(out + ((long long)(out_chunk0 + c) * Mo + m) * 16) = o;
+    *reinterpret_cast<uint4*>(dst + (long long)m * 16) = o;
   }
 }
 
@@ -445,8 +454,14 @@ extern "C" int mtldas_c_pool(const void* dev_x, int n, int channels, int h, int 
     set_error("c_pool: bad arguments");
     return MTLDAS_ERR_ARG;
   }
-  const long long total = (long long)n * Ho * Wo * (channels / 8);
-  poolc_kernel<<<(int)std::min<long long>(148 * 16, (total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+  const long long mo = (long long)n * Ho * Wo;
+  if (mo >= (1ll << 31) || (long long)n * h * w >= (1ll << 27)) {
+    set_error("c_pool: batch too large for the 32-bit index arithmetic of this kernel");
+    return MTLDAS_ERR_UNSUPPORTED;
+  }
+  const int chunks = channels / 8;
+  const unsigned bx = (unsigned)std::max<long long>(1, std::min<long long>((mo + 255) / 256, (148 * 16 + chunks - 1) / chunks));
+  poolc_kernel<<<dim3(bx, (unsigned)chunks), 256, 0, (cudaStream_t)stream>>>(
       (const char*)dev_x, (char*)dev_out, n, channels / 8, h, w, Ho, Wo, stride, pad, is_avg, out_channel0 / 8);
   CKC(cudaGetLastError(), "c_pool");
   return 0;
