@@ -248,6 +248,14 @@ MTLDAS_API int mtldas_c_read(const void* dev_x, int n, int channels_total, int c
  * channels first_channel + wi*window_stride .. +100, time block tb covers samples tb*250 .. +250
  * (n_time / 250 full blocks); dev_patches receives [n_windows * (n_time/250), 1, 100, 250], window-major.
  * Shard windows across GPUs with no collective (mtldas_b200.ddp.shard_windows). */
+/* The same forward WITHOUT materialising the patches: the stem reads every window's 100 rows x 250 samples straight
+ * out of dev_array (one bulk copy per input row, row pitch n_time), outputs [n_windows * (n_time/250), classes],
+ * window-major.  Each array element is read once per window that covers it instead of being copied into a patch
+ * tensor and read again.  bf16 plan only; dev_array 16-byte aligned and n_time a multiple of 4 (else
+ * MTLDAS_ERR_UNSUPPORTED: gather with mtldas_window_gather and call mtldas_plan_forward_eval). */
+MTLDAS_API int mtldas_plan_forward_eval_windows(mtldas_plan* plan, const float* dev_array, long long n_channels,
+                                                long long n_time, int first_channel, int window_stride, int n_windows,
+                                                float* dev_out0, float* dev_out1, void* stream);
 MTLDAS_API int mtldas_window_gather(const float* dev_array, long long n_channels, long long n_time, int first_channel,
                                     int window_stride, int n_windows, float* dev_patches, void* stream);
 

@@ -267,6 +267,18 @@ int mtldas_nll_loss(const float* dev_logp0, const long long* dev_y0, int classes
   return 0;
 }
 
+int mtldas_plan_forward_eval_windows(mtldas_plan* plan, const float* dev_array, long long n_channels, long long n_time,
+                                     int first_channel, int window_stride, int n_windows, float* dev_out0,
+                                     float* dev_out1, void* stream) {
+  if (!plan || !dev_array || !dev_out0 || window_stride < 1 || first_channel < 0) {
+    set_error("forward_eval_windows: bad arguments");
+    return MTLDAS_ERR_ARG;
+  }
+  if (n_windows == 0) return 0;
+  return plan_forward_windows(*plan->p, dev_array, n_channels, n_time, first_channel, window_stride, n_windows, dev_out0,
+                              dev_out1, (cudaStream_t)stream);
+}
+
 int mtldas_window_gather(const float* dev_array, long long n_channels, long long n_time, int first_channel,
                          int window_stride, int n_windows, float* dev_patches, void* stream) {
   if (!dev_array || !dev_patches || n_windows < 0 || window_stride < 1 || first_channel < 0 || n_time < kPatchW ||

@@ -39,6 +39,7 @@ float umma_selftest(int n_cols, int row_shift, int swap);
 int umma_rate(int n_cols, int mode, int reps, float* host_out2);
 
 cudaError_t launch_stem(const StemParams& p, int precision, cudaStream_t stream, bool pdl = false);
+cudaError_t launch_stem_umma(const StemParams& p, cudaStream_t stream, bool pdl);   // cudaErrorInvalidValue: not eligible
 cudaError_t launch_pool(const PoolParams& p, int precision, cudaStream_t stream, bool pdl = false);
 cudaError_t launch_head(const HeadParams& p, int precision, cudaStream_t stream, bool pdl = false);
 cudaError_t launch_pack(const PackParams& p, cudaStream_t stream);

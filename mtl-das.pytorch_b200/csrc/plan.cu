@@ -608,7 +608,7 @@ int plan_pack_eval(Plan& p, const void* const* state, cudaStream_t stream) {
 // forward (eval)
 // ---------------------------------------------------------------------------------------------
 static int run_pass(Plan& p, const float* x, int nb, float* out0, float* out1, cudaStream_t stream,
-                    std::vector<cudaEvent_t>* evs = nullptr, bool first_pass = true) {
+                    std::vector<cudaEvent_t>* evs = nullptr, bool first_pass = true, const StemSource* src = nullptr) {
   bool first_op = true;
   for (const Op& op : p.program) {
     // programmatic dependent launch for everything but the first kernel of a forward (what runs before it on the
@@ -631,7 +631,23 @@ static int run_pass(Plan& p, const float* x, int nb, float* out0, float* out1, c
       q.Hin = kPatchH, q.Win = kPatchW, q.H = t.H, q.W = t.W, q.Wp = t.Wp, q.Pimg = t.Pimg;
       q.body = (long long)nb * t.Pimg;
       q.w_umma = (p.precision == 0 && p.use_umma_stem) ? p.ws + p.stem_wu_off : nullptr;
-      CK(launch_stem(q, p.precision, stream, pdl));
+      if (src && src->nt > 0) {   // windows of a streaming array, read in place (tensor-core stem only)
+        q.x_stride_a = src->stride_a, q.x_stride_b = src->stride_b, q.x_row_pitch = src->row_pitch;
+        q.x_nt = src->nt, q.x_n0 = src->n0;
+        if (!q.w_umma) {
+          set_error("forward_windows: needs the bf16 tensor-core stem");
+          return -4;
+        }
+        cudaError_t se = launch_stem_umma(q, stream, pdl);
+        if (se == cudaErrorInvalidValue) {
+          cudaGetLastError();
+          set_error("forward_windows: the array must be 16-byte aligned with n_time a multiple of 4");
+          return -4;
+        }
+        CK(se);
+      } else {
+        CK(launch_stem(q, p.precision, stream, pdl));
+      }
     } else if (op.kind == 1) {
       ConvParams q = p.conv_params(p.convs[op.index], nb);
       static int pool_dbg = -1;
@@ -736,6 +752,38 @@ static int forward_eager(Plan& p, const float* x, int n, float* out0, float* out
     int nb = std::min(p.mb, n - s);
     int rc = run_pass(p, x + (size_t)s * kPatchH * kPatchW, nb, out0 + (size_t)s * c0,
                       out1 ? out1 + (size_t)s * c1 : nullptr, stream, nullptr, s == 0);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
+int plan_forward_windows(Plan& p, const float* array, long long n_channels, long long n_time, int first_channel,
+                         int window_stride, int n_windows, float* out0, float* out1, cudaStream_t stream) {
+  if (!p.ws || !p.packed) {
+    set_error("forward_windows: bind a workspace and pack weights first");
+    return -3;
+  }
+  if (p.precision != 0 || !p.use_umma_stem || (n_time & 3) || (reinterpret_cast<uintptr_t>(array) & 15)) {
+    set_error("forward_windows: needs the bf16 plan with the tensor-core stem, a 16-byte aligned array and n_time %% 4 == 0 "
+              "(otherwise gather the windows with mtldas_window_gather)");
+    return -4;
+  }
+  const int nt = (int)(n_time / kPatchW);
+  const long long n = (long long)n_windows * nt;
+  if (nt < 1 || n_windows < 0 || n > (1ll << 30) ||
+      (long long)first_channel + (long long)(n_windows > 0 ? n_windows - 1 : 0) * window_stride + kPatchH > n_channels) {
+    set_error("forward_windows: windows do not fit the array");
+    return -1;
+  }
+  StemSource src;
+  src.stride_a = (long long)window_stride * n_time, src.stride_b = kPatchW, src.row_pitch = n_time, src.nt = nt;
+  const float* base = array + (long long)first_channel * n_time;
+  const int c0 = p.heads[0].classes, c1 = p.heads.size() > 1 ? p.heads[1].classes : 0;
+  p.last_launches = 0;
+  for (long long s = 0; s < n; s += p.mb) {
+    const int nb = (int)std::min<long long>(p.mb, n - s);
+    src.n0 = (int)s;
+    int rc = run_pass(p, base, nb, out0 + (size_t)s * c0, out1 ? out1 + (size_t)s * c1 : nullptr, stream, nullptr, s == 0, &src);
     if (rc) return rc;
   }
   return 0;

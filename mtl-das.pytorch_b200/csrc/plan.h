@@ -69,6 +69,11 @@ struct Op {
   int index;
 };
 
+struct StemSource {   // see StemParams::x_stride_a ... (types.h); nt == 0: contiguous patches
+  long long stride_a = 0, stride_b = 0, row_pitch = 0;
+  int nt = 0, n0 = 0;
+};
+
 struct Plan {
   int kind, mb, precision, ntasks;
   bool training = false;   // plan built for the training program (no inference-only re-groupings)
@@ -127,6 +132,11 @@ bool split_output_channels(ConvOpHost& op, long long positions, bool even_if_res
 int persist_stages_for(const ConvOpHost& op, size_t extra);
 int plan_pack_eval(Plan& p, const void* const* state, cudaStream_t stream);
 int plan_forward_eval(Plan& p, const float* x, int n, float* out0, float* out1, cudaStream_t stream);
+
+// Forward over the windows of a streaming array read IN PLACE by the stem (no patch tensor): window wi = fibre channels
+// first_channel + wi*window_stride .. +100, time block tb = samples tb*250 .. +250; outputs window-major.
+int plan_forward_windows(Plan& p, const float* array, long long n_channels, long long n_time, int first_channel,
+                         int window_stride, int n_windows, float* out0, float* out1, cudaStream_t stream);
 
 int plan_profile_eval(Plan& p, const float* x, int n, float* out0, float* out1, cudaStream_t stream,
                       float* ms_per_op, int cap);

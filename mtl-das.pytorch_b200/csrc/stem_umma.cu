@@ -47,8 +47,12 @@ __global__ void __launch_bounds__(kStemThreads, 1) stem_umma_kernel(const __grid
   const uint32_t row_pitch = (uint32_t)p.Wp * 16u;             // one windowed input row
   const uint32_t ybuf_bytes = ((uint32_t)kStemInRows * row_pitch + (128u - (uint32_t)p.Wp) * 16u + 127u) & ~127u;
   uint8_t* ybuf = smem + 256 + 2048;                           // [2][kStemInRows][Wp][16 B] (+ slack for rows >= Wp)
-  const uint32_t raw_bytes = ((uint32_t)(kStemInRows - 1) * (uint32_t)p.Win * 4u + 32u + 127u) & ~127u;
+  const uint32_t raw_bytes = (uint32_t)p.raw_stage_bytes;
   uint8_t* rawbuf = ybuf + 2 * ybuf_bytes;                     // [2] fp32 staging of a unit's input rows
+  // windowed source (rows of an image are x_row_pitch floats apart, e.g. windows of a streaming array): one bulk copy
+  // per input row into a staging row of raw_pitch bytes; contiguous patches: ONE bulk copy per unit
+  const bool windowed = p.x_row_pitch != (long long)p.Win;
+  const uint32_t raw_pitch = ((uint32_t)p.Win * 4u + 16u + 15u) & ~15u;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   ptx::pdl_launch_dependents();
@@ -111,13 +115,27 @@ __global__ void __launch_bounds__(kStemThreads, 1) stem_umma_kernel(const __grid
         const int n = stem_fdiv(u, magic_upi), q = u - n * units_per_image;
         const int h0 = q * kStemRows, rows = min(kStemRows, p.H - h0);
         const int ya = max(3 * h0 - 2, 0), yb = min(3 * h0 - 2 + 3 * rows + 4, p.Hin);
-        const unsigned long long lo = ((unsigned long long)(n * p.Hin + ya) * p.Win) * 4ull;
-        const unsigned long long hi = ((unsigned long long)(n * p.Hin + yb) * p.Win) * 4ull;
-        const unsigned long long alo = lo & ~15ull, ahi = (hi + 15ull) & ~15ull;
-        const uint32_t bytes = (uint32_t)(ahi - alo);
-        ptx::mbar_arrive_expect_tx(bars + kStemBarRawFull + b, bytes);
-        ptx::bulk_g2s(rawbuf + (size_t)b * raw_bytes, reinterpret_cast<const char*>(p.x) + alo, bytes,
-                      bars + kStemBarRawFull + b);
+        const long long gi = (long long)n + p.x_n0;
+        const unsigned long long img = (unsigned long long)((gi / p.x_nt) * p.x_stride_a + (gi % p.x_nt) * p.x_stride_b);
+        if (!windowed) {
+          const unsigned long long lo = (img + (unsigned long long)ya * p.Win) * 4ull;
+          const unsigned long long hi = (img + (unsigned long long)yb * p.Win) * 4ull;
+          const unsigned long long alo = lo & ~15ull, ahi = (hi + 15ull) & ~15ull;
+          const uint32_t bytes = (uint32_t)(ahi - alo);
+          ptx::mbar_arrive_expect_tx(bars + kStemBarRawFull + b, bytes);
+          ptx::bulk_g2s(rawbuf + (size_t)b * raw_bytes, reinterpret_cast<const char*>(p.x) + alo, bytes,
+                        bars + kStemBarRawFull + b);
+        } else {
+          // every row starts at the same offset inside its 16-byte line (x_row_pitch is a multiple of 4 floats)
+          const unsigned long long a0 = (img + (unsigned long long)ya * (unsigned long long)p.x_row_pitch) * 4ull;
+          const uint32_t row_bytes = (uint32_t)(((a0 & 15ull) + (unsigned long long)p.Win * 4ull + 15ull) & ~15ull);
+          ptx::mbar_arrive_expect_tx(bars + kStemBarRawFull + b, row_bytes * (uint32_t)(yb - ya));
+          for (int y = ya; y < yb; ++y) {
+            const unsigned long long a = (img + (unsigned long long)y * (unsigned long long)p.x_row_pitch) * 4ull;
+            ptx::bulk_g2s(rawbuf + (size_t)b * raw_bytes + (size_t)(y - ya) * raw_pitch,
+                          reinterpret_cast<const char*>(p.x) + (a & ~15ull), row_bytes, bars + kStemBarRawFull + b);
+          }
+        }
       }
     }
     __syncwarp();
@@ -132,7 +150,11 @@ __global__ void __launch_bounds__(kStemThreads, 1) stem_umma_kernel(const __grid
       const int h0 = q * kStemRows, rows = min(kStemRows, p.H - h0);
       const int y0 = 3 * h0 - 2, total = (3 * rows + 5) * p.Wp;
       const int ya = max(y0, 0), yb = min(y0 + 3 * rows + 4, p.Hin);
-      const int mis = (int)((((unsigned long long)(n * p.Hin + ya) * p.Win) * 4ull & 15ull) >> 2);
+      const long long gi = (long long)n + p.x_n0;
+      const unsigned long long img = (unsigned long long)((gi / p.x_nt) * p.x_stride_a + (gi % p.x_nt) * p.x_stride_b);
+      const unsigned long long first = img + (unsigned long long)ya * (unsigned long long)(windowed ? p.x_row_pitch : (long long)p.Win);
+      const int mis = (int)((first * 4ull & 15ull) >> 2);
+      const int src_pitch = windowed ? (int)(raw_pitch >> 2) : p.Win;   // floats between staged rows
       uint8_t* dst = ybuf + (size_t)b * ybuf_bytes;
       const float* raw = reinterpret_cast<const float*>(rawbuf + (size_t)b * raw_bytes) + mis;
       ptx::mbar_wait(bars + kStemBarRawFull + b, (it >> 1) & 1);
@@ -141,7 +163,7 @@ __global__ void __launch_bounds__(kStemThreads, 1) stem_umma_kernel(const __grid
         const int r = stem_fdiv(g, magic_wp), j = g - r * p.Wp;
         const int iy = y0 + r, ix0 = 3 * j - 2;
         const bool row_ok = iy >= ya && iy < yb;
-        const float* src = raw + (row_ok ? iy - ya : 0) * p.Win;
+        const float* src = raw + (row_ok ? iy - ya : 0) * src_pitch;
         float v[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -207,14 +229,24 @@ __global__ void __launch_bounds__(kStemThreads, 1) stem_umma_kernel(const __grid
   if (warp == 4) ptx::tmem_dealloc(tmem_base, 512);
 }
 
-cudaError_t launch_stem_umma(const StemParams& p, cudaStream_t stream, bool pdl) {
+cudaError_t launch_stem_umma(const StemParams& p_in, cudaStream_t stream, bool pdl) {
+  StemParams p = p_in;
+  if (p.x_nt == 0) p.x_nt = 1, p.x_n0 = 0, p.x_stride_a = (long long)p.Hin * p.Win, p.x_stride_b = 0, p.x_row_pitch = p.Win;
+  const bool windowed = p.x_row_pitch != (long long)p.Win;
   const size_t row_pitch = (size_t)p.Wp * 16;
   const size_t ybuf = (((size_t)(3 * kStemRows + 5) * row_pitch + (size_t)(128 - p.Wp) * 16) + 127) & ~(size_t)127;
-  const size_t raw = ((size_t)(3 * kStemRows + 4) * p.Win * 4 + 32 + 127) & ~(size_t)127;
+  const size_t raw_contig = (size_t)(3 * kStemRows + 4) * p.Win * 4 + 32;
+  const size_t raw_rows = (size_t)(3 * kStemRows + 4) * ((((size_t)p.Win * 4 + 16 + 15) & ~(size_t)15));
+  const size_t raw = ((windowed ? raw_rows : raw_contig) + 127) & ~(size_t)127;
+  p.raw_stage_bytes = (int)raw;
   const size_t smem = 256 + 2048 + 2 * ybuf + 2 * raw;
-  // bulk copies need 16-byte aligned spans: the patch tensor must start aligned and an image must be a multiple of 16 B
-  if (p.Wp > 128 || smem > 225 * 1024 || (reinterpret_cast<uintptr_t>(p.x) & 15) || ((size_t)p.Hin * p.Win * 4) % 16)
-    return cudaErrorInvalidValue;
+  // bulk copies need 16-byte aligned spans: the source must start aligned; contiguous patches: an image must be a
+  // multiple of 16 B; windowed rows: the row pitch and the image strides must be multiples of 4 floats... except the
+  // time-block stride (Win = 250 floats): blocks alternate between offsets 0 and 8 inside a 16-byte line, handled
+  // per image by the kernel
+  if (p.Wp > 128 || smem > 225 * 1024 || (reinterpret_cast<uintptr_t>(p.x) & 15)) return cudaErrorInvalidValue;
+  if (!windowed && ((size_t)p.Hin * p.Win * 4) % 16) return cudaErrorInvalidValue;
+  if (windowed && ((p.x_row_pitch & 3) || (p.x_stride_a & 1) || (p.x_stride_b & 1))) return cudaErrorInvalidValue;
   static PerDeviceSmem configured;
   {
     cudaError_t e = configured.ensure(smem, [](int bytes) {

@@ -92,6 +92,13 @@ struct StemParams {        // 7x7 / stride 3 / pad 2, Cin = 1 (modelA_MTL.py:74)
   long long body;
   int raw;                 // 1: store conv + bias without the ReLU (training: BatchNorm follows as its own pass)
   const char* w_umma;      // bf16 UMMA image [8 K-chunks][16 cout][8] (K = 49 taps padded to 64) or null
+  // Where image n's samples live, in floats from x (all zero = a contiguous patch tensor [nb,1,Hin,Win]):
+  //   first sample of image n = ((n + x_n0) / x_nt) * x_stride_a + ((n + x_n0) % x_nt) * x_stride_b, rows x_row_pitch apart.
+  // A streaming array [channels, n_time] read in place (no patch materialisation): x_nt = time blocks per window,
+  // x_stride_a = window_stride * n_time, x_stride_b = Win, x_row_pitch = n_time, x pointing at the first window's row.
+  long long x_stride_a, x_stride_b, x_row_pitch;
+  int x_nt, x_n0;
+  int raw_stage_bytes;     // tensor-core stem: bytes of one fp32 staging stage (set by its launcher)
 };
 
 struct PoolParams {        // MaxPool2d(2,2,ceil_mode=True) (modelA_MTL.py:116)

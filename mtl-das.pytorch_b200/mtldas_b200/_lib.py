@@ -53,6 +53,7 @@ def _load():
         "mtldas_train_last_launch_count": (ci, [vp]),
         "mtldas_train_read_tensor": (ci, [vp, c.c_char_p, ci, vp, vp]),
         "mtldas_train_describe": (sz, [vp, c.c_char_p, sz]),
+        "mtldas_plan_forward_eval_windows": (ci, [vp, vp, c.c_longlong, c.c_longlong, ci, ci, ci, vp, vp, vp]),
         "mtldas_window_gather": (ci, [vp, c.c_longlong, c.c_longlong, ci, ci, ci, vp, vp]),
         "mtldas_nll_loss": (ci, [vp, vp, ci, vp, vp, vp, ci, vp, ci, vp, vp, vp]),
         "mtldas_adam_step": (ci, [vp, vp, vp, vp, sz, ci, cf, cf, cf, cf, cf, vp]),

@@ -17,7 +17,8 @@ WINDOW, TBLOCK = 100, 250
 
 
 class StreamingInference:
-    def __init__(self, state_dict, kind="MTL", precision="bf16", micro_batch=512, stride=10, device=None):
+    def __init__(self, state_dict, kind="MTL", precision="bf16", micro_batch=512, stride=10, device=None, in_place=True):
+        self.in_place = in_place      # False: always gather the windows into a patch tensor first (mtldas_window_gather)
         self.plan = EvalPlan(kind, micro_batch, precision, device)
         self.device, self.stride = self.plan.device, int(stride)
         self.plan.pack({k: v.to(self.device) for k, v in state_dict.items()})
@@ -37,6 +38,15 @@ class StreamingInference:
             n_windows = max(0, (n_ch - first_channel - WINDOW) // self.stride + 1)
         n_tb = n_time // TBLOCK
         n = n_windows * n_tb
+        if self.in_place and n and self.plan.precision == "bf16" and n_time % 4 == 0 and slab.data_ptr() % 16 == 0:
+            # the stem cuts the windows out of the array itself: no patch tensor is written or re-read
+            outs = [torch.empty((n, c), dtype=torch.float32, device=self.device) for c in self.plan.classes]
+            with torch.cuda.device(self.device):
+                check(lib.mtldas_plan_forward_eval_windows(
+                    self.plan._h, ctypes.c_void_p(slab.data_ptr()), n_ch, n_time, first_channel, self.stride, n_windows,
+                    ctypes.c_void_p(outs[0].data_ptr()), ctypes.c_void_p(outs[1].data_ptr()) if len(outs) > 1 else None,
+                    _stream_ptr(self.device)), "forward_eval_windows")
+            return tuple(o.view(n_windows, n_tb, -1) for o in outs)
         patches = torch.empty((n, 1, WINDOW, TBLOCK), dtype=torch.float32, device=self.device)
         with torch.cuda.device(self.device):
             check(lib.mtldas_window_gather(ctypes.c_void_p(slab.data_ptr()), n_ch, n_time, first_channel, self.stride,
