@@ -315,7 +315,7 @@ def measure_extras(args, dev, world, rank, barrier):
     ms = timed(lambda: si.run(slab))
     out["streaming"] = {"value": world * nwin * (n_time // 250) / (ms * 1e-3), "unit": "windows/s", "ms_per_step": ms,
                         "workload": "array [%d channels x %d samples] per GPU -> %d windows x %d blocks, stride %d, "
-                                    "window gather + MTL forward, windows sharded across ranks, no collective"
+                                    "windows read in place by the stem (no patch tensor) + MTL forward, windows sharded across ranks, no collective"
                                     % (n_ch, n_time, nwin, n_time // 250, stride)}
     return out
 

@@ -190,7 +190,7 @@ def test_reference_trainer_call_sequence_on_the_dropin_module(tmp_path):
             optimizer.zero_grad()
             loss.backward()
             optimizer.step()
-            v = float(loss)
+            v = float(loss.detach())
             first_train_loss = v if first_train_loss is None else first_train_loss
             last_train_loss = v
     l1, a1, a2 = validate()
