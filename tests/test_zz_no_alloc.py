@@ -41,6 +41,15 @@ def test_static_scratch_conv_matches_allocating_entry_point(precision):
     for c in cases:            # consecutive calls, no synchronisation in between (same stream -> ordered)
         got.append(conv2d_nchw_static(precision=precision, **c))
     torch.cuda.synchronize()
+    # independent comparator (torch CPU, fp64) besides the allocating entry point
+    import torch.nn.functional as F
+    for c, g_ in zip(cases, got):
+        rd = (lambda t: t.cpu().bfloat16().double()) if precision == "bf16" else (lambda t: t.cpu().double())
+        xin = torch.cat((c["x"], c["x2"]), 1) if c["x2"] is not None else c["x"]
+        k = c["weight"].shape[-1]
+        y = F.conv2d(rd(xin), rd(c["weight"]), c["bias"].cpu().double(), stride=c["stride"], padding=k // 2)
+        ref = torch.relu(y) if c["epilogue"] == 1 else torch.relu(y + rd(c["aux"]))
+        assert float((g_.cpu().double() - ref).abs().max()) <= (6e-3 if precision == "bf16" else 1e-4) * float(ref.abs().max())
     for g_, w_ in zip(got, want):
         assert g_.shape == w_.shape
         scale = float(w_.abs().max())
