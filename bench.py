@@ -400,7 +400,8 @@ def measure_train(args, dev, world, rank, barrier):
                           "every tensor is L2-resident, so this fraction measures launch-chain latency, not DRAM"}
     return {"value": world * nb * steps / (float(ms.item()) * 1e-3), "unit": UNIT, "ms_per_step": float(ms.item()) / steps,
             "roofline": train_roof, "replica_checksum_spread": spread, "replica_checksum": sums,
-            "optimizer": "mtldas_adam_step (one launch over the flat parameter buffer)",
+            "optimizer": "mtldas_adam_step (one launch over the flat parameter buffer)" if trainer._fused is None else "inside the fused collective kernel",
+            "collective": trainer.collective, "fused_collective_unavailable": getattr(trainer, "fused_unavailable", None),
             "steps": steps, "batch_per_gpu": nb, "scaling": "weak",
             "step": "pack weights + forward (batch-stat BN) + backward + all-reduce + Adam",
             "allreduce_bytes_per_step": plan.n_params * 4 if world > 1 else 0,

@@ -200,6 +200,21 @@ MTLDAS_API int mtldas_adam_step(float* dev_params, const float* dev_grads, float
                                 size_t n, int step, float lr, float beta1, float beta2, float eps, float weight_decay,
                                 void* stream);
 
+/* gradient all-reduce + Adam + parameter broadcast in one kernel (multi-GPU, NVLink / NVSwitch multicast) -----------
+ * Replaces, for data-parallel training, `all-reduce(grads); optimizer.step()` (the reference has no distributed code;
+ * its step is utils.py:372-374): rank r owns the slice [r*n/world, (r+1)*n/world) of the flat buffers, sums that slice
+ * of every rank's gradient inside the switch (multimem.ld_reduce), divides by world, applies the Adam rule of
+ * mtldas_adam_step and stores the updated slice into every rank's parameter buffer (multimem.st).
+ * mc_grads / mc_params are MULTICAST addresses of symmetric allocations (e.g. torch.distributed._symmetric_memory:
+ * handle.multicast_ptr) holding the flat gradient / parameter buffers; dev_params is this rank's ordinary address of
+ * the same parameter buffer; the two moment buffers hold the owned slice only (n_total / world floats).
+ * The kernel waits for nobody: the caller runs a cross-rank barrier before it (every gradient written) and after it
+ * (every slice landed) -- mtldas_b200.ddp.DataParallelTrainer uses the symmetric-memory handle's barrier. */
+MTLDAS_API int mtldas_reduce_adam_multimem(const float* mc_grads, float* mc_params, const float* dev_params,
+                                           float* dev_exp_avg_slice, float* dev_exp_avg_sq_slice, size_t n_total, int rank,
+                                           int world, int step, float lr, float beta1, float beta2, float eps,
+                                           float weight_decay, void* stream);
+
 /* validation bookkeeping on the device -----------------------------------------------------------------
  * Replaces, per validation batch, utils.py:274-291: criterion(out_t, y_t) sums, pred_t = torch.max(out_t, 1)[1]
  * (first maximum wins), (pred_t == y_t).sum(), and the label / prediction lists that become

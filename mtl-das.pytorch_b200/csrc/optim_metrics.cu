@@ -48,6 +48,59 @@ __global__ void __launch_bounds__(256) adam_kernel(const AdamArgs a) {
     adam_one(a.p[i], a.g[i], a.m[i], a.v[i], a);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Gradient all-reduce + Adam + parameter broadcast in ONE kernel over NVLink / NVSwitch multicast:
+// every rank owns the slice [rank * n / world, (rank + 1) * n / world) of the flat buffers.  For its slice it
+//   g   = multimem.ld_reduce.add( grads of ALL ranks )   (summed inside the switch, one load per 4 floats) * 1 / world
+//   p   = Adam(p, g)                                      (exp_avg / exp_avg_sq exist for the owned slice only)
+//   multimem.st( params of ALL ranks ) = p                (the updated slice lands in every replica)
+// replacing ncclAllReduce (4.54 MB) + the Adam launch.  Every element is updated once, by its owner, and broadcast, so
+// the replicas stay bit-identical by construction.  No waiting inside the kernel: the host brackets it with the
+// symmetric-memory barrier (all gradients written before, all slices landed after).
+// ---------------------------------------------------------------------------------------------------------------
+struct ReduceAdamArgs {
+  const float* mc_grads;   // multicast address of the flat gradient buffer
+  float* mc_params;        // multicast address of the flat parameter buffer
+  const float* params;     // this rank's own (unicast) parameter buffer
+  float* m;                // exp_avg of the owned slice   [n_slice]
+  float* v;                // exp_avg_sq of the owned slice [n_slice]
+  long long first, n_slice;  // owned slice, in floats (multiples of 4)
+  float inv_world;
+  AdamArgs a;              // p/g/m/v/n unused; the scalars are
+};
+
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float* mc_addr) {
+  float4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(mc_addr)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ void multimem_st(float* mc_addr, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w)
+               : "memory");
+}
+
+__global__ void __launch_bounds__(256) reduce_adam_multimem_kernel(const ReduceAdamArgs q) {
+  const long long n4 = q.n_slice >> 2, stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    const long long e = q.first + 4 * i;
+    float4 g = multimem_ld_reduce_add(q.mc_grads + e);
+    g.x *= q.inv_world, g.y *= q.inv_world, g.z *= q.inv_world, g.w *= q.inv_world;
+    float4 p = *reinterpret_cast<const float4*>(q.params + e);
+    float4 m = reinterpret_cast<float4*>(q.m)[i], v = reinterpret_cast<float4*>(q.v)[i];
+    adam_one(p.x, g.x, m.x, v.x, q.a);
+    adam_one(p.y, g.y, m.y, v.y, q.a);
+    adam_one(p.z, g.z, m.z, v.z, q.a);
+    adam_one(p.w, g.w, m.w, v.w, q.a);
+    reinterpret_cast<float4*>(q.m)[i] = m, reinterpret_cast<float4*>(q.v)[i] = v;
+    multimem_st(q.mc_params + e, p);
+  }
+  __threadfence_system();   // the broadcast stores are ordered before the caller's cross-rank barrier
+}
+
 struct MetricsArgs {
   const float* logp[2];
   const long long* y[2];
@@ -136,6 +189,35 @@ extern "C" int mtldas_adam_step(float* dev_params, const float* dev_grads, float
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("adam_step: %s", cudaGetErrorString(e));
+    return MTLDAS_ERR_CUDA;
+  }
+  return 0;
+}
+
+extern "C" int mtldas_reduce_adam_multimem(const float* mc_grads, float* mc_params, const float* dev_params,
+                                           float* dev_exp_avg_slice, float* dev_exp_avg_sq_slice, size_t n_total, int rank,
+                                           int world, int step, float lr, float beta1, float beta2, float eps,
+                                           float weight_decay, void* stream) {
+  if (!mc_grads || !mc_params || !dev_params || !dev_exp_avg_slice || !dev_exp_avg_sq_slice || world < 1 || rank < 0 ||
+      rank >= world || step < 1 || n_total == 0 || (n_total % (size_t)(4 * world)) != 0 ||
+      ((reinterpret_cast<uintptr_t>(mc_grads) | reinterpret_cast<uintptr_t>(mc_params) | reinterpret_cast<uintptr_t>(dev_params) |
+        reinterpret_cast<uintptr_t>(dev_exp_avg_slice) | reinterpret_cast<uintptr_t>(dev_exp_avg_sq_slice)) & 15)) {
+    set_error("reduce_adam_multimem: bad arguments (16-byte aligned buffers; n_total must be a multiple of 4 * world)");
+    return MTLDAS_ERR_ARG;
+  }
+  ReduceAdamArgs q{};
+  q.mc_grads = mc_grads, q.mc_params = mc_params, q.params = dev_params, q.m = dev_exp_avg_slice, q.v = dev_exp_avg_sq_slice;
+  q.n_slice = (long long)(n_total / (size_t)world), q.first = q.n_slice * rank;
+  q.inv_world = 1.f / (float)world;
+  const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
+  q.a.lr_over_bc1 = (float)((double)lr / bc1), q.a.inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
+  q.a.beta1 = beta1, q.a.beta2 = beta2, q.a.eps = eps, q.a.weight_decay = weight_decay;
+  const long long n4 = q.n_slice / 4;
+  const int blocks = (int)std::max<long long>(1, std::min<long long>(148 * 4, (n4 + 255) / 256));
+  reduce_adam_multimem_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(q);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("reduce_adam_multimem: %s", cudaGetErrorString(e));
     return MTLDAS_ERR_CUDA;
   }
   return 0;

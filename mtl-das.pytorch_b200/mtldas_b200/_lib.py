@@ -57,6 +57,7 @@ def _load():
         "mtldas_window_gather": (ci, [vp, c.c_longlong, c.c_longlong, ci, ci, ci, vp, vp]),
         "mtldas_nll_loss": (ci, [vp, vp, ci, vp, vp, vp, ci, vp, ci, vp, vp, vp]),
         "mtldas_adam_step": (ci, [vp, vp, vp, vp, sz, ci, cf, cf, cf, cf, cf, vp]),
+        "mtldas_reduce_adam_multimem": (ci, [vp, vp, vp, vp, vp, sz, ci, ci, ci, cf, cf, cf, cf, cf, vp]),
         "mtldas_eval_metrics": (ci, [vp, vp, ci, vp, vp, vp, ci, vp, ci, vp, vp, vp, vp, vp]),
         "mtldas_c_pack_conv": (ci, [vp, vp, vp, vp, vp, cf, ci, ci, ci, ci, vp, vp, vp]),
         "mtldas_c_conv": (ci, [vp, ci, ci, ci, ci, vp, vp, vp, ci, ci, ci, ci, ci, ci, ci, ci, ci, ci, vp]),

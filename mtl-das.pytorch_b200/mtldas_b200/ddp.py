@@ -62,7 +62,7 @@ def unflatten_like(flat: torch.Tensor, params: Sequence[torch.Tensor]) -> List[t
     return out
 
 
-def flatten_parameters_(module) -> torch.nn.Parameter:
+def flatten_parameters_(module, out: torch.Tensor = None) -> torch.nn.Parameter:
     """Re-home every parameter of `module` into ONE flat fp32 buffer (named_parameters order, the order of the flat
     gradient) and return that buffer as a Parameter.  The module's parameters become views of it, so the state_dict,
     the packing kernels and an optimizer stepping the flat tensor all see the same storage; the elementwise optimizers
@@ -72,6 +72,12 @@ def flatten_parameters_(module) -> torch.nn.Parameter:
     if not params:
         raise ValueError("module has no parameters")
     flat = torch.cat([p.detach().reshape(-1).float() for p in params]).contiguous()
+    if out is not None:          # caller-provided storage (e.g. a symmetric-memory allocation, possibly padded)
+        if out.dtype != torch.float32 or out.numel() < flat.numel() or out.device != flat.device:
+            raise ValueError("flatten_parameters_: `out` must be an fp32 buffer on the parameters' device, large enough")
+        out.zero_()
+        out[:flat.numel()].copy_(flat)
+        flat = out
     off = 0
     for p in params:
         n = p.numel()
@@ -115,25 +121,104 @@ class DataParallelTrainer:
     (mtldas_adam_step on a B200; torch.optim.Adam on the CPU, where only the host logic is exercised).
     Construction broadcasts rank 0's parameters and buffers to every rank of `group`."""
 
-    def __init__(self, module, optimizer=None, group=None, flat_adam=None, broadcast=True):
+    def __init__(self, module, optimizer=None, group=None, flat_adam=None, broadcast=True, fused_collective="auto"):
         self.module, self.optimizer, self.group = module, optimizer, group
         self._flat_param = None
+        self._flat = None
+        self._fused = None            # state of the one-kernel reduce + Adam + broadcast (multimem) path
+        self.collective = "none"
         if broadcast:
             broadcast_module_(module, group)
         if optimizer is None:
             if flat_adam is None:
                 raise ValueError("give an optimizer or flat_adam=dict(lr=..., weight_decay=...)")
-            self._flat_param = flatten_parameters_(module)
             kw = dict(flat_adam)
-            if self._flat_param.is_cuda:
-                from .engine import FlatAdam
-                self.optimizer = FlatAdam(self._flat_param, **kw)
-            else:
-                self.optimizer = torch.optim.Adam([self._flat_param], **kw)
+            first = next(module.parameters())
+            multi = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+            if first.is_cuda and multi and fused_collective in ("auto", True):
+                self._setup_fused(module, kw, group, required=fused_collective is True)
+            if self._fused is None:
+                self._flat_param = flatten_parameters_(module)
+                if self._flat_param.is_cuda:
+                    from .engine import FlatAdam
+                    self.optimizer = FlatAdam(self._flat_param, **kw)
+                else:
+                    self.optimizer = torch.optim.Adam([self._flat_param], **kw)
+                self.collective = "nccl all-reduce (AVG) + mtldas_adam_step" if multi and first.is_cuda else \
+                    ("all-reduce + Adam" if multi else "none (single rank)")
+        elif dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+            self.collective = "all-reduce (mean) + caller's optimizer"
         self.params = [p for _, p in module.named_parameters()]
-        self._flat = None
         self._loss_bufs = None
         self._state = None
+
+    def _setup_fused(self, module, kw, group, required):
+        """Flat parameter and gradient buffers in symmetric memory with an NVSwitch multicast mapping, so that ONE kernel
+        (mtldas_reduce_adam_multimem) sums the gradient slices in the switch, applies Adam and broadcasts the updated
+        slice to every replica.  Falls back to NCCL all-reduce + mtldas_adam_step when the mapping is not available."""
+        try:
+            import torch.distributed._symmetric_memory as symm
+            world, rank = dist.get_world_size(group), dist.get_rank(group)
+            pg = group if group is not None else dist.group.WORLD
+            gname = pg.group_name
+            try:
+                symm.enable_symm_mem_for_group(gname)
+            except Exception:
+                pass
+            dev = next(module.parameters()).device
+            n = sum(p.numel() for p in module.parameters())
+            unit = 4 * world
+            n_pad = (n + unit - 1) // unit * unit
+            pbuf = symm.empty(n_pad, dtype=torch.float32, device=dev)
+            gbuf = symm.empty(n_pad, dtype=torch.float32, device=dev)
+            hp, hg = symm.rendezvous(pbuf, gname), symm.rendezvous(gbuf, gname)
+            if not hp.multicast_ptr or not hg.multicast_ptr:
+                raise RuntimeError("no multicast mapping for symmetric memory on this system")
+            gbuf.zero_()
+            self._flat_param = flatten_parameters_(module, out=pbuf)
+            self._flat = gbuf[:n]
+            self._flat_param.grad = None
+            ns = n_pad // world
+            self._fused = dict(hp=hp, hg=hg, pbuf=pbuf, gbuf=gbuf, n=n, n_pad=n_pad, rank=rank, world=world, step=0,
+                               m=torch.zeros(ns, dtype=torch.float32, device=dev), v=torch.zeros(ns, dtype=torch.float32, device=dev),
+                               lr=float(kw.get("lr", 1e-3)), betas=tuple(kw.get("betas", (0.9, 0.999))),
+                               eps=float(kw.get("eps", 1e-8)), weight_decay=float(kw.get("weight_decay", 0.0)))
+            hp.barrier(channel=0)
+            self.collective = "mtldas_reduce_adam_multimem (multimem.ld_reduce + Adam + multimem.st, one kernel)"
+        except Exception as e:          # pragma: no cover - depends on the machine
+            self._fused, self._flat = None, None
+            if required:
+                raise
+            self.fused_unavailable = repr(e)[:300]
+
+    @property
+    def lr(self):
+        return self._fused["lr"] if self._fused else getattr(self.optimizer, "lr", None)
+
+    @lr.setter
+    def lr(self, value):
+        if self._fused:
+            self._fused["lr"] = float(value)
+        elif hasattr(self.optimizer, "lr"):
+            self.optimizer.lr = float(value)
+        else:
+            for g in self.optimizer.param_groups:
+                g["lr"] = float(value)
+
+    def _fused_step(self, device):
+        import ctypes
+        from ._lib import lib, check
+        from .engine import _stream_ptr
+        f = self._fused
+        f["step"] += 1
+        f["hg"].barrier(channel=0)                     # every rank's gradient is written
+        with torch.cuda.device(device):
+            check(lib.mtldas_reduce_adam_multimem(
+                ctypes.c_void_p(f["hg"].multicast_ptr), ctypes.c_void_p(f["hp"].multicast_ptr),
+                ctypes.c_void_p(f["pbuf"].data_ptr()), ctypes.c_void_p(f["m"].data_ptr()), ctypes.c_void_p(f["v"].data_ptr()),
+                f["n_pad"], f["rank"], f["world"], f["step"], f["lr"], f["betas"][0], f["betas"][1], f["eps"],
+                f["weight_decay"], _stream_ptr(device)), "reduce_adam_multimem")
+        f["hp"].barrier(channel=1)                     # every updated slice has landed in every replica
 
     def step(self, x_local: torch.Tensor, labels_local: Sequence[torch.Tensor]):
         """x_local / labels_local: this rank's shard. Returns the local loss (python float is NOT taken here)."""
@@ -154,8 +239,11 @@ class DataParallelTrainer:
                 for p, g in zip(self.params, unflatten_like(self._flat, self.params)):
                     p.grad = g                     # views of the flat buffer: bound once, refilled every step
         plan.backward(douts, self._flat)
-        allreduce_mean_(self._flat, self.group)
-        self.optimizer.step()
+        if self._fused is not None:
+            self._fused_step(x_local.device)       # all-reduce + Adam + broadcast: one kernel between two barriers
+        else:
+            allreduce_mean_(self._flat, self.group)
+            self.optimizer.step()
         # parameters and BatchNorm buffers changed under the module (in-place kernels do not bump torch's version
         # counters): the eval-mode weight image packed earlier is stale
         if hasattr(m, "invalidate_packed"):

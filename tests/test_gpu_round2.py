@@ -299,3 +299,56 @@ def test_streaming_windows_read_in_place_equal_gathered_patches():
     c = direct.run(odd)
     d = gathered.run(odd)
     assert all(torch.equal(u, v) for u, v in zip(c, d))
+
+
+def _fused_worker(rank, world, port, tmp):
+    sys.path[:0] = [ROOT, os.path.join(ROOT, "mtl-das.pytorch_b200")]
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    import torch.distributed as dist
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    from model.modelA_MTL import MTL_Net
+    from mtldas_b200.ddp import DataParallelTrainer, replica_checksum, shard_range
+    from oracle import mtl_oracle as Or
+    sd = Or.synth_state_dict("MTL", seed=0)
+    res = {}
+    finals = {}
+    for mode in ("fused", "nccl"):
+        m = MTL_Net()
+        m.load_state_dict(sd, strict=True)
+        m.precision = "fp32"
+        m = m.cuda().train()
+        tr = DataParallelTrainer(m, flat_adam=dict(lr=1e-3, weight_decay=1e-5), fused_collective=True if mode == "fused" else False)
+        res[mode + "_collective"] = tr.collective
+        n = 8
+        for step in range(3):
+            x, yd, ye = Or.synth_patches(n, seed=200 + step)
+            lo, hi = shard_range(n, rank, world)
+            tr.step(x[lo:hi].cuda(), [yd[lo:hi].cuda(), ye[lo:hi].cuda()])
+        torch.cuda.synchronize()
+        res[mode + "_spread"], _ = replica_checksum(m)
+        finals[mode] = torch.cat([p.detach().reshape(-1) for p in m.parameters()]).cpu().double()
+        m.eval()                                         # eval after fused training sees the broadcast parameters
+        xe, _, _ = Or.synth_patches(4, seed=9)
+        res[mode + "_eval"] = m(xe.cuda())[0].cpu()
+    res["param_diff"] = float((finals["fused"] - finals["nccl"]).abs().max() / finals["nccl"].abs().max())
+    res["eval_diff"] = float((res.pop("fused_eval") - res.pop("nccl_eval")).abs().max())
+    torch.save(res, os.path.join(tmp, f"f{rank}.pt"))
+    dist.destroy_process_group()
+
+
+def test_two_gpu_fused_multimem_reduce_adam_equals_nccl_allreduce_plus_adam(tmp_path):
+    """mtldas_reduce_adam_multimem (gradient all-reduce + Adam + parameter broadcast in ONE kernel over NVSwitch
+    multicast) against NCCL all-reduce + mtldas_adam_step: same parameters after three steps
+    (the switch sums in a different order: <= 1e-6 relative), replicas bit-identical in both modes."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+    world, port = 2, 28800 + os.getpid() % 300
+    mp.spawn(_fused_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    res = [torch.load(os.path.join(str(tmp_path), f"f{r}.pt")) for r in range(world)]
+    print("fused collective vs NCCL:", res[0])
+    for r in res:
+        assert "multimem" in r["fused_collective"], r
+        assert r["fused_spread"] == 0.0 and r["nccl_spread"] == 0.0, r
+        assert r["param_diff"] <= 1e-5 and r["eval_diff"] <= 1e-4, r
