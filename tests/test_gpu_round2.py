@@ -231,7 +231,9 @@ def _nccl_worker(rank, world, port, tmp):
         m.load_state_dict(sd, strict=True)
     m.precision = "fp32"
     m = m.cuda()
-    tr = DataParallelTrainer(m, flat_adam=dict(lr=0.0, weight_decay=0.0))     # lr 0: the step leaves the weights alone
+    # NCCL path (the fused multimem path reduces inside its kernel and never materialises the mean gradient); lr 0:
+    # the step leaves the weights alone
+    tr = DataParallelTrainer(m, flat_adam=dict(lr=0.0, weight_decay=0.0), fused_collective=False)
     spread0, _ = replica_checksum(m)
     n = 12
     x, yd, ye = Or.synth_patches(n, seed=91)
