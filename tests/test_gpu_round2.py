@@ -308,13 +308,37 @@ def _fused_worker(rank, world, port, tmp):
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     import torch.distributed as dist
     torch.cuda.set_device(rank)
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     from model.modelA_MTL import MTL_Net
     from mtldas_b200.ddp import DataParallelTrainer, replica_checksum, shard_range
     from oracle import mtl_oracle as Or
     sd = Or.synth_state_dict("MTL", seed=0)
     res = {}
-    finals = {}
+    # ---- (1) the kernel alone, on injected per-rank gradients: exact comparison with an fp64 restatement --------
+    m = MTL_Net()
+    m.load_state_dict(sd, strict=True)
+    m.precision = "fp32"
+    m = m.cuda().train()
+    tr = DataParallelTrainer(m, flat_adam=dict(lr=1e-3, weight_decay=1e-5), fused_collective=True)
+    res["fused_collective"] = tr.collective
+    n = tr._flat.numel()
+    p64 = torch.cat([p.detach().reshape(-1) for p in m.parameters()]).cpu().double()
+    m64, v64 = torch.zeros_like(p64), torch.zeros_like(p64)
+    for step in range(1, 4):
+        gs = [torch.randn(n, generator=torch.Generator().manual_seed(1000 * step + r)) * (10.0 ** -(step + r)) for r in range(world)]
+        tr._flat.copy_(gs[rank].to(dev))
+        tr._fused_step(dev)
+        g = sum(x.double() for x in gs) / world + 1e-5 * p64
+        m64 = 0.9 * m64 + 0.1 * g
+        v64 = 0.999 * v64 + 0.001 * g * g
+        p64 = p64 - (1e-3 / (1 - 0.9 ** step)) * m64 / (v64.sqrt() / (1 - 0.999 ** step) ** 0.5 + 1e-8)
+    torch.cuda.synchronize()
+    got = torch.cat([p.detach().reshape(-1) for p in m.parameters()]).cpu().double()
+    res["kernel_err"] = float((got - p64).abs().max() / p64.abs().max())
+    res["kernel_spread"], _ = replica_checksum(m)
+    # ---- (2) three real training steps, fused vs NCCL all-reduce + mtldas_adam_step ------------------------------
+    finals, init = {}, None
     for mode in ("fused", "nccl"):
         m = MTL_Net()
         m.load_state_dict(sd, strict=True)
@@ -322,27 +346,27 @@ def _fused_worker(rank, world, port, tmp):
         m = m.cuda().train()
         tr = DataParallelTrainer(m, flat_adam=dict(lr=1e-3, weight_decay=1e-5), fused_collective=True if mode == "fused" else False)
         res[mode + "_collective"] = tr.collective
-        n = 8
+        init = torch.cat([p.detach().reshape(-1) for p in m.parameters()]).cpu().double()
+        nb = 8
         for step in range(3):
-            x, yd, ye = Or.synth_patches(n, seed=200 + step)
-            lo, hi = shard_range(n, rank, world)
+            x, yd, ye = Or.synth_patches(nb, seed=200 + step)
+            lo, hi = shard_range(nb, rank, world)
             tr.step(x[lo:hi].cuda(), [yd[lo:hi].cuda(), ye[lo:hi].cuda()])
         torch.cuda.synchronize()
         res[mode + "_spread"], _ = replica_checksum(m)
         finals[mode] = torch.cat([p.detach().reshape(-1) for p in m.parameters()]).cpu().double()
-        m.eval()                                         # eval after fused training sees the broadcast parameters
-        xe, _, _ = Or.synth_patches(4, seed=9)
-        res[mode + "_eval"] = m(xe.cuda())[0].cpu()
-    res["param_diff"] = float((finals["fused"] - finals["nccl"]).abs().max() / finals["nccl"].abs().max())
-    res["eval_diff"] = float((res.pop("fused_eval") - res.pop("nccl_eval")).abs().max())
+    # Adam's first steps move every parameter by ~lr * sign(g): elements whose gradient is at noise level (atomics, a
+    # flipped ReLU mask) can differ by a whole step between ANY two runs, so the statement is about the update as a whole
+    res["update_rel_l2"] = float((finals["fused"] - finals["nccl"]).norm() / (finals["nccl"] - init).norm())
     torch.save(res, os.path.join(tmp, f"f{rank}.pt"))
     dist.destroy_process_group()
 
 
 def test_two_gpu_fused_multimem_reduce_adam_equals_nccl_allreduce_plus_adam(tmp_path):
     """mtldas_reduce_adam_multimem (gradient all-reduce + Adam + parameter broadcast in ONE kernel over NVSwitch
-    multicast) against NCCL all-reduce + mtldas_adam_step: same parameters after three steps
-    (the switch sums in a different order: <= 1e-6 relative), replicas bit-identical in both modes."""
+    multicast): (1) on injected per-rank gradients, three steps against an fp64 restatement of
+    mean-gradient Adam (<= 1e-6), replicas bit-identical; (2) three real training steps against the NCCL all-reduce +
+    mtldas_adam_step trainer: the parameter updates agree (relative L2 of the update), replicas bit-identical."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
     import torch.multiprocessing as mp
@@ -352,5 +376,6 @@ def test_two_gpu_fused_multimem_reduce_adam_equals_nccl_allreduce_plus_adam(tmp_
     print("fused collective vs NCCL:", res[0])
     for r in res:
         assert "multimem" in r["fused_collective"], r
+        assert r["kernel_err"] <= 1e-6 and r["kernel_spread"] == 0.0, r
         assert r["fused_spread"] == 0.0 and r["nccl_spread"] == 0.0, r
-        assert r["param_diff"] <= 1e-5 and r["eval_diff"] <= 1e-4, r
+        assert r["update_rel_l2"] <= 5e-2, r
