@@ -161,10 +161,6 @@ class DataParallelTrainer:
             world, rank = dist.get_world_size(group), dist.get_rank(group)
             pg = group if group is not None else dist.group.WORLD
             gname = pg.group_name
-            try:
-                symm.enable_symm_mem_for_group(gname)
-            except Exception:
-                pass
             dev = next(module.parameters()).device
             n = sum(p.numel() for p in module.parameters())
             unit = 4 * world
