@@ -224,6 +224,24 @@ def conv_algorithmic_elems_per_sample(desc):
     return per_op
 
 
+def conv_flops_per_sample(desc):
+    """2 * MACs per sample of every conv op of the program (for the per-op bound max(FLOP / P, bytes / BW))."""
+    layers = {L["conv"]: L for L in desc["layers"]}
+    per_op = []
+    for op in desc["program"]:
+        f, seen = 0.0, set()
+        if op["op"] == "conv":
+            for g in op["groups"]:
+                for s in g["segs"]:
+                    if s["layer"] in seen:
+                        continue
+                    seen.add(s["layer"])
+                    L = layers[s["layer"]]
+                    f += 2.0 * L["cin"] * L["cout"] * L["k"] * L["k"] * op["H"] * op["W"]
+        per_op.append(f)
+    return per_op
+
+
 def hbm_peak():
     try:
         return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "measured"
@@ -242,6 +260,23 @@ def profiled_traffic(version, batch, precision, passes):
     if t.get("mtldas_version") != version or t.get("batch") != batch or t.get("precision") != precision or passes != 1:
         return None, "profiles/r2_traffic.json is from build %r, batch %r: not this run" % (t.get("mtldas_version"), t.get("batch"))
     return float(t["conv_dram_bytes_per_step"]) / float(t["conv_launches_per_step"]), t.get("source")
+
+
+def per_op_fracs(desc, per_op_ms, elems, batch, precision, hbm_gbs):
+    """measured / bound per conv op, bound = max(FLOP / sustained bf16 peak, algorithmic bytes / measured HBM peak)."""
+    try:
+        tf = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"])
+    except Exception:
+        tf = 1400.0
+    flops = conv_flops_per_sample(desc)
+    out = {}
+    for i, (ms, op) in enumerate(zip(per_op_ms, desc["program"])):
+        if op["op"] != "conv" or ms <= 0:
+            continue
+        t_f = flops[i] * batch / (tf * 1e12) * 1e3
+        t_b = elems[i] * batch * (2 if precision == "bf16" else 4) / (hbm_gbs * 1e9) * 1e3
+        out[op["name"] + f"#{i}"] = round(max(t_f, t_b) / ms, 3)
+    return out
 
 
 def measure_extras(args, dev, world, rank, barrier):
@@ -555,6 +590,7 @@ def run_ours(args):
                 "launches_per_step": n_conv, "avg_launch_ms": conv_ms / n_conv,
                 "algorithmic_bytes_per_step": conv_bytes, "peak_source": peak_src,
                 "share_of_step": conv_ms / sum(per_op_ms),
+                "per_op_frac_of_own_bound": per_op_fracs(desc, per_op_ms, elems, B, args.precision, peak),
                 "per_op_ms": {(op.get("name") or op["op"]) + f"#{i}": round(m, 4)
                               for i, (m, op) in enumerate(zip(per_op_ms, desc["program"]))}}
 
