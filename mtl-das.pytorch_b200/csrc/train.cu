@@ -217,17 +217,20 @@ TrainPlan* build_train_plan(int kind, int batch, int precision) {
     claim(tp, d, h.chunk0, 16, -1);
     tp.bwd.push_back({TOP_HEADBWD, (int)hi, 0});
   }
-  auto add_dgrad = [&](const ConvOpHost& inf, int ci, int g, int src_slot_lo, int src_slot_hi, bool stack_tasks) {
-    // gradient w.r.t. source tensor(s) of fprop group g read through slots [lo,hi) (one tensor, maybe 4 phases)
-    const ConvGroupHost& fg = inf.g[g];
-    const SrcRef sr = fg.src[src_slot_lo];
-    const int dsrc = grad_of(tp, sr.tensor);
+  auto add_dgrad = [&](const ConvOpHost& inf, int ci, int g, int src_slot_lo, int src_slot_hi, bool stack_tasks,
+                       bool all_groups = false) {
+    // gradient w.r.t. source tensor(s) of fprop group g read through slots [lo,hi) (one tensor, maybe 4 phases).
+    // all_groups: the tasks' input gradients (same layer shape, different channel slices of one tensor) go out as the
+    // groups of ONE launch instead of one launch per task.
+    const int G = all_groups ? inf.ngroups : 1;
+    const SrcRef sr0 = inf.g[all_groups ? 0 : g].src[src_slot_lo];
+    const int dsrc = grad_of(tp, sr0.tensor);
     const int Wp = inf.W + 1;
     const int nphase = src_slot_hi - src_slot_lo > 1 ? 4 : 1;
     for (int ph = 0; ph < nphase; ++ph) {
       ConvOpHost d{};
       d.name = "dgrad:" + inf.name + (nphase > 1 ? "/ph" + std::to_string(ph) : "") + "/s" + std::to_string(src_slot_lo);
-      d.H = inf.H, d.W = inf.W, d.ngroups = 1, d.nsrc = 1;
+      d.H = inf.H, d.W = inf.W, d.ngroups = G, d.nsrc = 1;
       d.Cout = inf.nchunks * 8;                                  // channels of the source
       d.nchunks = (stack_tasks ? inf.ngroups : 1) * inf.Cout / 8;  // K = output channels of the fprop conv
       TrainPlan::DgradPack dp{};
@@ -249,37 +252,56 @@ TrainPlan* build_train_plan(int kind, int batch, int precision) {
         gg.aux_tensor = -1, gg.aux_chunk0 = 0, gg.aux_nchunks = d.Cout / 8, gg.out_tensor = -1, gg.out_chunk0 = 0;
         for (auto& s : gg.src) s = SrcRef{-1, 0, -1};
       }
-      d.g[0].src[0] = SrcRef{tp.dy_of[ci], stack_tasks ? 0 : fg.out_chunk0, -1};
-      d.g[0].out_tensor = dsrc, d.g[0].out_chunk0 = sr.chunk0;
-      if (p.tensors[sr.tensor].layout == LAY_P8S2) {
-        const int phase = nphase > 1 ? ph : sr.phase;
-        d.g[0].out_phase = phase;
-        const TensorInfo& st = p.tensors[sr.tensor];
-        d.Hv = (st.H - (phase >> 1) + 1) / 2, d.Wv = (st.W - (phase & 1) + 1) / 2;
+      bool accum = false;
+      for (int gi = 0; gi < G; ++gi) {
+        const int fgi = all_groups ? gi : g;
+        const ConvGroupHost& fg = inf.g[fgi];
+        const SrcRef sr = fg.src[src_slot_lo];
+        d.g[gi].src[0] = SrcRef{tp.dy_of[ci], stack_tasks ? 0 : fg.out_chunk0, -1};
+        d.g[gi].out_tensor = dsrc, d.g[gi].out_chunk0 = sr.chunk0;
+        if (p.tensors[sr.tensor].layout == LAY_P8S2) {
+          const int phase = nphase > 1 ? ph : sr.phase;
+          d.g[gi].out_phase = phase;
+          const TensorInfo& st = p.tensors[sr.tensor];
+          d.Hv = (st.H - (phase >> 1) + 1) / 2, d.Wv = (st.W - (phase & 1) + 1) / 2;
+        }
+        const bool seen = claim(tp, dsrc, sr.chunk0, d.Cout / 8, d.g[gi].out_phase);
+        if (gi == 0) accum = seen;
+        // (the groups of a merged launch are the tasks' slices of one tensor at one point of the schedule: same state)
       }
-      const int phase_key = d.g[0].out_phase;
-      d.epi = claim(tp, dsrc, sr.chunk0, d.Cout / 8, phase_key) ? EPI_ACCUM : EPI_NONE;
+      d.epi = accum ? EPI_ACCUM : EPI_NONE;
       choose_tiling(d, (long long)p.mb * (d.H + 1) * (d.W + 1));
       p.convs.push_back(d);
       dp.conv = (int)p.convs.size() - 1;
       // transposed weight placement
-      const int g_lo = stack_tasks ? 0 : g, g_hi = stack_tasks ? inf.ngroups : g + 1;
-      for (int gi = g_lo; gi < g_hi; ++gi)
-        for (auto& s : inf.g[gi].segs) {
-          TrainPlan::TSeg ts{};
-          ts.layer = s.layer;
-          const bool dual = s.split != INT_MAX;
-          ts.ci_lo = dual ? (src_slot_lo == 0 ? 0 : s.split) : 0;
-          ts.ci_n = dual ? s.split : p.layers[s.layer].cin;
-          ts.k_off = s.cout_off + (stack_tasks ? gi * inf.Cout : 0);
-          ts.n_off = dual ? 0 : s.k_off;
-          dp.segs.push_back(ts);
-        }
+      for (int gi = 0; gi < G; ++gi) {
+        const int fgi = all_groups ? gi : g;
+        const int g_lo = stack_tasks ? 0 : fgi, g_hi = stack_tasks ? inf.ngroups : fgi + 1;
+        for (int gj = g_lo; gj < g_hi; ++gj)
+          for (auto& s : inf.g[gj].segs) {
+            TrainPlan::TSeg ts{};
+            ts.layer = s.layer;
+            const bool dual = s.split != INT_MAX;
+            ts.ci_lo = dual ? (src_slot_lo == 0 ? 0 : s.split) : 0;
+            ts.ci_n = dual ? s.split : p.layers[s.layer].cin;
+            ts.k_off = s.cout_off + (stack_tasks ? gj * inf.Cout : 0);
+            ts.n_off = dual ? 0 : s.k_off;
+            ts.group = gi;
+            dp.segs.push_back(ts);
+          }
+      }
       tp.dgrads.push_back(dp);
       tp.bwd.push_back({TOP_DGRAD, (int)tp.dgrads.size() - 1, 0});
     }
   };
 
+  const char* nomerge = getenv("MTLDAS_NO_DGRAD_MERGE");
+  const bool merge_task_dgrads = !(nomerge && nomerge[0] == '1');
+  auto same_source_tensor = [&](const ConvOpHost& inf, int slot) {
+    for (int g = 1; g < inf.ngroups; ++g)
+      if (inf.g[g].src[slot].tensor != inf.g[0].src[slot].tensor || inf.g[g].src[slot].phase != inf.g[0].src[slot].phase) return false;
+    return true;
+  };
   tp.dy_of.assign(n_inf_convs, -1);
   for (size_t ci = 0; ci < n_inf_convs; ++ci) tp.dy_of[ci] = clone_tensor(p, "dy:" + p.convs[ci].name, tp.y_of[ci], LAY_P8);
   tp.dy_stem = clone_tensor(p, "dy:stem", tp.y_stem, LAY_P8);
@@ -311,9 +333,11 @@ TrainPlan* build_train_plan(int kind, int batch, int precision) {
       add_dgrad(inf, ci, 0, 0, 4, false);
     } else if (inf.nsrc == 2) {
       add_dgrad(inf, ci, 0, 0, 1, true);                       // shared source: tasks stacked along K
-      for (int g = 0; g < inf.ngroups; ++g) add_dgrad(inf, ci, g, 1, 2, false);
+      if (merge_task_dgrads && same_source_tensor(inf, 1)) add_dgrad(inf, ci, 0, 1, 2, false, true);
+      else for (int g = 0; g < inf.ngroups; ++g) add_dgrad(inf, ci, g, 1, 2, false);
     } else {
-      for (int g = 0; g < inf.ngroups; ++g) add_dgrad(inf, ci, g, 0, 1, false);
+      if (merge_task_dgrads && inf.ngroups > 1 && same_source_tensor(inf, 0)) add_dgrad(inf, ci, 0, 0, 1, false, true);
+      else for (int g = 0; g < inf.ngroups; ++g) add_dgrad(inf, ci, g, 0, 1, false);
     }
   }
   // stem
@@ -443,7 +467,7 @@ static int pack_train(TrainPlan& tp, const void* const* state, cudaStream_t st) 
       q.seg = make_seg(p, PackSegHost{ts.layer, INT_MAX, 0, 0}, state);
       q.seg.transpose = 1, q.seg.ci_lo = ts.ci_lo, q.seg.ci_n = ts.ci_n, q.seg.k_off = ts.k_off, q.seg.cout_off = ts.n_off;
       for (int t = 0; t < 9; ++t) q.seg.tap_map[t] = dp.tap_map[t];
-      q.dst = p.ws + c.g[0].w_off, q.bias_dst = nullptr;
+      q.dst = p.ws + c.g[ts.group].w_off, q.bias_dst = nullptr;
       q.Cout_p = c.Cout, q.K_tap = c.nchunks * 8, q.fp32 = p.precision == 0 ? 0 : 1, q.fold = 0;
       packs.push_back(q);
     }

@@ -42,6 +42,7 @@ struct TrainPlan {
   };
   struct TSeg {
     int layer, ci_lo, ci_n, k_off, n_off;
+    int group = 0;           // group of the input-gradient conv this block of transposed weights belongs to
   };
   struct DgradPack {
     int conv;
