@@ -89,16 +89,6 @@ __device__ __forceinline__ long long gtime() {
     p.dbg[(size_t)blockIdx.x * 16 + (slot) + 1] = clock64();                             \
   }
 
-// sigmoid(x) * a with ONE special-function op: a * (0.5 * tanh(x / 2) + 0.5).  exp + reciprocal are two MUFU ops per
-// element, and the mask layers evaluate 32-128 sigmoids per position: at 16 MUFU results per cycle and SM that alone was
-// 0.15 ms of att_mask_generator1.3 (batch 4096).  tanh.approx is accurate to ~2^-11, below the bf16 rounding of the result.
-__device__ __forceinline__ float sigmoid_mul(float x, float a) {
-  float t;
-  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.5f * x));
-  const float h = 0.5f * a;
-  return fmaf(h, t, h);
-}
-
 // relu + round-to-nearest bf16 of two floats in one instruction; lo lands in the low half (lower channel)
 __device__ __forceinline__ uint32_t relu_pack_bf16x2(float lo, float hi) {
   uint32_t r;
@@ -147,7 +137,7 @@ __device__ __forceinline__ void epilogue_cols(const float* bias_s, int c0, bool 
       for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j] + a[j], 0.f);
     } else if (EPI == EPI_SIGMOID_MUL) {
 #pragma unroll
-      for (int j = 0; j < 16; ++j) v[j] = sigmoid_mul(v[j], a[j]);
+      for (int j = 0; j < 16; ++j) v[j] = __fdividef(a[j], 1.f + __expf(-v[j]));
     } else if (EPI == EPI_RELU) {
 #pragma unroll
       for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
@@ -215,7 +205,7 @@ __device__ __forceinline__ void epilogue_cols_aux(const float* bias_s, int c0, c
       for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j] + a[j], 0.f);
     } else {  // EPI_SIGMOID_MUL
 #pragma unroll
-      for (int j = 0; j < 16; ++j) v[j] = sigmoid_mul(v[j], a[j]);
+      for (int j = 0; j < 16; ++j) v[j] = __fdividef(a[j], 1.f + __expf(-v[j]));
     }
   } else {
 #pragma unroll
