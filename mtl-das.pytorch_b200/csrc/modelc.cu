@@ -20,6 +20,7 @@
 
 #include <algorithm>
 #include <cstdint>
+#include <cstdlib>
 
 #include "../../include/mtldas.h"
 #include "kernels.h"
@@ -44,6 +45,7 @@ struct ConvCParams {
   int out_chunk0;       // first destination plane (channel offset / 8 inside the concat tensor)
   int Nt;               // output channels per CTA (multiple of 16, <= 256)
   int relu;
+  int ks;               // K steps per K unit of the weight layout (weight_layout())
 };
 
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
@@ -204,9 +206,13 @@ __global__ void __launch_bounds__(kCThreads, 2) convc_umma_kernel(const __grid_c
           if (u >= kCStages) ptx::mbar_wait(empty + s, ((u / kCStages) - 1) & 1);
           const int nch = 2 * min(kCUnitSteps, KC - kc0);
           ptx::mbar_arrive_expect_tx(full + s, (uint32_t)(nch * Nt * 16));
-          for (int c = 0; c < nch; ++c)
+          for (int c = 0; c < nch; ++c) {                 // layout [n tile][K unit][tap][chunk][Nt][8]
+            const int gc = kc0 * 2 + c, ku = gc / (2 * p.ks), cl = gc - ku * 2 * p.ks;
+            const int nchu = min(2 * p.ks, cin_chunks - ku * 2 * p.ks);
             ptx::bulk_g2s(b_base + (size_t)s * b_stage + (size_t)c * Nt * 16,
-                          p.w + (((long long)tap * cin_chunks + kc0 * 2 + c) * p.cout + n0) * 16, (uint32_t)(Nt * 16), full + s);
+                          p.w + (((long long)blockIdx.y * ntaps * cin_chunks + (long long)ku * ntaps * 2 * p.ks + tap * nchu + cl) * Nt) * 16,
+                          (uint32_t)(Nt * 16), full + s);
+          }
         }
     }
     __syncwarp();
@@ -214,6 +220,330 @@ __global__ void __launch_bounds__(kCThreads, 2) convc_umma_kernel(const __grid_c
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 4) ptx::tmem_dealloc(tmem_base, cols);
+}
+
+// ---------------------------------------------------------------------------------------------
+// convc_window_kernel: every stride-1 convolution (84 of the 94).  Positions are enumerated in the PADDED image
+// (Hp = H + 2 ph rows of Wp = W + 2 pw positions); a tile is 128 consecutive padded positions and tap (r, q) of the
+// kernel is the same 128 rows shifted by r * Wp + q positions.  So one WINDOW of 128 + (kh-1) * Wp + (kw-1) positions per
+// 32-channel unit is brought into shared memory once (bulk copies of whole row segments, the zero padding is written
+// there, not in HBM) and all kh * kw taps are UMMAs whose A descriptor start address is shifted: the input is read from
+// L2 about once instead of kh * kw times, by one warp issuing a few bulk copies instead of 128 threads issuing 16-byte
+// copies per tap.  Outputs whose padded position is not a valid output (right / bottom margin) are computed and dropped.
+// Persistent: one CTA per SM walks over the (m tile, n tile) work items, the accumulator is double-buffered in TMEM so
+// that the four epilogue warps store tile t while the MMA thread is on tile t + 1.
+// ---------------------------------------------------------------------------------------------
+struct ConvWParams {
+  const char* x;        // planar-8 bf16 input (unpadded), cin/8 planes of m_in positions
+  const char* w;        // packed weights [tap][cin/8][cout][8]
+  const float* bias;
+  char* out;            // planar-8 bf16 destination (unpadded)
+  long long m_in, m_out;
+  int pp_total;         // n * Hp * Wp padded positions
+  int n, cin, H, W, Hp, Wp, Ho, Wo, cout;
+  int kh, kw;           // taps used: rows [tap_r0, tap_r0 + kh) of the kernel, all kw columns
+  int ph, pw;           // padding seen by those taps
+  int tap_r0;           // H == 1: the kernel rows above / below the centre only ever meet padding and are skipped
+  int ntaps_full;       // taps of the whole kernel (the weight layout's)
+  int out_chunk0, Nt, relu;
+  int m_tiles, n_tiles;
+  int mt;               // m tiles (128 positions each) per work item: 1, 2 or 4 independent accumulators
+  int sets;             // accumulator sets in TMEM: 2 = the epilogue of an item overlaps the UMMAs of the next one
+  int win;              // positions per window
+  int a_stages, b_stages;
+  int ks;               // K steps (16 channels) per window stage / weight slice
+  int tps;              // taps per weight slice (one slice = one B stage)
+  long long* trace;     // MTLDAS_C_TRACE: clock64 stamps of CTA 0, [role 0..3][event < 64][4]
+};
+
+constexpr int kWThreads = 256;                  // warp 0 windows, warp 1 weights, warp 2 MMA issue, warps 4-7 epilogue
+constexpr int kWMaxA = 8, kWMaxB = 12;
+constexpr uint32_t kWHeader = 512 + 2048;       // mbarriers + TMEM slot, then the layer's bias (<= 512 floats)
+constexpr uint32_t kWSmemBudget = 225 * 1024;   // one CTA per SM (<= 512 TMEM columns); two CTAs per SM get half each (<= 256)
+
+// Waits of the producer / epilogue warps: they back off between polls so that the MMA-issue thread (one thread, bound by
+// its own instruction latency) keeps the issue slots and the mbarrier unit.  Bounded like ptx::mbar_wait.
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
+  if (ptx::mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  uint32_t spins = 0;
+  while (!ptx::mbar_try_wait(bar, parity)) {
+    __nanosleep(32);
+    if ((++spins & 255u) == 0 && clock64() - t0 > 4000000000ll) {
+      printf("mtldas: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+      __trap();
+    }
+  }
+}
+
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(ptx::smem_u32(bar)), "r"(bytes) : "memory");
+}
+
+// UMMA / commit executed by the whole warp on warp-uniform operands; one elected lane issues (always the same one: the
+// commit tracks the UMMAs of the thread that issued them)
+__device__ __forceinline__ void umma_bf16_elect(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                                uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, e;\n\t.reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "mov.b64 da, {%1, %2};\n\t"
+      "mov.b64 db, {%3, %4};\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}"
+      ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate));
+}
+__device__ __forceinline__ void umma_commit_elect(uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}"
+      ::"r"(ptx::smem_u32(bar)) : "memory");
+}
+
+// eight accumulator columns + bias, lower clamp (0 = ReLU), rounded to one 16-byte granule of bf16
+__device__ __forceinline__ uint4 bias_act_pack8(const uint32_t* r, const float* bias, float lo) {
+  const float4 b0 = *reinterpret_cast<const float4*>(bias), b1 = *reinterpret_cast<const float4*>(bias + 4);
+  uint4 o;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
+  h[0] = __floats2bfloat162_rn(fmaxf(__uint_as_float(r[0]) + b0.x, lo), fmaxf(__uint_as_float(r[1]) + b0.y, lo));
+  h[1] = __floats2bfloat162_rn(fmaxf(__uint_as_float(r[2]) + b0.z, lo), fmaxf(__uint_as_float(r[3]) + b0.w, lo));
+  h[2] = __floats2bfloat162_rn(fmaxf(__uint_as_float(r[4]) + b1.x, lo), fmaxf(__uint_as_float(r[5]) + b1.y, lo));
+  h[3] = __floats2bfloat162_rn(fmaxf(__uint_as_float(r[6]) + b1.z, lo), fmaxf(__uint_as_float(r[7]) + b1.w, lo));
+  return o;
+}
+
+#define WTRACE(role, ev, slot) \
+  do { if (p.trace && blockIdx.x == 0 && (ev) < 64) p.trace[((role) * 64 + (ev)) * 4 + (slot)] = clock64(); } while (0)
+
+__global__ void __launch_bounds__(kWThreads, 2) convc_window_kernel(const __grid_constant__ ConvWParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint64_t* a_full = reinterpret_cast<uint64_t*>(smem);            // [kWMaxA] one arrival + the window's bytes
+  uint64_t* a_empty = a_full + kWMaxA;                              // [kWMaxA] one tcgen05.commit
+  uint64_t* b_full = a_empty + kWMaxA;                              // [kWMaxB] one arrival + the slice's bytes
+  uint64_t* b_empty = b_full + kWMaxB;                              // [kWMaxB] one tcgen05.commit
+  uint64_t* acc_full = b_empty + kWMaxB;                            // [2] one tcgen05.commit per tile
+  uint64_t* acc_empty = acc_full + 2;                               // [2] four epilogue warps
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 384);
+  float* bias_s = reinterpret_cast<float*>(smem + 512);             // [cout]
+  const int Nt = p.Nt, SA = p.a_stages, SB = p.b_stages, win = p.win, ks = p.ks, MT = p.mt, SETS = p.sets;
+  const uint32_t a_stage = 2u * (uint32_t)ks * (uint32_t)win * 16u;  // 2 ks chunk planes of `win` positions
+  const uint32_t b_stage = (uint32_t)p.tps * 2u * (uint32_t)ks * (uint32_t)Nt * 16u;
+  uint8_t* a_base = smem + kWHeader;
+  uint8_t* b_base = a_base + (size_t)SA * a_stage;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);      // provably warp-uniform: role code stays in
+  const int lane = threadIdx.x & 31;                                          // uniform registers
+  const int KC = p.cin >> 4;                                        // K steps (16 channels)
+  const int KU = (KC + ks - 1) / ks;                                // units of ks K steps
+  const int ntaps = p.kh * p.kw;
+  const int nslices = (ntaps + p.tps - 1) / p.tps;
+  const int total = p.m_tiles * p.n_tiles;
+  const uint32_t set_cols = ((uint32_t)Nt + 31u) & ~31u;            // TMEM columns of one accumulator set
+  uint32_t cols = 32;
+  while (cols < (uint32_t)(SETS * MT) * set_cols) cols <<= 1;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < SA; ++s) ptx::mbar_init(a_full + s, 1), ptx::mbar_init(a_empty + s, 1);
+    for (int s = 0; s < SB; ++s) ptx::mbar_init(b_full + s, 1), ptx::mbar_init(b_empty + s, 1);
+    for (int s = 0; s < 2; ++s) ptx::mbar_init(acc_full + s, 1), ptx::mbar_init(acc_empty + s, 4);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 2) ptx::tmem_alloc(tmem_slot, cols);
+  for (int i = threadIdx.x; i < p.cout; i += blockDim.x) bias_s[i] = p.bias[i];
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+
+  if (warp == 0) {
+    // ---------------- window producer: the whole warp; one stage = one tile's window of one 32-channel unit ----------------
+    const bool padded = (p.ph | p.pw) != 0;
+    int a = 0, round = 0, ev = 0;
+    for (int w = blockIdx.x; w < total; w += gridDim.x) {
+      const int pp0 = (w / p.n_tiles) * 128 * MT;
+      for (int ku = 0; ku < KU; ++ku) {
+        if (lane == 0) WTRACE(0, ev, 0);
+        if (round) mbar_wait_relaxed(a_empty + a, (uint32_t)(round - 1) & 1u);
+        if (lane == 0) WTRACE(0, ev, 1);
+        uint8_t* stage = a_base + (size_t)a * a_stage;
+        const int nch = 2 * min(ks, KC - ku * ks);
+        const char* xk = p.x + (long long)(ku * 2 * ks) * p.m_in * 16;
+        if (!padded) {
+          // padded position == input position: one copy per chunk plane, across rows and images
+          const int npos = min(win, p.pp_total - pp0);
+          if (lane < nch) {
+            mbar_expect_tx(a_full + a, (uint32_t)npos * 16u);
+            ptx::bulk_g2s(stage + (size_t)lane * win * 16, xk + ((long long)lane * p.m_in + pp0) * 16, (uint32_t)npos * 16u,
+                          a_full + a);
+          }
+        } else {
+          // one task per (padded row of the window, chunk plane): bulk copy of the row's interior, zeros in its padding
+          const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+          const int row0 = pp0 / p.Wp, row1 = min((pp0 + win - 1) / p.Wp, p.n * p.Hp - 1);
+          const int ncopies = (row1 - row0 + 1) * nch;
+          for (int i = lane; i < ncopies; i += 32) {
+            const int row = row0 + i / nch, c = i - (i / nch) * nch;
+            const int img = row / p.Hp, hp = row - img * p.Hp;
+            const int rel = pp0 - row * p.Wp;                         // window start relative to this padded row
+            const int w_lo = max(0, rel), w_hi = min(p.Wp, rel + win);  // the row's cells inside the window
+            uint4* cells = reinterpret_cast<uint4*>(stage + ((long long)c * win - rel) * 16);   // cells[wp]
+            if (hp < p.ph || hp >= p.ph + p.H) {                      // a padding row
+              for (int x = w_lo; x < w_hi; ++x) cells[x] = z;
+              continue;
+            }
+            for (int x = w_lo; x < min(p.pw, w_hi); ++x) cells[x] = z;
+            for (int x = max(p.pw + p.W, w_lo); x < w_hi; ++x) cells[x] = z;
+            const int lo = max(p.pw, rel), hi = min(p.pw + p.W, rel + win);
+            if (lo >= hi) continue;
+            const uint32_t bytes = (uint32_t)(hi - lo) * 16u;
+            mbar_expect_tx(a_full + a, bytes);
+            ptx::bulk_g2s(stage + ((size_t)c * win + (lo - rel)) * 16,
+                          xk + ((long long)c * p.m_in + ((long long)img * p.H + (hp - p.ph)) * p.W + (lo - p.pw)) * 16, bytes,
+                          a_full + a);
+          }
+          fence_proxy_async();               // the zeros (generic proxy) are read by the UMMAs (async proxy)
+        }
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(a_full + a);
+        if (lane == 0) WTRACE(0, ev, 2);
+        ++ev;
+        if (++a == SA) a = 0, ++round;
+      }
+    }
+  } else if (warp == 1) {
+    // ---------------- weight producer: one stage = `tps` taps of one K unit for this tile's output channels: contiguous in
+    // the packed layout [n tile][K unit][tap][chunk][Nt][8], one bulk copy ----------------
+    const int cin_chunks = p.cin >> 3;
+    int b = 0, round = 0, ev = 0;
+    for (int w = blockIdx.x; w < total; w += gridDim.x) {
+      const char* wn = p.w + (long long)(w % p.n_tiles) * p.ntaps_full * cin_chunks * Nt * 16;
+      for (int ku = 0; ku < KU; ++ku) {
+        const int nch = 2 * min(ks, KC - ku * ks);
+        const char* wu = wn + ((long long)ku * p.ntaps_full * 2 * ks + (long long)p.tap_r0 * p.kw * nch) * Nt * 16;
+        for (int sl = 0; sl < nslices; ++sl) {
+          const int t0 = sl * p.tps, nt = min(p.tps, ntaps - t0);
+          if (lane == 0) WTRACE(1, ev, 0);
+          if (round) mbar_wait_relaxed(b_empty + b, (uint32_t)(round - 1) & 1u);
+          if (lane == 0) {
+            WTRACE(1, ev, 1);
+            const uint32_t bytes = (uint32_t)(nt * nch * Nt * 16);
+            ptx::mbar_arrive_expect_tx(b_full + b, bytes);
+            ptx::bulk_g2s(b_base + (size_t)b * b_stage, wu + (long long)t0 * nch * Nt * 16, bytes, b_full + b);
+            WTRACE(1, ev, 2);
+          }
+          ++ev;
+          if (++b == SB) b = 0, ++round;
+        }
+      }
+    }
+  }
+  else if (warp == 2) {
+    // ---------------- MMA issue: tile t accumulates into TMEM set t & 1; a tap is a shifted A descriptor.  All 32 lanes
+    // run this code on warp-uniform values only (kernel parameters and loop counters: the descriptors then live in
+    // uniform registers, which is what UTCHMMA reads) and one elected lane issues; consecutive UMMAs go to the MT
+    // independent accumulators of the work item ----------------
+    const uint32_t idesc = ptx::umma_idesc_bf16(128, Nt, 0, 0);
+    const uint64_t a_hi = ptx::umma_desc(0, (uint32_t)win * 16u, 128u);        // LBO: next chunk plane; SBO: next 8 rows
+    const uint64_t b_hi = ptx::umma_desc(0, (uint32_t)Nt * 16u, 128u);
+    const uint32_t a_hl = (uint32_t)a_hi, a_hh = (uint32_t)(a_hi >> 32), b_hl = (uint32_t)b_hi, b_hh = (uint32_t)(b_hi >> 32);
+    const uint32_t a16 = ptx::smem_u32(a_base) >> 4, b16 = ptx::smem_u32(b_base) >> 4;
+    int a = 0, around = 0, b = 0, bround = 0, t = 0, ev = 0;
+    for (int w = blockIdx.x; w < total; w += gridDim.x, ++t) {
+      // one accumulator set: the epilogue of item t - 1 must have drained it (a second CTA on the SM fills the gap);
+      // two sets: item t uses set t & 1, drained by the epilogue of item t - 2
+      const int set = SETS == 2 ? (t & 1) : 0, use = SETS == 2 ? (t >> 1) : t;
+      if (use >= 1) {
+        ptx::mbar_wait(acc_empty + set, (uint32_t)(use - 1) & 1u);
+        ptx::tc_fence_after();
+      }
+      const uint32_t d = tmem_base + (uint32_t)(set * MT) * set_cols;
+      uint32_t acc = 0u;
+      for (int ku = 0; ku < KU; ++ku) {
+        const int nk = min(ks, KC - ku * ks);
+        if (lane == 0) WTRACE(2, ev, 0);
+        ptx::mbar_wait(a_full + a, (uint32_t)around & 1u);
+        const uint32_t a_st = (a16 + (uint32_t)a * (a_stage >> 4)) | a_hl;
+        int r = 0, q = 0;
+        for (int sl = 0; sl < nslices; ++sl) {
+          const int nt = min(p.tps, ntaps - sl * p.tps);
+          if (lane == 0) WTRACE(2, ev, 1);
+          ptx::mbar_wait(b_full + b, (uint32_t)bround & 1u);
+          ptx::tc_fence_after();
+          if (lane == 0) WTRACE(2, ev, 2);
+          uint32_t b_lo = (b16 + (uint32_t)b * (b_stage >> 4)) | b_hl;
+          for (int tl = 0; tl < nt; ++tl) {
+            uint32_t a_lo = a_st + (uint32_t)(r * p.Wp + q);                   // 16-byte units: one position
+            for (int j = 0; j < nk; ++j, a_lo += (uint32_t)(2 * win), b_lo += (uint32_t)(2 * Nt)) {
+              uint32_t dm = d, am = a_lo;
+              for (int mt = 0; mt < MT; ++mt, dm += set_cols, am += 128u) umma_bf16_elect(dm, am, a_hh, b_lo, b_hh, idesc, acc);
+              acc = 1u;
+            }
+            if (++q == p.kw) q = 0, ++r;
+          }
+          umma_commit_elect(b_empty + b);
+          if (lane == 0) WTRACE(2, ev, 3);
+          ++ev;
+          if (++b == SB) b = 0, ++bround;
+        }
+        umma_commit_elect(a_empty + a);
+        if (++a == SA) a = 0, ++around;
+      }
+      umma_commit_elect(acc_full + set);
+    }
+  } else if (warp >= 4) {
+    // ---------------- epilogue: bias + ReLU, bf16, 16-byte granules at the concat offset ----------------
+    const int q4 = warp & 3;                                        // the TMEM lane quarter this warp may read
+    const int hwp = p.Hp * p.Wp;
+    const long long oplane = p.m_out * 16;
+    const float lo = p.relu ? 0.f : -INFINITY;
+    int t = 0;
+    for (int w = blockIdx.x; w < total; w += gridDim.x, ++t) {
+      const int set = SETS == 2 ? (t & 1) : 0, use = SETS == 2 ? (t >> 1) : t;
+      const int n0 = (w % p.n_tiles) * Nt;
+      const float* bias = bias_s + n0;
+      if (threadIdx.x == 128) WTRACE(3, t, 0);
+      mbar_wait_relaxed(acc_full + set, (uint32_t)use & 1u);
+      ptx::tc_fence_after();
+      if (threadIdx.x == 128) WTRACE(3, t, 1);
+      for (int mt = 0; mt < MT; ++mt) {
+        const int pp = ((w / p.n_tiles) * MT + mt) * 128 + q4 * 32 + lane;       // padded position of this thread's row
+        const int img = pp / hwp, rem = pp - img * hwp;
+        const int ho = rem / p.Wp, wo = rem - ho * p.Wp;
+        const bool store = pp < p.pp_total && ho < p.Ho && wo < p.Wo;
+        const long long m = ((long long)img * p.Ho + ho) * p.Wo + wo;
+        char* out_row = p.out + ((long long)(p.out_chunk0 + (n0 >> 3)) * p.m_out + m) * 16;
+        const uint32_t trow = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(set * MT + mt) * set_cols;
+        int c0 = 0;
+        for (; c0 + 32 <= Nt; c0 += 32) {
+          uint32_t r[32];
+          ptx::tmem_ld32_issue(trow + (uint32_t)c0, r);
+          ptx::tmem_wait32(r);
+          if (store) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              *reinterpret_cast<uint4*>(out_row + ((c0 >> 3) + k) * oplane) = bias_act_pack8(r + 8 * k, bias + c0 + 8 * k, lo);
+          }
+        }
+        if (c0 < Nt) {                                              // Nt is a multiple of 16
+          uint32_t r[16];
+          ptx::tmem_ld16_issue(trow + (uint32_t)c0, r);
+          ptx::tmem_wait16(r);
+          if (store) {
+#pragma unroll
+            for (int k = 0; k < 2; ++k)
+              *reinterpret_cast<uint4*>(out_row + ((c0 >> 3) + k) * oplane) = bias_act_pack8(r + 8 * k, bias + c0 + 8 * k, lo);
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(acc_empty + set);
+      if (threadIdx.x == 128) WTRACE(3, t, 2);
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) ptx::tmem_dealloc(tmem_base, cols);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -342,7 +672,7 @@ __global__ void __launch_bounds__(256) packc_kernel(const float* __restrict__ w,
                                                     const float* __restrict__ beta, const float* __restrict__ rmean,
                                                     const float* __restrict__ rvar, float eps, int cout, int cin, int taps,
                                                     __nv_bfloat16* __restrict__ dst, float* __restrict__ bias,
-                                                    float* __restrict__ first_w) {
+                                                    float* __restrict__ first_w, int Nt, int ks) {
   const int total = cout * cin * taps;
   for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
     const int co = i / (cin * taps), r1 = i - co * cin * taps, ci = r1 / taps, t = r1 - ci * taps;
@@ -350,7 +680,12 @@ __global__ void __launch_bounds__(256) packc_kernel(const float* __restrict__ w,
     if (r1 == 0) bias[co] = beta[co] - rmean[co] * sc;
     const float v = w[i] * sc;
     if (first_w) first_w[t * cout + co] = v;                            // [tap][cout] fp32 (cin == 1)
-    else dst[(((size_t)t * (cin >> 3) + (ci >> 3)) * cout + co) * 8 + (ci & 7)] = __float2bfloat16(v);
+    else {                                                              // [n tile][K unit][tap][chunk][Nt][8]
+      const int CC = cin >> 3, gc = ci >> 3, ku = gc / (2 * ks), cl = gc - ku * 2 * ks, nch = min(2 * ks, CC - ku * 2 * ks);
+      const int nt = co / Nt, col = co - nt * Nt;
+      dst[((((size_t)nt * taps * CC + (size_t)ku * taps * 2 * ks + (size_t)t * nch + cl) * Nt) + col) * 8 + (ci & 7)] =
+          __float2bfloat16(v);
+    }
   }
 }
 
@@ -371,6 +706,27 @@ int pick_nt(int cout) {   // output channels per CTA: the largest divisor of cou
   for (int parts = 1; parts <= 8; ++parts)
     if (cout % parts == 0 && (cout / parts) % 16 == 0 && cout / parts <= 256) return cout / parts;
   return 0;
+}
+
+
+// Weight layout shared by both convolution kernels: [n tile][K unit][tap][chunk of the unit][Nt][8] bf16, a K unit being
+// `ks` K steps (2 ks chunks of 8 channels; the last unit may be shorter).  Every (n tile, K unit, run of taps) is one
+// contiguous block: the window kernel brings a weight slice with ONE bulk copy (a bulk copy costs ~70 cycles of issue
+// whatever its size).  ks is chosen so that a slice (one synchronisation step of the MMA warp) carries >= ~8 UMMAs.
+struct WeightLayout {
+  int Nt, ks, m_max;
+};
+WeightLayout weight_layout(int cin, int cout, int kh, int kw) {
+  WeightLayout l{};
+  l.Nt = pick_nt(cout);
+  if (!l.Nt) return l;
+  const size_t tap_step = 32 * (size_t)l.Nt;                       // bytes of one tap, one K step
+  l.m_max = (int)std::max<size_t>(1, (l.Nt >= 128 ? 48 * 1024 : 32 * 1024) / tap_step);
+  const int ntaps = kh * kw, KC = cin / 16;
+  l.ks = 1;
+  if (ntaps < l.m_max)
+    while (l.ks * 2 <= KC && l.ks * 2 * ntaps <= l.m_max && l.ks < 8) l.ks *= 2;
+  return l;
 }
 
 }  // namespace
@@ -396,9 +752,17 @@ extern "C" int mtldas_c_pack_conv(const float* dev_w, const float* dev_gamma, co
     return MTLDAS_ERR_ARG;
   }
   const int total = cout * cin * kh * kw;
+  WeightLayout lay{1, 1, 1};
+  if (cin != 1) {
+    lay = weight_layout(cin, cout, kh, kw);
+    if (!lay.Nt) {
+      set_error("c_pack_conv: cout %d not supported (a multiple of 16 with a divisor <= 256)", cout);
+      return MTLDAS_ERR_UNSUPPORTED;
+    }
+  }
   packc_kernel<<<std::min(592, (total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
       dev_w, dev_gamma, dev_beta, dev_rmean, dev_rvar, eps, cout, cin, kh * kw, cin == 1 ? nullptr : (__nv_bfloat16*)dev_packed,
-      dev_bias, cin == 1 ? (float*)dev_packed : nullptr);
+      dev_bias, cin == 1 ? (float*)dev_packed : nullptr, lay.Nt, lay.ks);
   CKC(cudaGetLastError(), "c_pack_conv");
   return 0;
 }
@@ -425,16 +789,97 @@ extern "C" int mtldas_c_conv(const void* dev_x, int n, int cin, int h, int w, co
     CKC(cudaGetLastError(), "c_conv (first)");
     return 0;
   }
-  const int Nt = pick_nt(cout);
+  const WeightLayout lay = weight_layout(cin, cout, kh, kw);
+  const int Nt = lay.Nt;
   if ((cin % 16) || !Nt) {
     set_error("c_conv: cin %d / cout %d not supported (multiples of 16)", cin, cout);
     return MTLDAS_ERR_UNSUPPORTED;
+  }
+  static const bool use_window = [] {
+    const char* e = getenv("MTLDAS_C_WINDOW");       // 0: the gather kernel for every layer (A/B timing)
+    return !(e && e[0] == '0');
+  }();
+  if (use_window && sh == 1 && sw == 1 && cout <= 512) {
+    ConvWParams q{};
+    q.x = (const char*)dev_x, q.w = (const char*)dev_packed, q.bias = dev_bias, q.out = (char*)dev_out;
+    q.m_in = (long long)n * h * w, q.m_out = m_out;
+    q.n = n, q.cin = cin, q.H = h, q.W = w, q.Ho = Ho, q.Wo = Wo, q.cout = cout;
+    q.kh = kh, q.kw = kw, q.ph = ph, q.pw = pw, q.tap_r0 = 0;
+    if (h == 1 && kh == 2 * ph + 1) q.tap_r0 = ph, q.kh = 1, q.ph = 0;      // one-row images: only the centre kernel row
+    q.Hp = h + 2 * q.ph, q.Wp = w + 2 * q.pw;
+    q.out_chunk0 = out_channel0 / 8, q.Nt = Nt, q.relu = relu;
+    const long long pp_total = (long long)n * q.Hp * q.Wp;
+    const int ntaps = q.kh * q.kw;
+    // One synchronisation step of the MMA warp (a weight slice) carries up to m_max UMMAs: `tps` taps x `ks` K steps,
+    // ks being fixed by the weight layout.
+    const size_t tap_step = 32 * (size_t)Nt;                                 // bytes of one tap, one K step
+    q.ks = lay.ks, q.ntaps_full = kh * kw;
+    const int per_slice = std::max(1, lay.m_max / lay.ks), nsl = (ntaps + per_slice - 1) / per_slice;
+    q.tps = (ntaps + nsl - 1) / nsl;
+    const size_t b_stage = (size_t)q.tps * q.ks * tap_step;
+    const int set_cols = (Nt + 31) & ~31, halo = (q.kh - 1) * q.Wp + (q.kw - 1);
+    int dev = 0, sms = 0;
+    CKC(cudaGetDevice(&dev), "c_conv (device)");
+    CKC(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev), "c_conv (device)");
+    // Configurations, best first.  Two CTAs per SM double the UMMA issue rate (one issuing warp per CTA, bound by its own
+    // instruction latency: ~70 cycles per UMMA in the unrolled m-tile loop, ~220 in the tap loop), so they come first;
+    // each CTA then gets half of the shared memory and at most 256 TMEM columns.
+    static const int force_ctas = [] { const char* e = getenv("MTLDAS_C_CTAS"); return e ? atoi(e) : 0; }();
+    static const int mt_cap = [] { const char* e = getenv("MTLDAS_C_MT"); return e ? atoi(e) : 4; }();
+    struct Cfg { int ctas, sets, mt; };
+    static const Cfg cfgs[] = {{2, 2, 4}, {2, 2, 2}, {2, 1, 2}, {2, 2, 1}, {2, 1, 1}, {1, 2, 4}, {1, 2, 2}, {1, 2, 1}, {1, 1, 2}, {1, 1, 1}};
+    size_t a_stage = 0, smem_w = 0;
+    int ctas = 0;
+    for (const Cfg& c : cfgs) {
+      if ((force_ctas && c.ctas != force_ctas) || c.mt > mt_cap) continue;
+      if (c.sets * c.mt * set_cols > (c.ctas == 2 ? 256 : 512)) continue;
+      const long long items_c = (pp_total + 128 * c.mt - 1) / (128 * c.mt) * (cout / Nt);
+      if (c.mt > 1 && items_c < 2ll * sms * c.ctas) continue;              // keep every CTA busy for a few items
+      const size_t bud = (c.ctas == 2 ? kWSmemBudget / 2 - 1024 : kWSmemBudget) - kWHeader;
+      q.win = (128 * c.mt + halo + 7) & ~7;
+      a_stage = 32 * (size_t)q.ks * q.win;
+      if (2 * a_stage + 2 * b_stage > bud) continue;
+      q.b_stages = 3 * b_stage <= bud * 45 / 100 ? (4 * b_stage <= bud * 30 / 100 ? 4 : 3) : 2;
+      q.a_stages = (int)std::min<size_t>(kWMaxA, (bud - q.b_stages * b_stage) / a_stage);
+      if (q.a_stages < 2) continue;
+      q.mt = c.mt, q.sets = c.sets, ctas = c.ctas, smem_w = bud + kWHeader;
+      break;
+    }
+    if (pp_total < (1ll << 31) - 65536 && ctas) {
+      q.pp_total = (int)pp_total;
+      q.m_tiles = (int)((pp_total + 128 * q.mt - 1) / (128 * q.mt)), q.n_tiles = cout / Nt;
+      static PerDeviceSmem configured_w;
+      CKC(configured_w.ensure(kWSmemBudget, [](int bytes) {
+            return cudaFuncSetAttribute(convc_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+          }), "c_conv (attribute)");
+      const long long items = (long long)q.m_tiles * q.n_tiles;
+      static const bool trace = getenv("MTLDAS_C_TRACE") != nullptr;      // timeline of CTA 0 on stdout (tools/modelc_layer.py)
+      if (trace) cudaMalloc(&q.trace, 1024 * 8), cudaMemset(q.trace, 0, 1024 * 8);
+      convc_window_kernel<<<(unsigned)std::min<long long>(items, (long long)sms * ctas), kWThreads, smem_w, st>>>(q);
+      CKC(cudaGetLastError(), "c_conv (window)");
+      if (trace) {
+        static long long h[1024];
+        cudaDeviceSynchronize();
+        cudaMemcpy(h, q.trace, sizeof(h), cudaMemcpyDeviceToHost);
+        cudaFree(q.trace);
+        const long long z = h[2 * 256];
+        printf("window kernel: %d CTA/SM, A stages %d x %zu B, B stages %d x %zu B, ks %d tps %d mt %d sets %d win %d Nt %d\n", ctas, q.a_stages,
+               a_stage, q.b_stages, b_stage, q.ks, q.tps, q.mt, q.sets, q.win, Nt);
+        for (int i = 0; i < 40; ++i) {
+          const long long *a = h + i * 4, *b = h + 256 + i * 4, *m = h + 512 + i * 4, *e = h + 768 + i * 4;
+          printf("%2d | A wait %6lld got %6lld issued %6lld | B wait %6lld got %6lld issued %6lld | MMA a-wait %6lld b-wait %6lld got %6lld "
+                 "committed %6lld | EPI wait %6lld got %6lld done %6lld\n", i, a[0] - z, a[1] - z, a[2] - z, b[0] - z, b[1] - z, b[2] - z,
+                 m[0] - z, m[1] - z, m[2] - z, m[3] - z, e[0] - z, e[1] - z, e[2] - z);
+        }
+      }
+      return 0;
+    }
   }
   ConvCParams p{};
   p.x = (const char*)dev_x, p.w = (const char*)dev_packed, p.bias = dev_bias, p.out = (char*)dev_out;
   p.m_in = (long long)n * h * w, p.m_out = m_out;
   p.n = n, p.cin = cin, p.H = h, p.W = w, p.Ho = Ho, p.Wo = Wo, p.cout = cout, p.kh = kh, p.kw = kw, p.sh = sh, p.sw = sw;
-  p.ph = ph, p.pw = pw, p.out_chunk0 = out_channel0 / 8, p.Nt = Nt, p.relu = relu;
+  p.ph = ph, p.pw = pw, p.out_chunk0 = out_channel0 / 8, p.Nt = Nt, p.relu = relu, p.ks = lay.ks;
   const size_t smem = 256 + 1024 + (size_t)kCStages * (2 * kCUnitSteps * 128 * 16 + 2 * kCUnitSteps * Nt * 16);
   static PerDeviceSmem configured;
   CKC(configured.ensure(smem, [](int bytes) {

@@ -23,6 +23,12 @@ CONVC_CASES = [
     (384, 384, 1, 3, 1, 1, 0, 1, 1, 6),       # InceptionE 1x3
     (448, 384, 3, 3, 1, 1, 1, 1, 1, 6),       # InceptionE 3x3 (28 K steps per tap)
     (2048, 320, 1, 1, 1, 1, 0, 0, 1, 6),      # InceptionE 1x1 over 2048 channels
+    (384, 384, 3, 1, 1, 1, 1, 0, 1, 6),       # InceptionE 3x1 on one-row images (only the centre kernel row meets data)
+    (192, 192, 7, 1, 1, 1, 3, 0, 4, 13, 67),  # 7x1, 67 images: every CTA of the persistent kernel walks several tiles
+    (32, 64, 3, 3, 1, 1, 1, 1, 47, 122, 48),  # Conv2d_2b at 48 images: ~20 tiles per CTA (TMEM sets, rings wrap many times)
+    (16, 48, 3, 3, 1, 1, 1, 1, 9, 11, 3),     # one K step only, N = 48 (16-column epilogue tail), tiny images
+    (32, 32, 3, 3, 1, 1, 0, 0, 49, 124, 40),  # Conv2d_2a at 40 images: four m tiles per work item (N = 32)
+    (96, 96, 3, 3, 1, 1, 1, 1, 10, 28, 300),  # InceptionA 3x3dbl_3 at 300 images: two m tiles per work item (N = 96)
 ]
 
 
@@ -36,8 +42,8 @@ def test_model_c_conv_unit_matches_torch(case):
     import ctypes
     from mtldas_b200 import lib
     from mtldas_b200._lib import check
-    cin, cout, kh, kw, sh, sw, ph, pw, H, W = case
-    n = 5
+    cin, cout, kh, kw, sh, sw, ph, pw, H, W = case[:10]
+    n = case[10] if len(case) > 10 else 5
     g = torch.Generator().manual_seed(cin + cout + kh)
     x = torch.randn(n, cin, H, W, generator=g)
     w = torch.randn(cout, cin, kh, kw, generator=g) / (cin * kh * kw) ** 0.5
