@@ -223,15 +223,18 @@ __global__ void __launch_bounds__(kCThreads, 2) convc_umma_kernel(const __grid_c
 }
 
 // ---------------------------------------------------------------------------------------------
-// convc_window_kernel: every stride-1 convolution (84 of the 94).  Positions are enumerated in the PADDED image
-// (Hp = H + 2 ph rows of Wp = W + 2 pw positions); a tile is 128 consecutive padded positions and tap (r, q) of the
-// kernel is the same 128 rows shifted by r * Wp + q positions.  So one WINDOW of 128 + (kh-1) * Wp + (kw-1) positions per
-// 32-channel unit is brought into shared memory once (bulk copies of whole row segments, the zero padding is written
-// there, not in HBM) and all kh * kw taps are UMMAs whose A descriptor start address is shifted: the input is read from
-// L2 about once instead of kh * kw times, by one warp issuing a few bulk copies instead of 128 threads issuing 16-byte
-// copies per tap.  Outputs whose padded position is not a valid output (right / bottom margin) are computed and dropped.
-// Persistent: one CTA per SM walks over the (m tile, n tile) work items, the accumulator is double-buffered in TMEM so
-// that the four epilogue warps store tile t while the MMA thread is on tile t + 1.
+// convc_window_kernel: the stride-1 convolutions (84 of the 94).  Positions are enumerated in a PADDED image whose
+// padding is shared between neighbours: Wp = W + pw positions per row (the right padding of a row is the left padding
+// of the next one), Hp = H + ph rows per image (the bottom padding of an image is the top padding of the next), pixel
+// (0, 0) of image 0 at position off = ph * Wp + pw.  Output (img, ho, wo) is position u = (img * Hp + ho) * Wp + wo and
+// reads, for tap (r, q), position u + r * Wp + q.  A work item is MT x 128 consecutive positions; ONE window of
+// MT * 128 + (kh-1) * Wp + (kw-1) positions per K unit is brought into shared memory (bulk copies of whole row
+// segments; the zero padding is written there, not in HBM) and every tap is a UMMA whose A descriptor start address is
+// shifted: the input is read from L2 about once instead of kh * kw times, by one warp issuing a few bulk copies instead
+// of 128 threads issuing 16-byte copies per tap.  Positions that are no valid output (margins, padding rows) are
+// computed and dropped: layers where they are more than ~45 % extra go to the gather kernel instead.
+// Persistent: the CTAs walk over the (m group, n tile) work items; the accumulators live in TMEM (MT per set, two sets
+// when they fit: four epilogue warps store item t while the MMA warp is on item t + 1).
 // ---------------------------------------------------------------------------------------------
 struct ConvWParams {
   const char* x;        // planar-8 bf16 input (unpadded), cin/8 planes of m_in positions
@@ -240,9 +243,11 @@ struct ConvWParams {
   char* out;            // planar-8 bf16 destination (unpadded)
   long long m_in, m_out;
   int pp_total;         // n * Hp * Wp padded positions
-  int n, cin, H, W, Hp, Wp, Ho, Wo, cout;
+  int n, cin, H, W, Ho, Wo, cout;
+  int Hp, Wp;           // H + ph rows per image, W + pw positions per row (see the kernel comment)
   int kh, kw;           // taps used: rows [tap_r0, tap_r0 + kh) of the kernel, all kw columns
   int ph, pw;           // padding seen by those taps
+  int off;              // ph * Wp + pw: position of pixel (0, 0) of image 0 in the padded enumeration
   int tap_r0;           // H == 1: the kernel rows above / below the centre only ever meet padding and are skipped
   int ntaps_full;       // taps of the whole kernel (the weight layout's)
   int out_chunk0, Nt, relu;
@@ -377,29 +382,29 @@ __global__ void __launch_bounds__(kWThreads, 2) convc_window_kernel(const __grid
                           a_full + a);
           }
         } else {
-          // one task per (padded row of the window, chunk plane): bulk copy of the row's interior, zeros in its padding
+          // one task per (row of the window, chunk plane): bulk copy of the row's pixels, zeros in its padding.  Rows are
+          // counted from one image period before the first image (the window may start in the top padding of image 0).
           const uint4 z = make_uint4(0u, 0u, 0u, 0u);
-          const int row0 = pp0 / p.Wp, row1 = min((pp0 + win - 1) / p.Wp, p.n * p.Hp - 1);
+          const int s0 = pp0 - p.off + p.Hp * p.Wp;
+          const int row0 = s0 / p.Wp, row1 = min((s0 + win - 1) / p.Wp, (p.n + 1) * p.Hp - 1);
           const int ncopies = (row1 - row0 + 1) * nch;
           for (int i = lane; i < ncopies; i += 32) {
             const int row = row0 + i / nch, c = i - (i / nch) * nch;
-            const int img = row / p.Hp, hp = row - img * p.Hp;
-            const int rel = pp0 - row * p.Wp;                         // window start relative to this padded row
+            const int img = row / p.Hp - 1, hp = row - (img + 1) * p.Hp;
+            const int rel = s0 - row * p.Wp;                          // window start relative to this row
             const int w_lo = max(0, rel), w_hi = min(p.Wp, rel + win);  // the row's cells inside the window
             uint4* cells = reinterpret_cast<uint4*>(stage + ((long long)c * win - rel) * 16);   // cells[wp]
-            if (hp < p.ph || hp >= p.ph + p.H) {                      // a padding row
+            if (img < 0 || hp >= p.H) {                               // a padding row (shared by two images)
               for (int x = w_lo; x < w_hi; ++x) cells[x] = z;
               continue;
             }
-            for (int x = w_lo; x < min(p.pw, w_hi); ++x) cells[x] = z;
-            for (int x = max(p.pw + p.W, w_lo); x < w_hi; ++x) cells[x] = z;
-            const int lo = max(p.pw, rel), hi = min(p.pw + p.W, rel + win);
-            if (lo >= hi) continue;
-            const uint32_t bytes = (uint32_t)(hi - lo) * 16u;
+            for (int x = max(p.W, w_lo); x < w_hi; ++x) cells[x] = z;   // right padding = left padding of the next row
+            const int hi = min(p.W, w_hi);
+            if (w_lo >= hi) continue;
+            const uint32_t bytes = (uint32_t)(hi - w_lo) * 16u;
             mbar_expect_tx(a_full + a, bytes);
-            ptx::bulk_g2s(stage + ((size_t)c * win + (lo - rel)) * 16,
-                          xk + ((long long)c * p.m_in + ((long long)img * p.H + (hp - p.ph)) * p.W + (lo - p.pw)) * 16, bytes,
-                          a_full + a);
+            ptx::bulk_g2s(stage + ((size_t)c * win + (w_lo - rel)) * 16,
+                          xk + ((long long)c * p.m_in + ((long long)img * p.H + hp) * p.W + w_lo) * 16, bytes, a_full + a);
           }
           fence_proxy_async();               // the zeros (generic proxy) are read by the UMMAs (async proxy)
         }
@@ -552,7 +557,7 @@ __global__ void __launch_bounds__(kWThreads, 2) convc_window_kernel(const __grid
 __global__ void __launch_bounds__(256) convc_first_kernel(const float* __restrict__ x, const float* __restrict__ w9,
                                                           const float* __restrict__ bias, char* __restrict__ out, int n,
                                                           int H, int W, int Ho, int Wo, int cout) {
-  __shared__ float ws[9 * 64], bs[64];
+  __shared__ __align__(16) float ws[9 * 64], bs[64];
   for (int i = threadIdx.x; i < 9 * cout; i += 256) ws[i] = w9[i];       // [tap][cout]
   for (int i = threadIdx.x; i < cout; i += 256) bs[i] = bias[i];
   __syncthreads();
@@ -569,12 +574,17 @@ __global__ void __launch_bounds__(256) convc_first_kernel(const float* __restric
       for (int q = 0; q < 3; ++q) v[r * 3 + q] = src[r * W + q];
     for (int c0 = 0; c0 < cout; c0 += 8) {
       float acc[8];
+      *reinterpret_cast<float4*>(acc) = *reinterpret_cast<const float4*>(bs + c0);
+      *reinterpret_cast<float4*>(acc + 4) = *reinterpret_cast<const float4*>(bs + c0 + 4);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] = bs[c0 + j];
-#pragma unroll
-      for (int t = 0; t < 9; ++t)
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = fmaf(v[t], ws[t * cout + c0 + j], acc[j]);
+      for (int t = 0; t < 9; ++t) {               // 128-bit broadcast reads: the kernel was bound by 288 scalar LDS per thread
+        const float4 w0 = *reinterpret_cast<const float4*>(ws + t * cout + c0);
+        const float4 w1 = *reinterpret_cast<const float4*>(ws + t * cout + c0 + 4);
+        acc[0] = fmaf(v[t], w0.x, acc[0]), acc[1] = fmaf(v[t], w0.y, acc[1]);
+        acc[2] = fmaf(v[t], w0.z, acc[2]), acc[3] = fmaf(v[t], w0.w, acc[3]);
+        acc[4] = fmaf(v[t], w1.x, acc[4]), acc[5] = fmaf(v[t], w1.y, acc[5]);
+        acc[6] = fmaf(v[t], w1.z, acc[6]), acc[7] = fmaf(v[t], w1.w, acc[7]);
+      }
       uint4 q4;
       __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&q4);
 #pragma unroll
@@ -629,6 +639,55 @@ __global__ void __launch_bounds__(256) poolc_kernel(const char* __restrict__ x, 
 #pragma unroll
     for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(acc[2 * j] * sc, acc[2 * j + 1] * sc);
     *reinterpret_cast<uint4*>(dst + (long long)m * 16) = o;
+  }
+}
+
+// F.avg_pool2d(x, 3, 1, 1) as a separable rolling sum: a thread owns one (image, column, 8-channel chunk) and walks down
+// the rows, three 16-byte loads and ~50 arithmetic instructions per output instead of nine loads and ~250 (the generic
+// kernel above is instruction bound on these layers, three times off the HBM time).
+__device__ __forceinline__ void add_cell(float* acc, const char* p) {
+  const uint4 g = *reinterpret_cast<const uint4*>(p);
+  const uint32_t w[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    acc[2 * j] += __uint_as_float(w[j] << 16);              // bf16 -> fp32 is a shift
+    acc[2 * j + 1] += __uint_as_float(w[j] & 0xffff0000u);
+  }
+}
+__global__ void __launch_bounds__(256) avgpoolc_kernel(const char* __restrict__ x, char* __restrict__ out, int n, int H, int W,
+                                                       int out_chunk0) {
+  const unsigned idx = blockIdx.x * 256u + threadIdx.x;
+  if (idx >= (unsigned)n * W) return;
+  const unsigned img = idx / (unsigned)W;
+  const int wo = (int)(idx - img * (unsigned)W);
+  const long long M = (long long)n * H * W;
+  const char* col = x + ((long long)blockIdx.y * M + (long long)img * H * W + wo) * 16;
+  char* dst = out + ((long long)(out_chunk0 + blockIdx.y) * M + (long long)img * H * W + wo) * 16;
+  const bool left = wo > 0, right = wo + 1 < W;
+  float r0[8], r1[8], r2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) r0[j] = 0.f, r1[j] = 0.f;
+  add_cell(r1, col);
+  if (left) add_cell(r1, col - 16);
+  if (right) add_cell(r1, col + 16);
+  for (int h = 0; h < H; ++h) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) r2[j] = 0.f;
+    if (h + 1 < H) {
+      const char* p = col + (long long)(h + 1) * W * 16;
+      add_cell(r2, p);
+      if (left) add_cell(r2, p - 16);
+      if (right) add_cell(r2, p + 16);
+    }
+    uint4 o;
+    __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      hh[j] = __floats2bfloat162_rn((r0[2 * j] + r1[2 * j] + r2[2 * j]) * (1.f / 9.f),
+                                    (r0[2 * j + 1] + r1[2 * j + 1] + r2[2 * j + 1]) * (1.f / 9.f));
+    *reinterpret_cast<uint4*>(dst + (long long)h * W * 16) = o;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) r0[j] = r1[j], r1[j] = r2[j];
   }
 }
 
@@ -806,9 +865,11 @@ extern "C" int mtldas_c_conv(const void* dev_x, int n, int cin, int h, int w, co
     q.n = n, q.cin = cin, q.H = h, q.W = w, q.Ho = Ho, q.Wo = Wo, q.cout = cout;
     q.kh = kh, q.kw = kw, q.ph = ph, q.pw = pw, q.tap_r0 = 0;
     if (h == 1 && kh == 2 * ph + 1) q.tap_r0 = ph, q.kh = 1, q.ph = 0;      // one-row images: only the centre kernel row
-    q.Hp = h + 2 * q.ph, q.Wp = w + 2 * q.pw;
+    q.Hp = h + q.ph, q.Wp = w + q.pw, q.off = q.ph * q.Wp + q.pw;     // padding shared by neighbouring rows / images
     q.out_chunk0 = out_channel0 / 8, q.Nt = Nt, q.relu = relu;
     const long long pp_total = (long long)n * q.Hp * q.Wp;
+    static const int max_waste = [] { const char* e = getenv("MTLDAS_C_WASTE"); return e ? atoi(e) : 145; }();
+    const bool window_ok = q.kh > q.ph && q.kw > q.pw && pp_total * 100 <= m_out * max_waste;   // else: the gather kernel
     const int ntaps = q.kh * q.kw;
     // One synchronisation step of the MMA warp (a weight slice) carries up to m_max UMMAs: `tps` taps x `ks` K steps,
     // ks being fixed by the weight layout.
@@ -845,7 +906,7 @@ extern "C" int mtldas_c_conv(const void* dev_x, int n, int cin, int h, int w, co
       q.mt = c.mt, q.sets = c.sets, ctas = c.ctas, smem_w = bud + kWHeader;
       break;
     }
-    if (pp_total < (1ll << 31) - 65536 && ctas) {
+    if (pp_total < (1ll << 31) - 65536 && ctas && window_ok) {
       q.pp_total = (int)pp_total;
       q.m_tiles = (int)((pp_total + 128 * q.mt - 1) / (128 * q.mt)), q.n_tiles = cout / Nt;
       static PerDeviceSmem configured_w;
@@ -905,6 +966,12 @@ extern "C" int mtldas_c_pool(const void* dev_x, int n, int channels, int h, int 
     return MTLDAS_ERR_UNSUPPORTED;
   }
   const int chunks = channels / 8;
+  if (is_avg && stride == 1 && pad == 1) {
+    avgpoolc_kernel<<<dim3((unsigned)(((long long)n * w + 255) / 256), (unsigned)chunks), 256, 0, (cudaStream_t)stream>>>(
+        (const char*)dev_x, (char*)dev_out, n, h, w, out_channel0 / 8);
+    CKC(cudaGetLastError(), "c_pool (avg)");
+    return 0;
+  }
   const unsigned bx = (unsigned)std::max<long long>(1, std::min<long long>((mo + 255) / 256, (148 * 16 + chunks - 1) / chunks));
   poolc_kernel<<<dim3(bx, (unsigned)chunks), 256, 0, (cudaStream_t)stream>>>(
       (const char*)dev_x, (char*)dev_out, n, channels / 8, h, w, Ho, Wo, stride, pad, is_avg, out_channel0 / 8);

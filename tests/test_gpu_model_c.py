@@ -74,6 +74,38 @@ def test_model_c_conv_unit_matches_torch(case):
     assert float(out[0].abs().max()) == 0.0 and float(out[-1].abs().max()) == 0.0      # neighbours of the slice untouched
 
 
+@pytest.mark.parametrize("case", [(64, 10, 28, 1, 1, 1), (768, 4, 13, 1, 1, 1), (2048, 1, 6, 1, 1, 1), (24, 5, 1, 1, 1, 1),
+                                  (64, 47, 122, 0, 2, 0), (192, 21, 58, 0, 2, 0), (288, 10, 28, 0, 2, 0)],
+                         ids=lambda c: "c%d_%dx%d_%s" % (c[0], c[1], c[2], "avg" if c[3] else "max"))
+def test_model_c_pool_unit_matches_torch(case):
+    """F.avg_pool2d(x, 3, 1, 1) (the padding counts: divide by 9 everywhere) and the 3x3 / stride-2 max pools, on bf16
+    values: the average is one bf16 rounding of the fp32 sum, the maximum is exact."""
+    import ctypes
+    from mtldas_b200 import lib
+    from mtldas_b200._lib import check
+    C, H, W, is_avg, stride, pad = case
+    n = 7
+    x = torch.randn(n, C, H, W, generator=torch.Generator().manual_seed(C + H)).bfloat16().float()
+    ref = F.avg_pool2d(x.double(), 3, 1, 1) if is_avg else F.max_pool2d(x.double(), 3, stride)
+    Ho, Wo = ref.shape[2:]
+    dev = torch.device("cuda:0")
+    xp = _planar(x).to(dev)
+    ctot, c0 = C + 16, 8
+    out = torch.zeros((ctot // 8, n * Ho * Wo, 8), dtype=torch.bfloat16, device=dev)
+    p = lambda t: ctypes.c_void_p(t.data_ptr())  # noqa: E731
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    check(lib.mtldas_c_pool(p(xp), n, C, H, W, p(out), ctot, c0, stride, pad, is_avg, st), "pool")
+    got = torch.empty((n, C, Ho, Wo), device=dev)
+    check(lib.mtldas_c_read(p(out), n, ctot, c0, C, Ho * Wo, p(got), st), "read")
+    torch.cuda.synchronize()
+    got = got.cpu().double()
+    if is_avg:
+        assert float((got - ref).abs().max()) <= 2.0 ** -8 * float(ref.abs().max())
+    else:
+        assert torch.equal(got, ref)
+    assert float(out[0].abs().max()) == 0.0 and float(out[-1].abs().max()) == 0.0
+
+
 def test_model_c_forward_matches_oracle():
     """Multi_Classifier.forward (eval) for 9 patches: logits within 1e-2 of the fp64 oracle (relative to the largest
     logit; north_star bf16 tolerance), same argmax wherever the top-2 margin is clear, stage features within 2e-2."""
