@@ -9,6 +9,7 @@ GAP + fc) and returns raw logits [N, 32] (the reference's loss is CrossEntropyLo
 forward (batch statistics, Dropout, backward) is not built for this model: it raises -- there is no PyTorch fallback.
 """
 import ctypes
+import os
 
 import torch
 import torch.nn as nn
@@ -57,9 +58,36 @@ class _Program:
         for name in ("Mixed_7b", "Mixed_7c"):
             t = self.inception_e(t, name)
         self.last = t
+        self._schedule()
+        self.graph = None
         for name, (c, h, w) in self.shapes.items():
             if name != "x":
                 self.buf[name] = torch.empty((c // 8, n * h * w, 8), dtype=torch.bfloat16, device=device)
+
+    def _schedule(self):
+        """Read-after-write dependencies between the ops (every tensor is written once, nothing is reused) and a stream
+        lane per op: the stem is lane 0, the branches of an Inception block take lanes 0..3 in order of appearance."""
+        writers, self.deps, self.lane = {}, [], []
+        block_lanes = {}
+        for i, (kind, src, dst, c0, arg) in enumerate(self.ops):
+            self.deps.append(list(writers.get(src, ())))
+            writers.setdefault(dst, []).append(i)
+            name = arg if kind == "conv" else dst              # a pool inside a block writes "<block>.avgpool" / the block
+            lane = 0
+            if kind == "pool" and "." not in name and src.startswith("Mixed"):
+                name = dst + ".maxpool"                            # InceptionB / D pool straight into the block tensor
+            if "." in name:
+                block, branch = name.split(".", 1)
+                branch = branch.rstrip("ab").rstrip("0123456789").rstrip("_")
+                if branch == "avgpool":
+                    branch = "branch_pool"                         # the pool and its 1x1 conv are one chain
+                lanes = block_lanes.setdefault(block, {})
+                lane = lanes.setdefault(branch, len(lanes))
+            self.lane.append(lane)
+        self.cross = [False] * len(self.ops)
+        for i, ds in enumerate(self.deps):
+            for d in ds:
+                self.cross[d] = True       # an event per producer (also same-lane consumers: lanes fold modulo the stream count)
 
     # ---- op builders ---------------------------------------------------------------------------------
     def tensor(self, name, c, h, w):
@@ -143,6 +171,25 @@ class _Program:
         self.conv(t, n + ".branch3x3dbl_3b", out, 1472)
         self.conv(self.pool(x, n + ".avgpool", 1, 1, True), n + ".branch_pool", out, 1856)
         return out
+
+
+class _GraphRun:
+    """The layer program of one (device, batch) captured once as a CUDA graph over four streams and replayed: ~110 launches
+    per forward cost more host time than the GPU needs for a small batch, and the small layers of the 4x13 and 1x6 stages
+    do not fill 148 SMs one at a time."""
+
+    def __init__(self, module, prog, packed):
+        dev = prog.device
+        self.packed = packed
+        self.x = torch.empty((prog.n, 1, 100, 250), dtype=torch.float32, device=dev)
+        self.logits = torch.empty((prog.n, module.num_classes), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            module._launch(prog, packed, self.x, self.logits, None)        # eager once: kernel attributes, lazy module load
+            torch.cuda.synchronize(dev)
+            self.side = [torch.cuda.Stream(dev) for _ in range(3)]
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                module._launch(prog, packed, self.x, self.logits, [torch.cuda.current_stream(dev)] + self.side)
 
 
 class Multi_Classifier(nn.Module):
@@ -245,31 +292,62 @@ class Multi_Classifier(nn.Module):
                 self._programs.pop(next(iter(self._programs)))
             prog = self._programs[key] = _Program(n, dev)
         packed = self._pack(dev)
-        logits = torch.empty((n, self.num_classes), dtype=torch.float32, device=dev)
-        st = _stream_ptr(dev)
-        ptr = lambda name: ctypes.c_void_p(x.data_ptr() if name == "x" else prog.buf[name].data_ptr())  # noqa: E731
-        self.last_launch_count = 0
-        with torch.cuda.device(dev):
-            for kind, src, dst, c0, arg in prog.ops:
-                c, h, w = prog.shapes[src]
-                ctot = prog.shapes[dst][0]
-                if kind == "conv":
-                    cin, cout, k, s, pad = _SPECS[arg]
-                    wp, bp, _ = packed[arg]
-                    check(lib.mtldas_c_conv(ptr(src), n, cin, h, w, ctypes.c_void_p(wp.data_ptr()),
-                                            ctypes.c_void_p(bp.data_ptr()), ptr(dst), ctot, c0, cout, k[0], k[1], s[0], s[1],
-                                            pad[0], pad[1], 1, st), "c_conv " + arg)
-                else:
-                    stride, pad, avg = arg
-                    check(lib.mtldas_c_pool(ptr(src), n, c, h, w, ptr(dst), ctot, c0, stride, pad, avg, st), "c_pool")
-                self.last_launch_count += 1
-            c, h, w = prog.shapes[prog.last]
-            fw, fb = packed["fc"]
-            check(lib.mtldas_c_head(ptr(prog.last), n, c, h * w, ctypes.c_void_p(fw.data_ptr()), ctypes.c_void_p(fb.data_ptr()),
-                                    self.num_classes, ctypes.c_void_p(logits.data_ptr()), st), "c_head")
-            self.last_launch_count += 1
         self._last_program = prog
-        return logits
+        self.last_launch_count = len(prog.ops) + 1
+        if os.environ.get("MTLDAS_C_NO_GRAPH"):
+            logits = torch.empty((n, self.num_classes), dtype=torch.float32, device=dev)
+            with torch.cuda.device(dev):
+                self._launch(prog, packed, x, logits, None)
+            return logits
+        run = prog.graph if prog.graph is not None and prog.graph.packed is packed else None
+        if run is None:
+            run = prog.graph = _GraphRun(self, prog, packed)
+        run.x.copy_(x)
+        run.graph.replay()
+        return run.logits.clone()
+
+    def _launch(self, prog, packed, x, logits, streams):
+        """Enqueue the layer program.  streams=None: everything on the current stream.  Otherwise a list of streams (the
+        first one is the current / capturing stream): the branches of an Inception block are independent until the
+        concat, each goes to its own stream (events carry the read-after-write dependencies; no buffer is reused)."""
+        n, dev = prog.n, prog.device
+        ptr = lambda name: ctypes.c_void_p(x.data_ptr() if name == "x" else prog.buf[name].data_ptr())  # noqa: E731
+        events = {}
+        for i, (kind, src, dst, c0, arg) in enumerate(prog.ops):
+            if streams is None:
+                st = _stream_ptr(dev)
+            else:
+                s = streams[prog.lane[i] % len(streams)]
+                for d in prog.deps[i]:
+                    if prog.lane[d] % len(streams) != prog.lane[i] % len(streams):
+                        s.wait_event(events[d])
+                st = ctypes.c_void_p(s.cuda_stream)
+            c, h, w = prog.shapes[src]
+            ctot = prog.shapes[dst][0]
+            if kind == "conv":
+                cin, cout, k, sd, pad = _SPECS[arg]
+                wp, bp, _ = packed[arg]
+                check(lib.mtldas_c_conv(ptr(src), n, cin, h, w, ctypes.c_void_p(wp.data_ptr()),
+                                        ctypes.c_void_p(bp.data_ptr()), ptr(dst), ctot, c0, cout, k[0], k[1], sd[0], sd[1],
+                                        pad[0], pad[1], 1, st), "c_conv " + arg)
+            else:
+                stride, pad, avg = arg
+                check(lib.mtldas_c_pool(ptr(src), n, c, h, w, ptr(dst), ctot, c0, stride, pad, avg, st), "c_pool")
+            if streams is not None and prog.cross[i]:
+                events[i] = torch.cuda.Event()
+                events[i].record(s)
+        if streams is not None:                       # join: the head reads the last block, written from every stream
+            for s in streams[1:]:
+                e = torch.cuda.Event()
+                e.record(s)
+                streams[0].wait_event(e)
+            st = ctypes.c_void_p(streams[0].cuda_stream)
+        else:
+            st = _stream_ptr(dev)
+        c, h, w = prog.shapes[prog.last]
+        fw, fb = packed["fc"]
+        check(lib.mtldas_c_head(ptr(prog.last), n, c, h * w, ctypes.c_void_p(fw.data_ptr()), ctypes.c_void_p(fb.data_ptr()),
+                                self.num_classes, ctypes.c_void_p(logits.data_ptr()), st), "c_head")
 
     def read_tensor(self, name):
         """Debug / tests: an intermediate tensor of the last forward as fp32 [n, C, H, W] (names = reference module names)."""

@@ -145,3 +145,21 @@ def test_model_c_forward_matches_oracle():
     from mtldas_b200 import MtldasError
     with pytest.raises(MtldasError):
         m(x.cuda())
+
+
+def test_model_c_graph_replay_equals_eager_launches():
+    """forward() replays a CUDA graph captured over four streams (Inception branches side by side); the same kernels
+    enqueued one after the other on one stream give the same bits, for two batch sizes and after new input data."""
+    from model.modelC_multiClassifier import Multi_Classifier
+    m = Multi_Classifier(init_weights=False)
+    m.load_state_dict(C.synth_state_dict_c(seed=1), strict=True)
+    m = m.cuda().eval()
+    for n, seed in ((6, 1), (33, 2), (6, 3)):
+        x = O.synth_patches(n, seed=seed)[0].cuda()
+        out = m(x)
+        prog = m._last_program
+        eager = torch.empty_like(out)
+        m._launch(prog, m._pack(x.device), x.contiguous(), eager, None)
+        torch.cuda.synchronize()
+        assert torch.equal(out, eager), float((out - eager).abs().max())
+        assert prog.graph is not None and m.last_launch_count == len(prog.ops) + 1

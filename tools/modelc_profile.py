@@ -48,7 +48,7 @@ for kind, src, dst, c0, arg in prog.ops:
         rows.append((ms, "pool:" + dst, f"{c} ch {h}x{w}", 0.0))
 tot = sum(r[0] for r in rows)
 print(f"batch {n}: sum of per-op times {tot:.3f} ms -> {n / tot * 1e3:.0f} patches/s (serialised)")
-for ms, name, what, tf in sorted(rows, reverse=True)[:40]:
+for ms, name, what, tf in sorted(rows, reverse=True)[:int(os.environ.get("TOP", "40"))]:
     print(f"{ms:8.4f} ms {100 * ms / tot:5.1f}%  {tf:7.1f} TFLOP/s  {name:32s} {what}")
 by = {}
 for ms, name, what, tf in rows:
