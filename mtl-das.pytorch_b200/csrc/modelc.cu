@@ -56,6 +56,9 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
+__device__ __forceinline__ void cp_async_arrive_noinc(uint64_t* bar) {   // this thread's arrival, deferred until its copies landed
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(ptx::smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 __global__ void __launch_bounds__(kCThreads, 2) convc_umma_kernel(const __grid_constant__ ConvCParams p) {
@@ -248,6 +251,7 @@ struct ConvWParams {
   int kh, kw;           // taps used: rows [tap_r0, tap_r0 + kh) of the kernel, all kw columns
   int ph, pw;           // padding seen by those taps
   int off;              // ph * Wp + pw: position of pixel (0, 0) of image 0 in the padded enumeration
+  int cells;            // padded window built cell by cell (cp.async) instead of row by row (bulk copies): narrow images
   int tap_r0;           // H == 1: the kernel rows above / below the centre only ever meet padding and are skipped
   int ntaps_full;       // taps of the whole kernel (the weight layout's)
   int out_chunk0, Nt, relu;
@@ -348,7 +352,7 @@ __global__ void __launch_bounds__(kWThreads, 2) convc_window_kernel(const __grid
   while (cols < (uint32_t)(SETS * MT) * set_cols) cols <<= 1;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < SA; ++s) ptx::mbar_init(a_full + s, 1), ptx::mbar_init(a_empty + s, 1);
+    for (int s = 0; s < SA; ++s) ptx::mbar_init(a_full + s, p.cells ? 33 : 1), ptx::mbar_init(a_empty + s, 1);
     for (int s = 0; s < SB; ++s) ptx::mbar_init(b_full + s, 1), ptx::mbar_init(b_empty + s, 1);
     for (int s = 0; s < 2; ++s) ptx::mbar_init(acc_full + s, 1), ptx::mbar_init(acc_empty + s, 4);
     ptx::fence_mbar_init();
@@ -381,6 +385,21 @@ __global__ void __launch_bounds__(kWThreads, 2) convc_window_kernel(const __grid
             ptx::bulk_g2s(stage + (size_t)lane * win * 16, xk + ((long long)lane * p.m_in + pp0) * 16, (uint32_t)npos * 16u,
                           a_full + a);
           }
+        } else if (p.cells) {
+          // narrow images: a row segment is a few cells, and a bulk copy costs ~70 cycles of issue whatever its size.
+          // Cell by cell instead: 16-byte cp.async with zero fill for the padding, one position (all chunk planes) per
+          // lane and step; each lane's arrival on the stage's barrier is deferred until its copies have landed.
+          const int s0 = pp0 - p.off + p.Hp * p.Wp;
+          for (int pos = lane; pos < win; pos += 32) {
+            const int v = s0 + pos, row = v / p.Wp, wp = v - row * p.Wp;
+            const int img = row / p.Hp - 1, hp = row - (img + 1) * p.Hp;
+            const bool ok = img >= 0 && img < p.n && hp < p.H && wp < p.W;
+            const char* src = ok ? xk + (((long long)img * p.H + hp) * p.W + wp) * 16 : p.x;
+            const long long plane = ok ? p.m_in * 16 : 0;
+            const uint32_t dst = ptx::smem_u32(stage) + (uint32_t)pos * 16u;
+            for (int c = 0; c < nch; ++c) cp_async16(dst + (uint32_t)(c * win) * 16u, src + c * plane, ok ? 16u : 0u);
+          }
+          cp_async_arrive_noinc(a_full + a);
         } else {
           // one task per (row of the window, chunk plane): bulk copy of the row's pixels, zeros in its padding.  Rows are
           // counted from one image period before the first image (the window may start in the top padding of image 0).
@@ -467,6 +486,7 @@ __global__ void __launch_bounds__(kWThreads, 2) convc_window_kernel(const __grid
         const int nk = min(ks, KC - ku * ks);
         if (lane == 0) WTRACE(2, ev, 0);
         ptx::mbar_wait(a_full + a, (uint32_t)around & 1u);
+        if (p.cells) fence_proxy_async();      // the cells were written through the generic proxy (cp.async)
         const uint32_t a_st = (a16 + (uint32_t)a * (a_stage >> 4)) | a_hl;
         int r = 0, q = 0;
         for (int sl = 0; sl < nslices; ++sl) {
@@ -866,6 +886,8 @@ extern "C" int mtldas_c_conv(const void* dev_x, int n, int cin, int h, int w, co
     q.kh = kh, q.kw = kw, q.ph = ph, q.pw = pw, q.tap_r0 = 0;
     if (h == 1 && kh == 2 * ph + 1) q.tap_r0 = ph, q.kh = 1, q.ph = 0;      // one-row images: only the centre kernel row
     q.Hp = h + q.ph, q.Wp = w + q.pw, q.off = q.ph * q.Wp + q.pw;     // padding shared by neighbouring rows / images
+    static const int cells_w = [] { const char* e = getenv("MTLDAS_C_CELLS_W"); return e ? atoi(e) : 8; }();
+    q.cells = (q.ph | q.pw) != 0 && w <= cells_w;
     q.out_chunk0 = out_channel0 / 8, q.Nt = Nt, q.relu = relu;
     const long long pp_total = (long long)n * q.Hp * q.Wp;
     static const int max_waste = [] { const char* e = getenv("MTLDAS_C_WASTE"); return e ? atoi(e) : 145; }();
@@ -896,6 +918,7 @@ extern "C" int mtldas_c_conv(const void* dev_x, int n, int cin, int h, int w, co
       if (c.sets * c.mt * set_cols > (c.ctas == 2 ? 256 : 512)) continue;
       const long long items_c = (pp_total + 128 * c.mt - 1) / (128 * c.mt) * (cout / Nt);
       if (c.mt > 1 && items_c < 2ll * sms * c.ctas) continue;              // keep every CTA busy for a few items
+      if (c.ctas == 2 && items_c <= sms && !force_ctas) continue;          // one item per SM at most: deeper rings instead
       const size_t bud = (c.ctas == 2 ? kWSmemBudget / 2 - 1024 : kWSmemBudget) - kWHeader;
       q.win = (128 * c.mt + halo + 7) & ~7;
       a_stage = 32 * (size_t)q.ks * q.win;
