@@ -45,7 +45,7 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=256, help="patches per CPU-baseline step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the model B / streaming side measurements")
-    ap.add_argument("--model-c-batch", type=int, default=512, help="patches per GPU per step of the model C side measurement")
+    ap.add_argument("--model-c-batch", type=int, default=2048, help="patches per GPU per step of the model C side measurement")
     ap.add_argument("--no-train", action="store_true", help="skip the training-step measurement (kernel tuning runs)")
     ap.add_argument("--train-batch", type=int, default=256, help="training patches per GPU per step")
     return ap.parse_args()

@@ -92,6 +92,20 @@ def test_model_c_layer_program_shapes():
         cover.sort()
         assert cover[0][0] == 0 and cover[-1][1] == prog.shapes[blk][0]
         assert all(a[1] == b[0] for a, b in zip(cover, cover[1:])), (blk, cover)
+    # stream schedule of the captured graph: dependencies are exactly the writers of the op's source tensor, a chain of a
+    # branch stays on one lane, the four branches of a block are on four different lanes, nothing is written twice
+    assert len(prog.deps) == len(prog.lane) == len(prog.ops)
+    for i, (kind, src, dst, c0, arg) in enumerate(prog.ops):
+        writers = [j for j, op in enumerate(prog.ops) if op[2] == src]
+        assert prog.deps[i] == writers and all(j < i for j in writers), (i, arg)
+        if "." in src:                                   # a branch-private tensor: its consumer stays on the producer's lane
+            assert len(writers) == 1 and prog.lane[i] == prog.lane[writers[0]], (i, arg)
+    for blk in ("Mixed_5c", "Mixed_6d", "Mixed_7b"):
+        heads = [i for i, op in enumerate(prog.ops) if op[1] == prog.ops[[o[2] for o in prog.ops].index(blk)][1]
+                 and (op[2] == blk or op[2].startswith(blk + "."))]
+        assert sorted(prog.lane[i] for i in heads) == [0, 1, 2, 3], (blk, [prog.lane[i] for i in heads])
+    written = [(op[2], op[3]) for op in prog.ops]
+    assert len(set(written)) == len(written)
 
 
 def test_model_c_boundary_class_and_launcher():
