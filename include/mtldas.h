@@ -237,9 +237,13 @@ MTLDAS_API int mtldas_eval_metrics(const float* dev_logp0, const long long* dev_
  * tensors and the layer program.  bf16 tensor-core path only.  All calls are asynchronous on `stream`.
  *
  * c_pack_conv: folds BatchNorm (running statistics, eps as given) into the conv weight [cout, cin, kh, kw] and writes
- *   the packed image [kh*kw][cin/8][cout][8] bf16 (cin == 1: [kh*kw][cout] fp32) and the bias [cout] fp32.
+ *   the packed image (kh*kw*cin*cout bf16 in the kernels' own order [output-channel tile][K unit][tap][8-channel
+ *   chunk][channel of the tile][8]: what one CTA consumes at a time is contiguous; cin == 1: [kh*kw][cout] fp32) and
+ *   the bias [cout] fp32.  The image is only meaningful to c_conv called with the same cout, cin, kh, kw.
  * c_conv: out[:, out_channel0 : +cout] = relu?(conv(x) + bias); x planar-8 [n, cin, h, w] (cin == 1: the fp32 patches
  *   [n,1,h,w], 3x3 / stride 2 / no padding only); any kernel size / stride / padding; cin, cout multiples of 16.
+ *   Stride-1 layers run the window kernel (the input window of a tile is staged once in shared memory, every tap is
+ *   a shifted tcgen05 operand descriptor), the others the gather kernel; the choice is internal.
  * c_pool: 3x3 max pool (is_avg 0; F.max_pool2d(x, 3, stride), no padding) or 3x3 average pool that counts the padding
  *   (is_avg 1; F.avg_pool2d(x, 3, stride, pad)), written at out_channel0 of the destination tensor.
  * c_head: logits = Linear(mean over the hw positions)  (AdaptiveAvgPool2d(1) + flatten + fc, modelC:137-146).

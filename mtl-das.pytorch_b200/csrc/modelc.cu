@@ -9,12 +9,17 @@
 // Layout "planar-8": a tensor [n, C, H, W] is C/8 planes of n*H*W positions, one position of one plane = 8 consecutive
 // channels as bf16 (16 bytes).  A channel concat is a chunk offset into the destination tensor.
 //
-// convc_umma_kernel: implicit GEMM on tcgen05.  One CTA = 128 output positions x Nt <= 256 output channels.  The K loop
-// runs over (tap, 32-channel unit); four gather warps build the A tile of a unit with 16-byte cp.async copies (zero fill
-// outside the image: any kernel size / stride / padding is index arithmetic, no im2col tensor, no tensor maps), one
-// producer thread brings the unit's weight slice with bulk copies, one thread issues the UMMAs into a TMEM accumulator;
-// a ring of stages overlaps the three.  The epilogue (folded-BN bias + ReLU, bf16, 16-byte stores at the concat offset)
-// is done by the gather warps.  This model is compute bound (1.1 GMAC per patch, Cout up to 448).
+// Two tcgen05 implicit-GEMM convolution kernels share one weight layout (weight_layout() below):
+//   convc_window_kernel  stride-1 layers: the window of input positions a tile needs is staged once in shared memory and
+//                        every tap is a shifted operand descriptor (see the comment in front of it);
+//   convc_umma_kernel    stride-2 layers and layers whose padded enumeration would waste > 45 %: one CTA = 128 output
+//                        positions x Nt <= 256 output channels; the K loop runs over (tap, 32-channel unit); four gather
+//                        warps build the A tile of a unit with 16-byte cp.async copies (zero fill outside the image: any
+//                        kernel size / stride / padding is index arithmetic), one producer thread brings the unit's
+//                        weights with bulk copies, one thread issues the UMMAs into a TMEM accumulator; a ring of stages
+//                        overlaps the three; the gather warps then run the epilogue.
+// Epilogue of both: folded-BN bias + ReLU, bf16, 16-byte stores at the concat offset.  No im2col tensor, no tensor maps.
+// This model is compute bound (1.1 GMAC per patch, Cout up to 448).
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
@@ -33,7 +38,6 @@ namespace {
 constexpr int kCStages = 4;       // ring depth
 constexpr int kCUnitSteps = 2;    // K steps (16 channels each) per ring stage
 constexpr int kCThreads = 192;    // warps 0-3 gather + epilogue, warp 4 MMA issue, warp 5 weight producer
-constexpr int kCHeader = 1024;    // mbarriers, TMEM slot, then bias at kCHeader
 
 struct ConvCParams {
   const char* x;        // planar-8 bf16 input, cin/8 planes of m_in positions
