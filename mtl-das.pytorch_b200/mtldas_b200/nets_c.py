@@ -302,9 +302,10 @@ class Multi_Classifier(nn.Module):
         run = prog.graph if prog.graph is not None and prog.graph.packed is packed else None
         if run is None:
             run = prog.graph = _GraphRun(self, prog, packed)
-        run.x.copy_(x)
-        run.graph.replay()
-        return run.logits.clone()
+        with torch.cuda.device(dev):              # replay on the input's device whatever the caller's current device is
+            run.x.copy_(x)
+            run.graph.replay()
+            return run.logits.clone()
 
     def _launch(self, prog, packed, x, logits, streams):
         """Enqueue the layer program.  streams=None: everything on the current stream.  Otherwise a list of streams (the
