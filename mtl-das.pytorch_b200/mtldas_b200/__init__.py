@@ -11,6 +11,7 @@ from .engine import (EvalPlan, TrainPlan, FlatAdam, EvalMetrics, conv2d_nchw, co
                      umma_selftest)
 from .nets import MTL_Net, Single_Task_Net  # noqa: F401
 from . import synth  # noqa: F401
+from .prefetch import DevicePrefetcher  # noqa: F401
 
 __all__ = ["MTL_Net", "Single_Task_Net", "EvalPlan", "TrainPlan", "FlatAdam", "EvalMetrics", "conv2d_nchw", "umma_selftest",
-           "lib", "MtldasError"]
+           "lib", "MtldasError", "DevicePrefetcher"]

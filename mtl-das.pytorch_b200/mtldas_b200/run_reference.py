@@ -8,7 +8,9 @@ What it does before handing control to the script (runpy, `__main__`):
     the script's own directory first on sys.path, so a PYTHONPATH override alone cannot shadow the reference's package;
   * provides inert stand-ins for matplotlib / seaborn / ptflops when they are not installed (utils.py:6,8,13 import
     them at module top only to draw curves and count MACs; SURVEY.md D8);
-  * makes sklearn's confusion_matrix return an empty matrix for empty inputs (utils.py:500 crashes on sklearn >= 1.x).
+  * makes sklearn's confusion_matrix return an empty matrix for empty inputs (utils.py:500 crashes on sklearn >= 1.x);
+  * runs every DataLoader iteration through mtldas_b200.prefetch.DevicePrefetcher (pinned staging + upload on a copy
+    stream two batches ahead; the loops' own `.cuda()` calls become no-ops).  MTLDAS_PREFETCH=0 leaves the loaders alone.
 `--check` only performs the set-up, imports the reference's utils.py and reports which classes it picked up.
 """
 import importlib
@@ -58,6 +60,9 @@ def prepare():
         skm.confusion_matrix = confusion_matrix
     except Exception:
         pass
+    if os.environ.get("MTLDAS_PREFETCH", "1") != "0":
+        from .prefetch import install_dataloader_prefetch
+        install_dataloader_prefetch(depth=2)
     return model
 
 
