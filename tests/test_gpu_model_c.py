@@ -1,5 +1,7 @@
 """Model C (Multi_Classifier, Inception-V3 with a 1-channel stem) on the GPU, through the C ABI, against the oracle
 (oracle/modelc_oracle.py, pinned to the unmodified reference by tests/golden/multi_classifier.npz)."""
+import os
+
 import pytest
 import torch
 import torch.nn.functional as F
@@ -72,6 +74,32 @@ def test_model_c_conv_unit_matches_torch(case):
     err = float((got.cpu().double() - ref).abs().max() / ref.abs().max())
     assert err <= 6e-3, (case, err)                                        # one bf16 rounding of the stored result
     assert float(out[0].abs().max()) == 0.0 and float(out[-1].abs().max()) == 0.0      # neighbours of the slice untouched
+
+
+def _fuzz_cases(count=int(os.environ.get("MTLDAS_FUZZ_CASES", "48")), seed=int(os.environ.get("MTLDAS_FUZZ_SEED", "20261107"))):
+    """Random geometries the Inception program does not contain: every kernel shape with every padding from 0 to k // 2
+    (also asymmetric), images down to one row / one column, strides 1 and 2, channel counts that split into one to three
+    output-channel tiles, batch sizes that leave ragged last tiles and give one to several m tiles per work item."""
+    import random
+    rnd = random.Random(seed)
+    cases = []
+    while len(cases) < count:
+        kh, kw = rnd.choice([(1, 1), (3, 3), (1, 3), (3, 1), (5, 5), (1, 7), (7, 1), (3, 5), (2, 2)])
+        s = rnd.choice([1, 1, 1, 2])
+        ph, pw = rnd.randint(0, kh // 2), rnd.randint(0, kw // 2)
+        H, W = rnd.randint(1, 14), rnd.randint(1, 30)
+        if H + 2 * ph < kh or W + 2 * pw < kw:
+            continue
+        cin = rnd.choice([16, 32, 48, 64, 80, 96, 160])
+        cout = rnd.choice([16, 32, 48, 64, 96, 128, 192, 320, 384])
+        n = rnd.choice([1, 2, 7, 33, 70, 150])
+        cases.append((cin, cout, kh, kw, s, s, ph, pw, H, W, n))
+    return cases
+
+
+@pytest.mark.parametrize("case", _fuzz_cases(), ids=lambda c: "c%d-%d_k%dx%d_s%d_p%d%d_%dx%d_n%d" % (c[0], c[1], c[2], c[3], c[4], c[6], c[7], c[8], c[9], c[10]))
+def test_model_c_conv_fuzz_matches_torch(case):
+    test_model_c_conv_unit_matches_torch(case)
 
 
 @pytest.mark.parametrize("case", [(64, 10, 28, 1, 1, 1), (768, 4, 13, 1, 1, 1), (2048, 1, 6, 1, 1, 1), (24, 5, 1, 1, 1, 1),
