@@ -25,6 +25,7 @@
 
 #include <algorithm>
 #include <cstdint>
+#include <cstdio>
 #include <cstdlib>
 
 #include "../../include/mtldas.h"
@@ -213,12 +214,14 @@ __global__ void __launch_bounds__(kCThreads, 2) convc_umma_kernel(const __grid_c
           if (u >= kCStages) ptx::mbar_wait(empty + s, ((u / kCStages) - 1) & 1);
           const int nch = 2 * min(kCUnitSteps, KC - kc0);
           ptx::mbar_arrive_expect_tx(full + s, (uint32_t)(nch * Nt * 16));
-          for (int c = 0; c < nch; ++c) {                 // layout [n tile][K unit][tap][chunk][Nt][8]
-            const int gc = kc0 * 2 + c, ku = gc / (2 * p.ks), cl = gc - ku * 2 * p.ks;
+          for (int c = 0; c < nch;) {                     // layout [n tile][K unit][tap][chunk][Nt][8]: the chunks of
+            const int gc = kc0 * 2 + c, ku = gc / (2 * p.ks), cl = gc - ku * 2 * p.ks;   // one K unit are contiguous
             const int nchu = min(2 * p.ks, cin_chunks - ku * 2 * p.ks);
+            const int run = min(nch - c, nchu - cl);      // one bulk copy per run (a copy costs ~70 cycles of issue)
             ptx::bulk_g2s(b_base + (size_t)s * b_stage + (size_t)c * Nt * 16,
                           p.w + (((long long)blockIdx.y * ntaps * cin_chunks + (long long)ku * ntaps * 2 * p.ks + tap * nchu + cl) * Nt) * 16,
-                          (uint32_t)(Nt * 16), full + s);
+                          (uint32_t)(run * Nt * 16), full + s);
+            c += run;
           }
         }
     }
@@ -809,6 +812,11 @@ WeightLayout weight_layout(int cin, int cout, int kh, int kw) {
   l.ks = 1;
   if (ntaps < l.m_max)
     while (l.ks * 2 <= KC && l.ks * 2 * ntaps <= l.m_max && l.ks < 8) l.ks *= 2;
+  // 1x1 layers: two window stages (128 positions x 2 ks chunks) and two weight slices must fit HALF an SM's shared
+  // memory, so that two CTAs share the SM -- two issuing warps keep the tensor pipe twice as busy as one (measured on
+  // 768 -> 192: one CTA with ks = 8 spends 1500 cycles per 8 UMMAs of 98 cycles each)
+  if (ntaps == 1)
+    while (l.ks > 1 && 2 * (size_t)l.ks * (32 * 128 + tap_step) > 104 * 1024) l.ks /= 2;
   return l;
 }
 
@@ -917,17 +925,25 @@ extern "C" int mtldas_c_conv(const void* dev_x, int n, int cin, int h, int w, co
     static const Cfg cfgs[] = {{2, 2, 4}, {2, 2, 2}, {2, 1, 2}, {2, 2, 1}, {2, 1, 1}, {1, 2, 4}, {1, 2, 2}, {1, 2, 1}, {1, 1, 2}, {1, 1, 1}};
     size_t a_stage = 0, smem_w = 0;
     int ctas = 0;
+    static const Cfg force_cfg = [] {          // MTLDAS_C_CFG="ctas,sets,mt": experiments
+      Cfg f{0, 0, 0};
+      const char* e = getenv("MTLDAS_C_CFG");
+      if (e) sscanf(e, "%d,%d,%d", &f.ctas, &f.sets, &f.mt);
+      return f;
+    }();
     for (const Cfg& c : cfgs) {
       if ((force_ctas && c.ctas != force_ctas) || c.mt > mt_cap) continue;
+      if (force_cfg.ctas && (c.ctas != force_cfg.ctas || c.sets != force_cfg.sets || c.mt != force_cfg.mt)) continue;
       if (c.sets * c.mt * set_cols > (c.ctas == 2 ? 256 : 512)) continue;
       const long long items_c = (pp_total + 128 * c.mt - 1) / (128 * c.mt) * (cout / Nt);
-      if (c.mt > 1 && items_c < 2ll * sms * c.ctas) continue;              // keep every CTA busy for a few items
-      if (c.ctas == 2 && items_c <= sms && !force_ctas) continue;          // one item per SM at most: deeper rings instead
+      if (c.mt > 1 && items_c < 2ll * sms * c.ctas && !force_cfg.ctas) continue;   // keep every CTA busy for a few items
+      if (c.ctas == 2 && items_c <= sms && !force_ctas && !force_cfg.ctas) continue;          // one item per SM at most: deeper rings instead
       const size_t bud = (c.ctas == 2 ? kWSmemBudget / 2 - 1024 : kWSmemBudget) - kWHeader;
       q.win = (128 * c.mt + halo + 7) & ~7;
       a_stage = 32 * (size_t)q.ks * q.win;
       if (2 * a_stage + 2 * b_stage > bud) continue;
       q.b_stages = 3 * b_stage <= bud * 45 / 100 ? (4 * b_stage <= bud * 30 / 100 ? 4 : 3) : 2;
+      while (q.b_stages > 2 && (bud - q.b_stages * b_stage) / a_stage < 2) --q.b_stages;   // two window stages come first
       q.a_stages = (int)std::min<size_t>(kWMaxA, (bud - q.b_stages * b_stage) / a_stage);
       if (q.a_stages < 2) continue;
       q.mt = c.mt, q.sets = c.sets, ctas = c.ctas, smem_w = bud + kWHeader;
