@@ -817,6 +817,11 @@ WeightLayout weight_layout(int cin, int cout, int kh, int kw) {
   // 768 -> 192: one CTA with ks = 8 spends 1500 cycles per 8 UMMAs of 98 cycles each)
   if (ntaps == 1)
     while (l.ks > 1 && 2 * (size_t)l.ks * (32 * 128 + tap_step) > 104 * 1024) l.ks /= 2;
+  // At least two K steps per unit: the gather kernel's ring unit (two K steps) then finds its weights in one contiguous
+  // block = one bulk copy (7x1 layers 750 -> 810 TFLOP/s), and the window kernel does twice the UMMAs per window stage
+  // (3x3 / 5x5 layers +7 %).  Not for wide kernels (1x7): their window rows are short and every extra chunk plane costs
+  // a bulk copy per row (0.080 -> 0.107 ms).
+  if (kw <= kh && l.ks == 1 && KC >= 2) l.ks = 2;
   return l;
 }
 
