@@ -191,3 +191,20 @@ def test_model_c_graph_replay_equals_eager_launches():
         torch.cuda.synchronize()
         assert torch.equal(out, eager), float((out - eager).abs().max())
         assert prog.graph is not None and m.last_launch_count == len(prog.ops) + 1
+
+
+def test_model_c_forward_is_batch_size_invariant():
+    """The first patches of a 300-patch batch (several m tiles per work item, many items per CTA, two CTAs per SM) get the
+    logits they get in a 9-patch batch (one m tile per item): the tiling never changes the order of a K reduction, and
+    eval-mode BatchNorm has no batch statistics -- bit-equal rows; the 9-patch result is the one checked against the oracle."""
+    from model.modelC_multiClassifier import Multi_Classifier
+    m = Multi_Classifier(init_weights=False)
+    m.load_state_dict(C.synth_state_dict_c(seed=0), strict=True)
+    m = m.cuda().eval()
+    x = O.synth_patches(300, seed=4242)[0].cuda()
+    big = m(x)
+    small = m(x[:9].contiguous())
+    mid = m(x[:130].contiguous())
+    torch.cuda.synchronize()
+    assert torch.equal(big[:9], small), float((big[:9] - small).abs().max())
+    assert torch.equal(big[:130], mid), float((big[:130] - mid).abs().max())
