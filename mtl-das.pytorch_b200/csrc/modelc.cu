@@ -42,7 +42,7 @@ constexpr int kCThreads = 192;    // warps 0-3 gather + epilogue, warp 4 MMA iss
 
 struct ConvCParams {
   const char* x;        // planar-8 bf16 input, cin/8 planes of m_in positions
-  const char* w;        // packed weights [tap][cin/8][cout][8] bf16 (BatchNorm folded)
+  const char* w;        // packed weights (BatchNorm folded), layout of weight_layout(): [n tile][K unit][tap][chunk][Nt][8] bf16
   const float* bias;    // [cout] folded BatchNorm shift
   char* out;            // planar-8 bf16 destination tensor (out_planes planes of m_out positions)
   long long m_in, m_out;
@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(kCThreads, 2) convc_umma_kernel(const __grid_c
   const uint32_t b_stage = 2u * kCUnitSteps * (uint32_t)Nt * 16u;
   uint8_t* a_base = smem + 256 + 1024;
   uint8_t* b_base = a_base + (size_t)kCStages * a_stage;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
   const int n0 = blockIdx.y * Nt;
   const int KC = p.cin >> 4;                                        // K steps per tap
   const int units_per_tap = (KC + kCUnitSteps - 1) / kCUnitSteps;
@@ -248,7 +248,7 @@ __global__ void __launch_bounds__(kCThreads, 2) convc_umma_kernel(const __grid_c
 // ---------------------------------------------------------------------------------------------
 struct ConvWParams {
   const char* x;        // planar-8 bf16 input (unpadded), cin/8 planes of m_in positions
-  const char* w;        // packed weights [tap][cin/8][cout][8]
+  const char* w;        // packed weights, layout of weight_layout(): [n tile][K unit][tap][chunk][Nt][8] bf16
   const float* bias;
   char* out;            // planar-8 bf16 destination (unpadded)
   long long m_in, m_out;

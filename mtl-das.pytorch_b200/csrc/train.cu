@@ -225,7 +225,6 @@ TrainPlan* build_train_plan(int kind, int batch, int precision) {
     const int G = all_groups ? inf.ngroups : 1;
     const SrcRef sr0 = inf.g[all_groups ? 0 : g].src[src_slot_lo];
     const int dsrc = grad_of(tp, sr0.tensor);
-    const int Wp = inf.W + 1;
     const int nphase = src_slot_hi - src_slot_lo > 1 ? 4 : 1;
     for (int ph = 0; ph < nphase; ++ph) {
       ConvOpHost d{};
@@ -269,7 +268,7 @@ TrainPlan* build_train_plan(int kind, int batch, int precision) {
         if (gi == 0) accum = seen;
         // (the groups of a merged launch are the tasks' slices of one tensor at one point of the schedule: same state)
       }
-      d.epi = accum ? EPI_ACCUM : EPI_NONE;
+      d.epi = accum ? (int)EPI_ACCUM : (int)EPI_NONE;
       choose_tiling(d, (long long)p.mb * (d.H + 1) * (d.W + 1));
       p.convs.push_back(d);
       dp.conv = (int)p.convs.size() - 1;
